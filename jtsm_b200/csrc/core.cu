@@ -1,0 +1,72 @@
+// Library-wide state: ABI version, error strings, launch counter, tuning knobs.
+#include <string.h>
+
+#include <map>
+#include <mutex>
+#include <string>
+
+#include "common.cuh"
+
+namespace jtsm {
+
+std::atomic<unsigned long long> g_launch_count{0};
+
+namespace {
+std::mutex g_tuning_mu;
+std::map<std::string, int>& tuning_map() {
+  static std::map<std::string, int> m = {
+      {"roi_pool_splits", 0},      // 0 = auto
+      {"roi_pool_force_gmem", 0},  // 1 = skip the smem-plane kernel
+      {"roi_pool_bwd_algo", 0},    // 0 = auto
+      {"roi_align_bwd_algo", 0},   // 0 = auto
+  };
+  return m;
+}
+}  // namespace
+
+int tuning(const char* key, int dflt) {
+  std::lock_guard<std::mutex> lk(g_tuning_mu);
+  auto& m = tuning_map();
+  auto it = m.find(key);
+  return it == m.end() ? dflt : it->second;
+}
+
+}  // namespace jtsm
+
+extern "C" int jtsm_abi_version(void) { return JTSM_ABI_VERSION; }
+
+extern "C" const char* jtsm_error_string(int code) {
+  switch (code) {
+    case JTSM_OK: return "ok";
+    case JTSM_ERR_INVALID_ARGUMENT: return "invalid argument";
+    case JTSM_ERR_UNSUPPORTED: return "unsupported configuration";
+    case JTSM_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+    default: break;
+  }
+  if (code >= JTSM_ERR_CUDA_BASE) return cudaGetErrorString((cudaError_t)(code - JTSM_ERR_CUDA_BASE));
+  return "unknown error";
+}
+
+extern "C" unsigned long long jtsm_launch_count(void) {
+  return jtsm::g_launch_count.load(std::memory_order_relaxed);
+}
+
+extern "C" int jtsm_set_tuning(const char* key, int value) {
+  if (!key) return JTSM_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(jtsm::g_tuning_mu);
+  auto& m = jtsm::tuning_map();
+  auto it = m.find(key);
+  if (it == m.end()) return JTSM_ERR_INVALID_ARGUMENT;
+  it->second = value;
+  return JTSM_OK;
+}
+
+extern "C" int jtsm_get_tuning(const char* key, int* value) {
+  if (!key || !value) return JTSM_ERR_INVALID_ARGUMENT;
+  std::lock_guard<std::mutex> lk(jtsm::g_tuning_mu);
+  auto& m = jtsm::tuning_map();
+  auto it = m.find(key);
+  if (it == m.end()) return JTSM_ERR_INVALID_ARGUMENT;
+  *value = it->second;
+  return JTSM_OK;
+}

@@ -1,0 +1,352 @@
+// RoIPool forward / backward for sm_100a.
+//
+// Reference arithmetic: torchvision.ops.roi_pool as constructed at
+// projects/WSL/wsl/modeling/poolers.py:183-186; the same algorithm is restated
+// in-tree at projects/WSL/wsl/layers/csrc/ROILoopPool/ROILoopPool_cpu.cpp:26-79
+// (forward) and :83-123 (backward).
+//
+// B200 design (see DESIGN.md "RoIPool"):
+//   * the feature map is NCHW and one channel plane (H*W*4 B = 30 KB at 75x100)
+//     fits in shared memory, while every plane is revisited by all RoIs of its
+//     image (~220 RoIs cover each cell at config 2).  So a CTA owns one
+//     (image, channel) plane: it is read from HBM/L2 exactly once, coalesced,
+//     and all RoI bins are then scanned out of shared memory.
+//   * integer bin edges are channel independent: computed once per call into
+//     a packed table (roi_bins.cuh) instead of per output element.
+//   * threads map to consecutive (roi, bin) outputs, so for a fixed channel a
+//     warp writes contiguous 4*P*P-byte runs of the [R, C, P, P] output.
+#include "roi_bins.cuh"
+
+namespace jtsm {
+
+// ---------------------------------------------------------------------------
+// prep: bin tables + per-image RoI index range
+// ---------------------------------------------------------------------------
+__global__ void roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch,
+                                     int height, int width, float scale, int PH, int PW,
+                                     PoolWorkspace ws) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= num_rois) return;
+  const float* q = rois + (size_t)r * 5;
+  const int b = (int)q[0];
+  const RoiRect rc = roi_rect(q[1], q[2], q[3], q[4], scale);
+  const int roi_w = max(rc.ew - rc.sw + 1, 1);
+  const int roi_h = max(rc.eh - rc.sh + 1, 1);
+  for (int p = 0; p < PH; ++p) ws.hbins[(size_t)r * PH + p] = bin_range(p, rc.sh, roi_h, PH, height);
+  for (int p = 0; p < PW; ++p) ws.wbins[(size_t)r * PW + p] = bin_range(p, rc.sw, roi_w, PW, width);
+  const bool ok = (b >= 0 && b < batch);
+  ws.batch_idx[r] = ok ? b : -1;
+  if (ok) {
+    atomicMin(ws.first + b, r);
+    atomicMin(ws.neg_last + b, -r);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------
+// grid.x = batch * channels * splits ; block = kThreads
+// dynamic smem: height * pitch floats
+template <typename T, typename A, int kThreads>
+__global__ void __launch_bounds__(kThreads)
+roi_pool_fwd_kernel(const T* __restrict__ input, int channels, int height, int width, int pitch,
+                    int PH, int PW, int splits, PoolWorkspace ws,
+                    const float* __restrict__ row_scale, T* __restrict__ output,
+                    A* __restrict__ argmax) {
+  extern __shared__ float plane[];
+  const int item = blockIdx.x;
+  const int s = item % splits;
+  const int nc = item / splits;
+  const int n = nc / channels;
+  const int c = nc - n * channels;
+
+  const int first = ws.first[n];
+  const int last = -ws.neg_last[n];
+  if (first > last) return;  // image has no RoIs (uniform per CTA)
+  const int len = last - first + 1;
+  const int r0 = first + (int)(((long long)len * s) / splits);
+  const int r1 = first + (int)(((long long)len * (s + 1)) / splits);
+  if (r0 >= r1) return;
+
+  // stage the plane: coalesced read, row pitch made odd for bank spread
+  const T* src = input + (size_t)nc * height * width;
+  for (int y = threadIdx.x / 32; y < height; y += kThreads / 32) {
+    const T* row = src + (size_t)y * width;
+    float* drow = plane + y * pitch;
+    for (int x = threadIdx.x % 32; x < width; x += 32) drow[x] = Elem<T>::to_f(row[x]);
+  }
+  __syncthreads();
+
+  const int PP = PH * PW;
+  const int total = (r1 - r0) * PP;
+  for (int i = threadIdx.x; i < total; i += kThreads) {
+    const int rl = i / PP;
+    const int bin = i - rl * PP;
+    const int ph = bin / PW;
+    const int pw = bin - ph * PW;
+    const int r = r0 + rl;
+    const size_t o = ((size_t)r * channels + c) * PP + bin;
+    if (ws.batch_idx[r] != n) continue;  // only when RoIs are not grouped by image
+    const uint32_t hb = __ldg(ws.hbins + (size_t)r * PH + ph);
+    const uint32_t wb = __ldg(ws.wbins + (size_t)r * PW + pw);
+    const int hs = range_lo(hb), he = range_hi(hb);
+    const int wstart = range_lo(wb), wend = range_hi(wb);
+    const bool empty = (he <= hs) || (wend <= wstart);
+    float m = empty ? 0.f : -FLT_MAX;
+    int mi = -1;
+    for (int h = hs; h < he; ++h) {
+      const float* prow = plane + h * pitch;
+      for (int w = wstart; w < wend; ++w) {
+        const float v = prow[w];
+        if (v > m) {
+          m = v;
+          mi = h * width + w;
+        }
+      }
+    }
+    if (row_scale) m = __fmul_rn(m, row_scale[r]);
+    output[o] = Elem<T>::from_f(m);
+    argmax[o] = Arg<A>::enc(mi);
+  }
+}
+
+// Fallback for planes that do not fit in shared memory: same mapping, reads the
+// plane through L1/L2.
+template <typename T, typename A, int kThreads>
+__global__ void __launch_bounds__(kThreads)
+roi_pool_fwd_gmem_kernel(const T* __restrict__ input, int channels, int height, int width,
+                         int PH, int PW, int splits, PoolWorkspace ws,
+                         const float* __restrict__ row_scale, T* __restrict__ output,
+                         A* __restrict__ argmax) {
+  const int item = blockIdx.x;
+  const int s = item % splits;
+  const int nc = item / splits;
+  const int n = nc / channels;
+  const int c = nc - n * channels;
+  const int first = ws.first[n];
+  const int last = -ws.neg_last[n];
+  if (first > last) return;
+  const int len = last - first + 1;
+  const int r0 = first + (int)(((long long)len * s) / splits);
+  const int r1 = first + (int)(((long long)len * (s + 1)) / splits);
+  const T* src = input + (size_t)nc * height * width;
+  const int PP = PH * PW;
+  const int total = (r1 - r0) * PP;
+  for (int i = threadIdx.x; i < total; i += kThreads) {
+    const int rl = i / PP;
+    const int bin = i - rl * PP;
+    const int ph = bin / PW;
+    const int pw = bin - ph * PW;
+    const int r = r0 + rl;
+    const size_t o = ((size_t)r * channels + c) * PP + bin;
+    if (ws.batch_idx[r] != n) continue;
+    const uint32_t hb = __ldg(ws.hbins + (size_t)r * PH + ph);
+    const uint32_t wb = __ldg(ws.wbins + (size_t)r * PW + pw);
+    const int hs = range_lo(hb), he = range_hi(hb);
+    const int wstart = range_lo(wb), wend = range_hi(wb);
+    const bool empty = (he <= hs) || (wend <= wstart);
+    float m = empty ? 0.f : -FLT_MAX;
+    int mi = -1;
+    for (int h = hs; h < he; ++h) {
+      const T* prow = src + (size_t)h * width;
+      for (int w = wstart; w < wend; ++w) {
+        const float v = Elem<T>::to_f(__ldg(prow + w));
+        if (v > m) {
+          m = v;
+          mi = h * width + w;
+        }
+      }
+    }
+    if (row_scale) m = __fmul_rn(m, row_scale[r]);
+    output[o] = Elem<T>::from_f(m);
+    argmax[o] = Arg<A>::enc(mi);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// backward, variant 0: one RED per output element straight into L2
+// (grad_input fp32; 16-bit gradients accumulate in an fp32 workspace).
+// ---------------------------------------------------------------------------
+template <typename T, typename A>
+__global__ void __launch_bounds__(256)
+roi_pool_bwd_red_kernel(const T* __restrict__ grad_output, long long sn, long long sc, long long sh,
+                        long long sw, const float* __restrict__ rois, const A* __restrict__ argmax,
+                        int batch, int channels, int hw, int num_rois, int PH, int PW,
+                        const float* __restrict__ row_scale, float* __restrict__ grad_acc) {
+  const int PP = PH * PW;
+  const long long total = (long long)num_rois * channels * PP;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const int a = Arg<A>::dec(argmax[e]);
+    if (a < 0) continue;
+    const int bin = (int)(e % PP);
+    const long long rc = e / PP;
+    const int c = (int)(rc % channels);
+    const int r = (int)(rc / channels);
+    const int b = (int)__ldg(rois + (size_t)r * 5);
+    if (b < 0 || b >= batch) continue;
+    const int ph = bin / PW, pw = bin - ph * PW;
+    float g = Elem<T>::to_f(grad_output[r * sn + c * sc + ph * sh + pw * sw]);
+    if (row_scale) g = __fmul_rn(g, row_scale[r]);
+    atomicAdd(grad_acc + ((size_t)b * channels + c) * hw + a, g);
+  }
+}
+
+template <typename T>
+__global__ void convert_from_f32_kernel(const float* __restrict__ src, T* __restrict__ dst, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = Elem<T>::from_f(src[i]);
+}
+
+}  // namespace jtsm
+
+// ---------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------
+using namespace jtsm;
+
+namespace {
+
+constexpr int kFwdThreads = 256;
+constexpr size_t kMaxPlaneSmem = 200 * 1024;
+
+int pick_splits(int planes, int num_rois, int ctas_per_sm) {
+  // enough CTAs for ~4 waves, but keep >= 64 RoIs per CTA so the plane load amortises
+  const int forced = tuning("roi_pool_splits", 0);
+  if (forced > 0) return forced;
+  const long long target = 4LL * kNumSMs * ctas_per_sm;
+  long long s = (target + planes - 1) / planes;
+  const long long cap = num_rois / 64 > 1 ? num_rois / 64 : 1;
+  if (s > cap) s = cap;
+  if (s < 1) s = 1;
+  return (int)s;
+}
+
+template <typename T, typename A>
+int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, int width,
+                        int num_rois, int PH, int PW, const PoolWorkspace& ws,
+                        const float* row_scale, void* output, void* argmax, cudaStream_t st) {
+  const int pitch = (width & 1) ? width : width + 1;
+  const size_t smem = (size_t)height * pitch * sizeof(float);
+  const int planes = batch * channels;
+  if (smem <= kMaxPlaneSmem && !tuning("roi_pool_force_gmem", 0)) {
+    auto k = roi_pool_fwd_kernel<T, A, kFwdThreads>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxPlaneSmem);
+      attr_set = true;
+    }
+    int per_sm = (int)((227 * 1024) / (smem + 1024));
+    per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+    const int splits = pick_splits(planes, num_rois, per_sm);
+    k<<<planes * splits, kFwdThreads, smem, st>>>((const T*)input, channels, height, width, pitch, PH,
+                                                   PW, splits, ws, row_scale, (T*)output, (A*)argmax);
+  } else {
+    const int splits = pick_splits(planes, num_rois, 8);
+    roi_pool_fwd_gmem_kernel<T, A, kFwdThreads><<<planes * splits, kFwdThreads, 0, st>>>(
+        (const T*)input, channels, height, width, PH, PW, splits, ws, row_scale, (T*)output,
+        (A*)argmax);
+  }
+  count_launch();
+  return cuda_status();
+}
+
+int run_prep(const float* rois, int num_rois, int batch, int height, int width, float scale, int PH,
+             int PW, const PoolWorkspace& ws, cudaStream_t st) {
+  cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
+  roi_pool_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width,
+                                                              scale, PH, PW, ws);
+  count_launch();
+  return cuda_status();
+}
+
+}  // namespace
+
+extern "C" size_t jtsm_roi_pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w) {
+  if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0) return 0;
+  return pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 1);
+}
+
+extern "C" int jtsm_roi_pool_forward(const void* input, const float* rois, int dtype, int batch,
+                                     int channels, int height, int width, int num_rois,
+                                     float spatial_scale, int pooled_h, int pooled_w,
+                                     const float* row_scale, void* output, void* argmax,
+                                     int argmax_dtype, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 ||
+      pooled_w <= 0 || pooled_h > 64 || pooled_w > 64)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (height > 32767 || width > 32767) return JTSM_ERR_UNSUPPORTED;
+  if (argmax_dtype == JTSM_ARGMAX_U16 && (long long)height * width >= 65535) return JTSM_ERR_INVALID_ARGUMENT;
+  if (num_rois == 0 || channels == 0) return JTSM_OK;  // nothing to write
+  if (!input || !rois || !output || !argmax || !workspace) return JTSM_ERR_INVALID_ARGUMENT;
+  if (batch == 0 || height == 0 || width == 0) return JTSM_ERR_INVALID_ARGUMENT;
+  if (workspace_bytes < jtsm_roi_pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w))
+    return JTSM_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 1);
+  int rc = run_prep(rois, num_rois, batch, height, width, spatial_scale, pooled_h, pooled_w, ws, st);
+  if (rc != JTSM_OK) return rc;
+  JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
+                        rc = launch_roi_pool_fwd<T, A>(input, batch, channels, height, width,
+                                                       num_rois, pooled_h, pooled_w, ws, row_scale,
+                                                       output, argmax, st);
+                      }));
+  return rc;
+}
+
+extern "C" size_t jtsm_roi_pool_backward_workspace_bytes(int dtype, int batch, int channels,
+                                                         int height, int width) {
+  if (dtype == JTSM_F32) return 256;
+  return (size_t)batch * channels * height * width * sizeof(float) + 256;
+}
+
+extern "C" int jtsm_roi_pool_backward(const void* grad_output, long long stride_n,
+                                      long long stride_c, long long stride_h, long long stride_w,
+                                      const float* rois, const void* argmax, int argmax_dtype,
+                                      int dtype, int batch, int channels, int height, int width,
+                                      int num_rois, int pooled_h, int pooled_w,
+                                      const float* row_scale, void* grad_input, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 ||
+      pooled_w <= 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  const size_t n_in = (size_t)batch * channels * height * width;
+  if (n_in == 0) return JTSM_OK;
+  if (!grad_input) return JTSM_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t esz = dtype == JTSM_F32 ? 4 : 2;
+  float* acc = (float*)grad_input;
+  if (dtype != JTSM_F32) {
+    if (!workspace || workspace_bytes < jtsm_roi_pool_backward_workspace_bytes(dtype, batch, channels, height, width))
+      return JTSM_ERR_WORKSPACE_TOO_SMALL;
+    acc = (float*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  }
+  cudaMemsetAsync(acc, 0, n_in * sizeof(float), st);
+  (void)esz;
+  const long long total = (long long)num_rois * channels * pooled_h * pooled_w;
+  int rc = JTSM_OK;
+  if (total > 0) {
+    if (!grad_output || !rois || !argmax) return JTSM_ERR_INVALID_ARGUMENT;
+    long long blocks = (total + 255) / 256;
+    const long long cap = (long long)kNumSMs * 8 * 4;
+    if (blocks > cap) blocks = cap;
+    JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
+                          roi_pool_bwd_red_kernel<T, A><<<(int)blocks, 256, 0, st>>>(
+                              (const T*)grad_output, stride_n, stride_c, stride_h, stride_w, rois,
+                              (const A*)argmax, batch, channels, height * width, num_rois, pooled_h,
+                              pooled_w, row_scale, acc);
+                        }));
+    count_launch();
+    rc = cuda_status();
+    if (rc != JTSM_OK) return rc;
+  }
+  if (dtype == JTSM_BF16) {
+    convert_from_f32_kernel<__nv_bfloat16><<<kNumSMs * 8, 256, 0, st>>>(acc, (__nv_bfloat16*)grad_input, n_in);
+    count_launch();
+  } else if (dtype == JTSM_F16) {
+    convert_from_f32_kernel<__half><<<kNumSMs * 8, 256, 0, st>>>(acc, (__half*)grad_input, n_in);
+    count_launch();
+  }
+  return cuda_status();
+}

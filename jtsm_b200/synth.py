@@ -1,0 +1,92 @@
+"""Seeded synthetic inputs for the BASELINE.json configurations.
+
+Everything is generated on the host with a CPU torch.Generator so that the CPU oracle
+and the GPU see identical bits.  seed = 20210600 + 100 * config + sweep_index.
+"""
+import math
+
+import torch
+
+CONFIGS = {
+    # name: dict(N, C, stride, img_h, img_w, R (per image), P, K, Kr, reg)
+    "c1": dict(N=1, C=512, stride=16, img_h=600, img_w=800, R=2000, P=7, K=20, Kr=0, reg=False),
+    "c2": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=2000, P=7, K=20, Kr=3, reg=False),
+    "c3": dict(N=2, C=2048, stride=8, img_h=600, img_w=800, R=4000, P=7, K=80, Kr=4, reg=True),
+    "c4": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=4000, P=7, K=20, Kr=3, reg=False),
+}
+
+
+def seed_for(config_index, sweep_index=0):
+    return 20210600 + 100 * int(config_index) + int(sweep_index)
+
+
+def generator(seed):
+    g = torch.Generator(device="cpu")
+    g.manual_seed(int(seed))
+    return g
+
+
+def feature_map(g, n, c, h, w):
+    """relu(randn): non-negative like a post-ReLU conv5 map (ROILoopPool assumes >= 0)."""
+    return torch.relu(torch.randn(n, c, h, w, generator=g))
+
+
+def proposals(g, num, img_h, img_w, min_size=20.0):
+    """MCG-like boxes [num,4] xyxy fp32: centre ~ U(image), sqrt(area) ~ logU(min_size,
+    min(H,W)), aspect ~ logU(1/3, 3), clipped to the image."""
+    cx = torch.rand(num, generator=g) * img_w
+    cy = torch.rand(num, generator=g) * img_h
+    lo, hi = math.log(min_size), math.log(float(min(img_h, img_w)))
+    s = torch.exp(lo + torch.rand(num, generator=g) * (hi - lo))
+    a = torch.exp((torch.rand(num, generator=g) * 2 - 1) * math.log(3.0))
+    w = s * torch.sqrt(a)
+    h = s / torch.sqrt(a)
+    x1 = (cx - w / 2).clamp(0, img_w)
+    y1 = (cy - h / 2).clamp(0, img_h)
+    x2 = (cx + w / 2).clamp(0, img_w)
+    y2 = (cy + h / 2).clamp(0, img_h)
+    # keep boxes non-degenerate (>= 1 px) like the reference's proposal filtering
+    x2 = torch.maximum(x2, x1 + 1.0).clamp(max=img_w)
+    y2 = torch.maximum(y2, y1 + 1.0).clamp(max=img_h)
+    x1 = torch.minimum(x1, x2 - 1.0)
+    y1 = torch.minimum(y1, y2 - 1.0)
+    return torch.stack([x1, y1, x2, y2], dim=1).float()
+
+
+def random_boxes(g, num, max_coord=100):
+    """Same construction as detectron2/utils/testing.py:29-40 `random_boxes`."""
+    boxes = torch.rand(num, 4, generator=g) * (max_coord * 0.5)
+    boxes.clamp_(min=1.0)
+    boxes[:, 2:] += boxes[:, :2]
+    return boxes
+
+
+def rois_from_boxes(boxes_per_image):
+    parts = []
+    for i, b in enumerate(boxes_per_image):
+        parts.append(torch.cat([torch.full((b.shape[0], 1), float(i)), b], dim=1))
+    return torch.cat(parts, dim=0)
+
+
+def image_labels(g, n, k, max_classes=3):
+    """Per image: sorted distinct class ids (1..max_classes of them)."""
+    out = []
+    for _ in range(n):
+        m = int(torch.randint(1, max_classes + 1, (1,), generator=g))
+        out.append(torch.randperm(k, generator=g)[:m].sort().values.to(torch.int64))
+    return out
+
+
+def pool_case(name, sweep_index=0, **over):
+    """Feature map + rois (+ objectness) for a named config."""
+    cfg = dict(CONFIGS[name])
+    cfg.update(over)
+    g = generator(seed_for(int(name[1:]), sweep_index))
+    h = int(math.ceil(cfg["img_h"] / cfg["stride"]))
+    w = int(math.ceil(cfg["img_w"] / cfg["stride"]))
+    feat = feature_map(g, cfg["N"], cfg["C"], h, w)
+    boxes = [proposals(g, cfg["R"], cfg["img_h"], cfg["img_w"]) for _ in range(cfg["N"])]
+    rois = rois_from_boxes(boxes)
+    obj = torch.rand(rois.shape[0], generator=g)
+    cfg.update(H=h, W=w, scale=1.0 / cfg["stride"])
+    return cfg, feat, boxes, rois, obj
