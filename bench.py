@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""bench.py -- RoIs/sec fwd+bwd over (pool + MIL + refine) for the JTSM hot path on B200.
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W [--impl reference]`;
+for N>1 launched under torch.distributed.run (one rank per GPU).  Rank 0 prints ONE JSON line.
+
+A "step" = one pass of the hot path over one image batch of the named workload
+(SURVEY.md 8d): pool fwd (x objectness) -> [given head logits] WSDDN MIL fwd + BCE ->
+Kr x (pseudo-gt top-k -> IoU label assignment -> weighted CE [+ box reg] -> softmax) ->
+backward of all of it (d logits) and RoIPool backward down to grad_feature.
+fc6/fc7 GEMMs are excluded (they stay in torch).
+
+  value : RoIs/s, whole job, inputs resident in HBM, CUDA-event timed, L2 flushed
+          (256 MiB write) between timed steps.
+  e2e   : same step driven from pinned HOST buffers through the public ops layer
+          (-> C ABI), H2D of feature map / rois / logits and D2H of losses + grad_feature
+          inside the timed region.
+  roofline : dominant kernel (RoIPool forward): algorithmic bytes / its CUDA-event time.
+  cpu_baseline : the CPU oracle port (oracle/jtsm_oracle.c, host threads) on a bounded
+          sample of the same workload.  --impl reference times the reference's own CPU
+          path (torchvision CPU roi_pool + the eager-PyTorch head composition).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "rois_per_sec_fwd_bwd_pool_mil_refine"
+UNIT = "RoIs/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c2")
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-rois", type=int, default=0, help="0 = auto (about 10-30 s)")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            d = json.load(fh)
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [t.strip() for t in l.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------
+# workload
+# ----------------------------------------------------------------------------------------------
+def make_workload(name, rank, dtype):
+    import torch
+
+    from jtsm_b200 import synth
+
+    w = synth.step_case(name, sweep_index=rank)
+    if dtype == "bf16":
+        w["feat"] = w["feat"].bfloat16()
+        w["grad_pooled_seed"] = w["grad_pooled_seed"]
+    return w
+
+
+def algorithmic_bytes(cfg, esz):
+    """compulsory traffic only."""
+    n, c, h, w_, r, p, k, kr = cfg["N"], cfg["C"], cfg["H"], cfg["W"], cfg["N"] * cfg["R"], cfg["P"], cfg["K"], cfg["Kr"]
+    pool_fwd = n * c * h * w_ * esz + 20 * r + r * c * p * p * esz
+    pool_bwd = r * c * p * p * esz + n * c * h * w_ * esz + 20 * r
+    mil = 7 * r * k * 4
+    refine = kr * (r * (16 + 12 + 3 * (k + 1) * 4) + (r * (16 + 2 * 4 * k * 4) if cfg.get("reg") else 0))
+    return dict(pool_fwd=pool_fwd, pool_bwd=pool_bwd, mil=mil, refine=refine,
+                step=pool_fwd + pool_bwd + mil + refine)
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+
+    from jtsm_b200 import _lib, hotpath
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (impl=b200) needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()  # fail loudly if libjtsm_b200.so is missing
+
+    wl = make_workload(a.config, rank, a.dtype)
+    cfg = wl["cfg"]
+    R = cfg["N"] * cfg["R"]
+    esz = 2 if a.dtype == "bf16" else 4
+    step = hotpath.HotPathStep(cfg, dev, dtype=torch.bfloat16 if a.dtype == "bf16" else torch.float32)
+    host = step.pin_host_inputs(wl)
+    resident = step.upload(host)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---------------- device-resident timing (value) ----------------
+    for _ in range(max(a.warmup, 3)):
+        step.run(resident)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lc0 = _lib.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    kev = []
+    barrier()
+    t_wall0 = time.perf_counter()
+    for i in range(a.steps):
+        flush.zero_()
+        ev[i][0].record()
+        kev.append(step.run(resident, time_dominant=True))
+        ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = _lib.launch_count() - lc0
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
+    dom_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / len(kev)
+
+    # ---------------- end-to-end from host buffers (e2e) ----------------
+    for _ in range(3):
+        step.run_from_host(host)
+    barrier()
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    for i in range(a.steps):
+        flush.zero_()
+        ev2[i][0].record()
+        step.run_from_host(host)  # ends with a blocking D2H of the results
+        ev2[i][1].record()
+    barrier()
+    e2e_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev2)
+
+    tm = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = (float(v) for v in tm.tolist())
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        ab = algorithmic_bytes(cfg, esz)
+        ach = ab["pool_fwd"] / (dom_ms * 1e-3) / 1e9
+        out = {
+            "metric": METRIC, "value": world * R * a.steps / (dev_ms * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": dev_ms / a.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32" if a.dtype == "fp32" else "bf16",
+            "data": "synthetic (seeded MCG-like proposals, relu(randn) conv5 map, random head logits)",
+            "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
+                       "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
+                       "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool",
+                       "l2": "flushed (256 MiB write) between timed steps", "stages": step.stages()},
+            "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes()},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": step.dominant_kernel(), "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "peak_source": peak_src, "traffic": step.ncu_traffic(),
+                         "algorithmic_bytes_per_launch": ab["pool_fwd"], "avg_launch_ms": dom_ms,
+                         "step_algorithmic_bytes": ab["step"],
+                         "step_frac": ab["step"] / (dev_ms / a.steps * 1e-3) / 1e9 / peak},
+            "clocks": clocks,
+            "wall_s_timed_region": t_wall,
+        }
+        if not a.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(wl, a, kind="port")
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU legs (the only places that execute oracle/)
+# ----------------------------------------------------------------------------------------------
+def cpu_baseline(wl, a, kind):
+    from oracle import cpu_step
+
+    cores = os.cpu_count() or 1
+    sample = a.cpu_sample_rois or cpu_step.auto_sample_rois(wl, kind)
+    t, n_rois, desc = cpu_step.time_step(wl, sample_rois=sample, threads=cores, kind=kind)
+    return {"value": n_rois / t, "unit": UNIT, "cores": cores, "kind": kind, "sample": desc, "seconds": t}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    from oracle import cpu_step
+
+    wl = make_workload(a.config, 0, "fp32")
+    cfg = wl["cfg"]
+    cores = os.cpu_count() or 1
+    sample = a.cpu_sample_rois or cpu_step.auto_sample_rois(wl, "reference", budget_s=6.0)
+    for _ in range(max(1, min(a.warmup, 1))):
+        cpu_step.time_step(wl, sample_rois=sample, threads=cores, kind="reference")
+    ts = []
+    desc = ""
+    for _ in range(a.steps):
+        t, n_rois, desc = cpu_step.time_step(wl, sample_rois=sample, threads=cores, kind="reference")
+        ts.append(t)
+    v = n_rois * len(ts) / sum(ts)
+    out = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 * sum(ts) / len(ts), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
+                   "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
+                   "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": desc},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

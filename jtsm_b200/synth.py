@@ -90,3 +90,31 @@ def pool_case(name, sweep_index=0, **over):
     obj = torch.rand(rois.shape[0], generator=g)
     cfg.update(H=h, W=w, scale=1.0 / cfg["stride"])
     return cfg, feat, boxes, rois, obj
+
+
+def step_case(name, sweep_index=0, **over):
+    """Everything one hot-path step consumes, generated on the host:
+    feature map, proposals, objectness, image labels, MIL logits (C, D), per-branch refinement
+    logits (+ deltas when box regression is on) and the gradient that fc6's backward would
+    hand to the pooling op."""
+    cfg, feat, boxes, rois, obj = pool_case(name, sweep_index, **over)
+    g = generator(seed_for(int(name[1:]), sweep_index) + 7)
+    r_total, k = rois.shape[0], cfg["K"]
+    labels = image_labels(g, cfg["N"], k, max_classes=3 if k <= 20 else 7)
+    sigma = 5.0
+    mil_cls = torch.randn(r_total, k, generator=g) * sigma
+    mil_det = torch.randn(r_total, k, generator=g) * sigma
+    ref_logits = [torch.randn(r_total, k + 1, generator=g) for _ in range(cfg["Kr"])]
+    ref_deltas = [torch.randn(r_total, 4 * k, generator=g) * 0.1 for _ in range(cfg["Kr"])] if cfg["reg"] else []
+    n_pooled = r_total * cfg["C"] * cfg["P"] * cfg["P"]
+    # one [C,P,P] gradient tile per RoI-slot mod 64 keeps host memory bounded at config 3
+    tile = torch.randn(min(r_total, 64), cfg["C"], cfg["P"], cfg["P"], generator=g)
+    return dict(name=name, cfg=cfg, feat=feat, boxes=boxes, rois=rois, objectness=obj, labels=labels,
+                mil_cls=mil_cls, mil_det=mil_det, ref_logits=ref_logits, ref_deltas=ref_deltas,
+                grad_tile=tile, n_pooled=n_pooled)
+
+
+def expand_grad_tile(tile, num_rois):
+    """grad_pooled[r] = tile[r % tile.shape[0]] (host or device)."""
+    reps = (num_rois + tile.shape[0] - 1) // tile.shape[0]
+    return tile.repeat(reps, 1, 1, 1)[:num_rois].contiguous()

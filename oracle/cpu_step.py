@@ -1,0 +1,66 @@
+"""CPU timing legs of bench.py (TEST / BASELINE INFRASTRUCTURE -- never imported by jtsm_b200/).
+
+kind="port":      oracle/jtsm_oracle.c (plain C restatement), fanned out over host threads by RoI range.
+kind="reference": what the reference itself executes with MODEL.DEVICE=cpu for this path:
+                  torchvision CPU roi_pool fwd+bwd (projects/WSL/wsl/modeling/poolers.py:183-186) and the
+                  eager-PyTorch head composition (oracle/ref_heads.py restates it; no CPU op exists).
+Both run a BOUNDED sample: the first `sample_rois` proposals of the workload's first image.
+"""
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+import torch
+
+from jtsm_b200 import synth
+
+from . import capi
+
+
+def auto_sample_rois(wl, kind, budget_s=15.0):
+    cfg = wl["cfg"]
+    # measured here: ~0.6 ms / RoI / 512 channels single-threaded for pool fwd+bwd at stride 8
+    per_roi = 1.2e-3 * cfg["C"] / 512.0
+    n = int(budget_s / per_roi)
+    return max(64, min(n, cfg["R"]))
+
+
+def _sample(wl, sample_rois):
+    rois = wl["rois"]
+    first = rois[rois[:, 0] == 0][:sample_rois].contiguous()
+    return first
+
+
+def time_step(wl, sample_rois, threads, kind):
+    cfg = wl["cfg"]
+    rois = _sample(wl, sample_rois)
+    r = rois.shape[0]
+    x = wl["feat"][:1].float().contiguous()
+    P = (cfg["P"], cfg["P"])
+    g = synth.expand_grad_tile(wl["grad_tile"], r)
+    scale = (wl["objectness"][:r] + 1.0)
+    desc = "first %d of %d proposals of image 0 of %s (pool fwd+bwd), %d threads" % (r, cfg["R"], wl["name"], threads)
+    if kind == "reference":
+        import torchvision
+
+        torch.set_num_threads(threads)
+        t0 = time.perf_counter()
+        xg = x.clone().requires_grad_()
+        out = torchvision.ops.roi_pool(xg, rois, P, cfg["scale"]) * scale.view(-1, 1, 1, 1)
+        out.backward(g)
+        t = time.perf_counter() - t0
+        return t, r, desc + ", torchvision CPU roi_pool"
+    xn, rn, gn = x.numpy(), rois.numpy(), (g * scale.view(-1, 1, 1, 1)).numpy()
+    capi.lib()
+    chunks = [(i * r // threads, (i + 1) * r // threads) for i in range(threads)]
+    t0 = time.perf_counter()
+
+    def work(rng):
+        out, arg = capi.roi_pool_forward(xn, rn, cfg["scale"], P, roi_range=rng)
+        return capi.max_pool_backward(gn[rng[0]:rng[1]], arg[rng[0]:rng[1]], rn[rng[0]:rng[1]], tuple(x.shape))
+
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(work, chunks))
+    gi = np.sum(parts, axis=0)
+    t = time.perf_counter() - t0
+    return t, r, desc + ", oracle C port"
