@@ -97,6 +97,113 @@ JTSM_API int jtsm_roi_pool_backward(
     const float* row_scale, void* grad_input, void* workspace,
     size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------
+ * WSDDN two-stream MIL head: per image  scores = softmax(C, dim=1) * softmax(D, dim=0),
+ * image scores = clamp(sum_r scores, 1e-6, 1-1e-6), loss = BCE(image scores, one-hot).
+ * Replaces the eager composition in
+ *   projects/WSL/wsl/modeling/roi_heads/fast_rcnn_wsddn.py:571-584 (WSDDNOutputLayers.forward),
+ *   :364-379 (predict_probs_img) and :346-362 (binary_cross_entropy_loss; mean_loss=0 -> sum / N).
+ *
+ * cls_logits, det_logits, scores  [num_rois, num_classes] fp32 (num_classes <= 256)
+ * seg_offsets   [num_images + 1] int32, DEVICE: rows of image n are [seg[n], seg[n+1])
+ * labels_onehot [num_images, num_classes] fp32 or NULL (no loss)
+ * img_scores    [num_images, num_classes] clamped image scores (= pred_class_img_logits)
+ * col_stats     [num_images, num_classes, 3] (col max of D, col sum-exp, unclamped image sum): saved for backward
+ * loss          [1] or NULL;  grad_img [num_images, num_classes] d loss / d (unclamped image sum) or NULL
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_wsddn_workspace_bytes(int num_images);
+JTSM_API int jtsm_wsddn_forward(const float* cls_logits, const float* det_logits,
+                                const int* seg_offsets, int num_images, int num_rois,
+                                int num_classes, const float* labels_onehot, int mean_loss,
+                                float* scores, float* img_scores, float* col_stats, float* loss,
+                                float* grad_img, void* workspace, size_t workspace_bytes,
+                                void* stream);
+/* d(cls_logits), d(det_logits) for upstream gradient
+ *   g[r,k] = grad_scores[r,k] (NULL = 0) + grad_img[n(r),k] * (*grad_loss) (NULL pointers = 0 / 1). */
+JTSM_API int jtsm_wsddn_backward(const float* cls_logits, const float* det_logits,
+                                 const float* scores, const float* col_stats,
+                                 const int* seg_offsets, int num_images, int num_rois,
+                                 int num_classes, const float* grad_scores, const float* grad_img,
+                                 const float* grad_loss, float* grad_cls, float* grad_det,
+                                 void* stream);
+
+/* ------------------------------------------------------------------------
+ * OICR refinement, one branch.
+ * jtsm_refine_assign = get_pgt_top_k (top_k = 1; roi_heads_oicr.py:675-811) +
+ *   label_and_sample_proposals (roi_heads.py:263-370: pairwise_iou boxes.py:369-391, Matcher
+ *   matcher.py:61-103, _sample_proposals roi_heads.py:222-254) + the weight preparation of
+ *   OICROutputs.__init__ (fast_rcnn_oicr.py:243-247), per image, one launch.
+ *
+ * prev_scores  [num_rois, score_stride]: class k in column k (WSDDN scores: stride K; a previous
+ *              branch's softmax: stride K+1)
+ * prev_boxes   [num_rois, boxes_per_row, 4]: boxes_per_row = 1 (proposal boxes / class-agnostic)
+ *              or num_classes (class-specific predict_boxes output)
+ * proposals    [num_rois, 4]
+ * img_cls_offsets [num_images+1] int32 DEVICE, img_cls_ids int64 DEVICE: gt_classes_img_int, ragged
+ * img_scores   [num_images, num_classes]: pred_class_img_logits (pseudo-gt weights)
+ * Matcher: thresholds iou_t0 (< iou_t1 if num_thresholds == 2), labels label0..label2 in {-1,0,1}
+ * outputs: pgt_* [total seeds] (seed g of image n at img_cls_offsets[n] + g);
+ *   matched_idx int64 [R] (seed index within the image), matched_iou [R] or NULL,
+ *   gt_classes int64 [R] (class | num_classes = background | -1 = ignore), gt_weights, gt_scores [R],
+ *   gt_boxes [R,4], loss_weights [R] (gt_weights with ignored rows zeroed),
+ *   counters int32 [num_images*3 + 1]: (fg, bg, ignore) per image, then #(loss_weights > 1e-12).
+ * ------------------------------------------------------------------------ */
+JTSM_API int jtsm_refine_assign(
+    const float* prev_scores, int score_stride, const float* prev_boxes, int boxes_per_row,
+    const float* proposals, const int* seg_offsets, int num_images, int num_rois, int num_classes,
+    const int* img_cls_offsets, const long long* img_cls_ids, int max_classes_per_image,
+    const float* img_scores, float iou_t0, float iou_t1, int label0, int label1, int label2,
+    int num_thresholds, float* pgt_boxes, long long* pgt_classes, float* pgt_scores,
+    float* pgt_weights, long long* matched_idx, float* matched_iou, long long* gt_classes,
+    float* gt_weights, float* gt_scores, float* gt_boxes, float* loss_weights, int* counters,
+    void* stream);
+JTSM_API size_t jtsm_refine_workspace_bytes(void);
+/* Weighted softmax cross-entropy, forward + backward + probabilities in one launch
+ * (OICROutputs.softmax_cross_entropy_loss + _log_accuracy, fast_rcnn_oicr.py:252-298; predict_probs :744-762):
+ *   loss = loss_scale * sum_r w_r CE(logits_r, gt_r; ignore -1) / *valid_count
+ *   grad_logits = (*grad_loss) * d loss / d logits.   probs / grad_logits / acc_counters may be NULL.
+ * acc_counters int32[4]: #(argmax == gt), #fg, #(fg and argmax == gt), #(fg and argmax == background). */
+JTSM_API int jtsm_refine_ce(const float* logits, int num_rois, int num_cols,
+                            const long long* gt_classes, const float* loss_weights,
+                            const int* valid_count, const float* grad_loss, float loss_scale,
+                            float* probs, float* grad_logits, float* loss, int* acc_counters,
+                            void* workspace, size_t workspace_bytes, void* stream);
+/* out = (accumulate ? out : 0) + scale * softmax(logits, dim=1)   (predict_probs_K, fast_rcnn_oicr.py:764-783) */
+JTSM_API int jtsm_softmax_rows(const float* logits, int num_rois, int num_cols, float scale,
+                               int accumulate, float* out, void* stream);
+/* Box regression loss of a refinement branch (OICROutputs.box_reg_loss, fast_rcnn_oicr.py:300-380):
+ * smooth-L1 (beta; < 1e-5 = L1) between pred_deltas[fg rows, gt-class columns] and
+ * Box2BoxTransform.get_deltas(proposals, gt_boxes) (box_regression.py:38-71), times loss_weights[r]
+ * when given ("smooth_l1_weighted"), summed, / num_rois.  grad_deltas dense [R, boxes_per_row*4] or NULL. */
+JTSM_API int jtsm_refine_box_reg(const float* pred_deltas, int boxes_per_row,
+                                 const float* proposals, const float* gt_boxes,
+                                 const long long* gt_classes, const float* loss_weights,
+                                 int num_rois, int num_classes, float wx, float wy, float ww,
+                                 float wh, float smooth_l1_beta, const float* grad_loss,
+                                 float loss_scale, float* loss, float* grad_deltas,
+                                 void* workspace, size_t workspace_bytes, void* stream);
+/* Box2BoxTransform.apply_deltas (box_regression.py:73-109): out [R, boxes_per_row, 4];
+ * deltas are multiplied by delta_scale first (1.0, or 1/Kr for predict_boxes_K). */
+JTSM_API int jtsm_apply_deltas(const float* deltas, const float* boxes, int num_rois,
+                               int boxes_per_row, float wx, float wy, float ww, float wh,
+                               float scale_clamp, float delta_scale, float* out, void* stream);
+/* pairwise_iou(boxes1 [n1,4], boxes2 [n2,4]) -> out [n1, n2]  (detectron2/structures/boxes.py:369-391) */
+JTSM_API int jtsm_pairwise_iou(const float* boxes1, int n1, const float* boxes2, int n2,
+                               float* out, void* stream);
+
+/* ------------------------------------------------------------------------
+ * batched_nms (detectron2/layers/nms.py:10-30 -> torchvision.ops.nms per class):
+ * greedy NMS inside each class (idxs int64 or NULL = one class), suppress IoU > iou_threshold,
+ * candidates visited in descending score (ties: lower index first).
+ * keep int64 [num_boxes]: first *num_keep entries = kept indices in descending-score order,
+ * rest = -1.  num_keep int64 [1] DEVICE.  Never synchronises.
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_nms_workspace_bytes(int num_boxes);
+JTSM_API int jtsm_batched_nms(const float* boxes, const float* scores, const long long* idxs,
+                              int num_boxes, float iou_threshold, long long* keep,
+                              long long* num_keep, void* workspace, size_t workspace_bytes,
+                              void* stream);
+
 #ifdef __cplusplus
 }
 #endif

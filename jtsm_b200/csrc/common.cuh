@@ -68,6 +68,13 @@ template <> struct Arg<unsigned short> {
     default: return JTSM_ERR_INVALID_ARGUMENT;                         \
   }
 
+// class-column register slots per lane (K <= 32*KT)
+#define JTSM_DISPATCH_KT(K, KT, ...)                         \
+  if ((K) <= 32) { constexpr int KT = 1; __VA_ARGS__; }      \
+  else if ((K) <= 64) { constexpr int KT = 2; __VA_ARGS__; } \
+  else if ((K) <= 128) { constexpr int KT = 4; __VA_ARGS__; }\
+  else { constexpr int KT = 8; __VA_ARGS__; }
+
 // --- warp helpers ----------------------------------------------------------
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll

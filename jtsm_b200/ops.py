@@ -111,3 +111,252 @@ def roi_pool_backward(grad, rois, argmax, input_shape, output_size, row_scale=No
             "roi_pool_backward",
         )
     return grad_input
+
+
+# --------------------------------------------------------------------------- segments
+_SEG_CACHE = {}
+
+
+def segment_offsets(counts, device):
+    """int32 device tensor [N+1] of row offsets for per-image row counts (cached per device)."""
+    key = (tuple(int(c) for c in counts), str(device))
+    t = _SEG_CACHE.get(key)
+    if t is None:
+        offs = [0]
+        for c in key[0]:
+            offs.append(offs[-1] + c)
+        t = torch.tensor(offs, dtype=torch.int32).to(device)
+        if len(_SEG_CACHE) > 256:
+            _SEG_CACHE.clear()
+        _SEG_CACHE[key] = t
+    return t
+
+
+def _f32c(t):
+    return t.detach().to(torch.float32).contiguous()
+
+
+# --------------------------------------------------------------------------- WSDDN MIL head
+def wsddn_forward(cls_logits, det_logits, num_preds_per_image, labels_onehot=None, mean_loss=True):
+    """-> dict(scores [R,K], img_scores [N,K] (clamped), loss [1] | None, grad_img, col_stats, seg).
+    fast_rcnn_wsddn.py:571-584, 346-379."""
+    _require_cuda(cls_logits, det_logits, labels_onehot)
+    C, D = _f32c(cls_logits), _f32c(det_logits)
+    r, k = C.shape
+    n = len(num_preds_per_image)
+    assert sum(int(c) for c in num_preds_per_image) == r and D.shape == C.shape
+    dev = C.device
+    seg = segment_offsets(num_preds_per_image, dev)
+    scores = torch.empty_like(C)
+    img_scores = torch.empty((n, k), dtype=torch.float32, device=dev)
+    col_stats = torch.empty((n, k, 3), dtype=torch.float32, device=dev)
+    loss = grad_img = None
+    if labels_onehot is not None:
+        labels_onehot = _f32c(labels_onehot)
+        assert labels_onehot.shape == (n, k)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        grad_img = torch.empty((n, k), dtype=torch.float32, device=dev)
+    L = lib()
+    ws_bytes = L.jtsm_wsddn_workspace_bytes(n)
+    ws = _workspace(ws_bytes, dev)
+    with torch.cuda.device(dev):
+        check(L.jtsm_wsddn_forward(_ptr(C), _ptr(D), _ptr(seg), n, r, k, _ptr(labels_onehot), int(bool(mean_loss)),
+                                   _ptr(scores), _ptr(img_scores), _ptr(col_stats), _ptr(loss), _ptr(grad_img),
+                                   _ptr(ws), ws_bytes, _stream()), "wsddn_forward")
+    return dict(scores=scores, img_scores=img_scores, loss=loss, grad_img=grad_img, col_stats=col_stats, seg=seg,
+                cls=C, det=D, n=n)
+
+
+def wsddn_backward(fwd, grad_scores=None, grad_loss=None, use_loss=True):
+    """-> (grad_cls, grad_det) for the state returned by wsddn_forward."""
+    C, D = fwd["cls"], fwd["det"]
+    r, k = C.shape
+    dC, dD = torch.empty_like(C), torch.empty_like(D)
+    if r == 0:
+        return dC, dD
+    if grad_scores is not None:
+        grad_scores = _f32c(grad_scores)
+    if grad_loss is not None:
+        grad_loss = _f32c(grad_loss).reshape(1)
+    gi = fwd["grad_img"] if use_loss else None
+    with torch.cuda.device(C.device):
+        check(lib().jtsm_wsddn_backward(_ptr(C), _ptr(D), _ptr(fwd["scores"]), _ptr(fwd["col_stats"]), _ptr(fwd["seg"]),
+                                        fwd["n"], r, k, _ptr(grad_scores), _ptr(gi), _ptr(grad_loss), _ptr(dC), _ptr(dD),
+                                        _stream()), "wsddn_backward")
+    return dC, dD
+
+
+# --------------------------------------------------------------------------- refinement branch
+_CLS_CACHE = {}
+
+
+def image_class_lists(gt_classes_img_int, device):
+    """(offsets int32 [N+1], ids int64 [total], max per image) on `device` for ragged per-image class lists."""
+    key = (tuple(tuple(int(v) for v in (c.tolist() if torch.is_tensor(c) else c)) for c in gt_classes_img_int), str(device))
+    hit = _CLS_CACHE.get(key)
+    if hit is None:
+        offs, ids = [0], []
+        for c in key[0]:
+            ids.extend(c)
+            offs.append(len(ids))
+        hit = (torch.tensor(offs, dtype=torch.int32).to(device), torch.tensor(ids, dtype=torch.int64).to(device),
+               max([len(c) for c in key[0]] + [0]), len(ids))
+        if len(_CLS_CACHE) > 256:
+            _CLS_CACHE.clear()
+        _CLS_CACHE[key] = hit
+    return hit
+
+
+def refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int, img_scores, num_classes,
+                  iou_thresholds=(0.5,), iou_labels=(0, 1), want_iou=False):
+    """Pseudo-gt (top-1 per image class) + IoU label assignment (roi_heads_oicr.py:675-811, roi_heads.py:263-370)."""
+    _require_cuda(prev_scores, prev_boxes, proposals, img_scores)
+    S, P = _f32c(prev_scores), _f32c(proposals)
+    Bx = _f32c(prev_boxes)
+    dev = S.device
+    r = S.shape[0]
+    n = len(num_preds_per_image)
+    bpr = 1 if Bx.numel() == r * 4 else num_classes
+    assert Bx.numel() == r * bpr * 4 and P.shape == (r, 4)
+    seg = segment_offsets(num_preds_per_image, dev)
+    coff, cids, cmax, ctot = image_class_lists(gt_classes_img_int, dev)
+    img_scores = _f32c(img_scores)
+    assert img_scores.shape == (n, num_classes)
+    thr = list(iou_thresholds)
+    lab = list(iou_labels)
+    assert len(thr) in (1, 2) and len(lab) == len(thr) + 1
+    f = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+    i64 = lambda *s: torch.zeros(s, dtype=torch.int64, device=dev)
+    out = dict(pgt_boxes=f(ctot, 4), pgt_classes=i64(ctot), pgt_scores=f(ctot), pgt_weights=f(ctot),
+               matched_idx=i64(r), matched_iou=f(r) if want_iou else None, gt_classes=i64(r), gt_weights=f(r),
+               gt_scores=f(r), gt_boxes=f(r, 4), loss_weights=f(r),
+               counters=torch.zeros(n * 3 + 1, dtype=torch.int32, device=dev), pgt_offsets=coff)
+    with torch.cuda.device(dev):
+        check(lib().jtsm_refine_assign(
+            _ptr(S), S.shape[1], _ptr(Bx), bpr, _ptr(P), _ptr(seg), n, r, num_classes, _ptr(coff), _ptr(cids), cmax,
+            _ptr(img_scores), float(thr[0]), float(thr[1]) if len(thr) > 1 else 0.0, int(lab[0]), int(lab[1]),
+            int(lab[2]) if len(lab) > 2 else 0, len(thr), _ptr(out["pgt_boxes"]), _ptr(out["pgt_classes"]),
+            _ptr(out["pgt_scores"]), _ptr(out["pgt_weights"]), _ptr(out["matched_idx"]), _ptr(out["matched_iou"]),
+            _ptr(out["gt_classes"]), _ptr(out["gt_weights"]), _ptr(out["gt_scores"]), _ptr(out["gt_boxes"]),
+            _ptr(out["loss_weights"]), _ptr(out["counters"]), _stream()), "refine_assign")
+    out["valid_count"] = out["counters"][n * 3:]
+    return out
+
+
+def refine_ce(logits, gt_classes, loss_weights, valid_count, grad_loss=None, loss_scale=1.0, want_probs=True,
+              want_grad=True, want_acc=True):
+    """Weighted CE fwd+bwd + softmax (fast_rcnn_oicr.py:282-298, 744-762) -> dict(loss, probs, grad_logits, acc)."""
+    _require_cuda(logits, gt_classes, loss_weights, valid_count)
+    X = _f32c(logits)
+    r, kc = X.shape
+    dev = X.device
+    gt = gt_classes.to(torch.int64).contiguous()
+    w = _f32c(loss_weights)
+    vc = valid_count.to(torch.int32).contiguous()
+    probs = torch.empty_like(X) if want_probs else None
+    grad = torch.empty_like(X) if want_grad else None
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    acc = torch.empty(4, dtype=torch.int32, device=dev) if want_acc else None
+    if grad_loss is not None:
+        grad_loss = _f32c(grad_loss).reshape(1)
+    L = lib()
+    wsb = L.jtsm_refine_workspace_bytes()
+    ws = _workspace(wsb, dev)
+    with torch.cuda.device(dev):
+        check(L.jtsm_refine_ce(_ptr(X), r, kc, _ptr(gt), _ptr(w), _ptr(vc), _ptr(grad_loss), float(loss_scale), _ptr(probs),
+                               _ptr(grad), _ptr(loss), _ptr(acc), _ptr(ws), wsb, _stream()), "refine_ce")
+    return dict(loss=loss, probs=probs, grad_logits=grad, acc=acc)
+
+
+def softmax_rows(logits, out=None, scale=1.0, accumulate=False):
+    _require_cuda(logits)
+    X = _f32c(logits)
+    if out is None:
+        out = torch.empty_like(X)
+        accumulate = False
+    with torch.cuda.device(X.device):
+        check(lib().jtsm_softmax_rows(_ptr(X), X.shape[0], X.shape[1], float(scale), int(bool(accumulate)), _ptr(out),
+                                      _stream()), "softmax_rows")
+    return out
+
+
+def refine_box_reg(pred_deltas, proposals, gt_boxes, gt_classes, loss_weights, num_classes, weights=(10.0, 10.0, 5.0, 5.0),
+                   smooth_l1_beta=0.0, grad_loss=None, loss_scale=1.0, want_grad=True):
+    """fast_rcnn_oicr.py:300-380 -> dict(loss, grad_deltas).  loss_weights=None -> plain "smooth_l1"."""
+    _require_cuda(pred_deltas, proposals, gt_boxes, gt_classes, loss_weights)
+    Dl, P, G = _f32c(pred_deltas), _f32c(proposals), _f32c(gt_boxes)
+    r = P.shape[0]
+    bpr = Dl.shape[1] // 4
+    dev = Dl.device
+    gt = gt_classes.to(torch.int64).contiguous()
+    w = _f32c(loss_weights) if loss_weights is not None else None
+    grad = torch.empty_like(Dl) if want_grad else None
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    if grad_loss is not None:
+        grad_loss = _f32c(grad_loss).reshape(1)
+    L = lib()
+    wsb = L.jtsm_refine_workspace_bytes()
+    ws = _workspace(wsb, dev)
+    with torch.cuda.device(dev):
+        check(L.jtsm_refine_box_reg(_ptr(Dl), bpr, _ptr(P), _ptr(G), _ptr(gt), _ptr(w), r, num_classes,
+                                    *(float(v) for v in weights), float(smooth_l1_beta), _ptr(grad_loss), float(loss_scale),
+                                    _ptr(loss), _ptr(grad), _ptr(ws), wsb, _stream()), "refine_box_reg")
+    return dict(loss=loss, grad_deltas=grad)
+
+
+def apply_deltas(deltas, boxes, weights=(10.0, 10.0, 5.0, 5.0), scale_clamp=None, delta_scale=1.0):
+    """Box2BoxTransform.apply_deltas (box_regression.py:73-109) -> [R, k*4]."""
+    import math
+
+    _require_cuda(deltas, boxes)
+    Dl, B = _f32c(deltas), _f32c(boxes)
+    r = B.shape[0]
+    bpr = Dl.shape[1] // 4 if r else 1
+    out = torch.empty_like(Dl)
+    if scale_clamp is None:
+        scale_clamp = math.log(1000.0 / 16)
+    with torch.cuda.device(Dl.device):
+        check(lib().jtsm_apply_deltas(_ptr(Dl), _ptr(B), r, bpr, *(float(v) for v in weights), float(scale_clamp),
+                                      float(delta_scale), _ptr(out), _stream()), "apply_deltas")
+    return out
+
+
+def pairwise_iou(boxes1, boxes2):
+    """detectron2/structures/boxes.py:369-391 on raw [n,4] tensors -> [n1, n2]."""
+    _require_cuda(boxes1, boxes2)
+    A, B = _f32c(boxes1), _f32c(boxes2)
+    out = torch.empty((A.shape[0], B.shape[0]), dtype=torch.float32, device=A.device)
+    with torch.cuda.device(A.device):
+        check(lib().jtsm_pairwise_iou(_ptr(A), A.shape[0], _ptr(B), B.shape[0], _ptr(out), _stream()), "pairwise_iou")
+    return out
+
+
+# --------------------------------------------------------------------------- NMS
+def batched_nms_raw(boxes, scores, idxs, iou_threshold):
+    """-> (keep int64 [n] padded with -1, num_keep int64 [1]) without any host sync."""
+    _require_cuda(boxes, scores, idxs)
+    B, S = _f32c(boxes), _f32c(scores)
+    n = B.shape[0]
+    dev = B.device
+    I = idxs.to(torch.int64).contiguous() if idxs is not None else None
+    keep = torch.empty(n, dtype=torch.int64, device=dev)
+    num = torch.zeros(1, dtype=torch.int64, device=dev)
+    L = lib()
+    wsb = L.jtsm_nms_workspace_bytes(n)
+    ws = _workspace(wsb, dev)
+    with torch.cuda.device(dev):
+        check(L.jtsm_batched_nms(_ptr(B), _ptr(S), _ptr(I), n, float(iou_threshold), _ptr(keep), _ptr(num), _ptr(ws), wsb,
+                                 _stream()), "batched_nms")
+    return keep, num
+
+
+def batched_nms(boxes, scores, idxs, iou_threshold):
+    """detectron2.layers.batched_nms signature (nms.py:10-30): int64 keep indices, descending score."""
+    assert boxes.shape[-1] == 4
+    keep, num = batched_nms_raw(boxes.float(), scores, idxs, iou_threshold)
+    return keep[: int(num.item())]
+
+
+def nms(boxes, scores, iou_threshold):
+    """torchvision.ops.nms signature."""
+    return batched_nms(boxes, scores, None, iou_threshold)
