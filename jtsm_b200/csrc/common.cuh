@@ -19,6 +19,7 @@ extern std::atomic<unsigned long long> g_launch_count;
 inline void count_launch(int n = 1) { g_launch_count.fetch_add(n, std::memory_order_relaxed); }
 
 int tuning(const char* key, int dflt);
+int num_sms();  // SM count of the current device (cached)
 
 inline int cuda_status() {
   cudaError_t e = cudaGetLastError();

@@ -18,6 +18,7 @@ std::map<std::string, int>& tuning_map() {
       {"roi_pool_splits", 0},      // 0 = auto
       {"roi_pool_force_gmem", 0},  // 1 = skip the smem-plane kernel
       {"roi_pool_bwd_algo", 0},    // 0 = auto
+      {"roi_pool_fwd_algo", 0},    // 0 = auto, 1 = direct smem scan, 2 = gmem scan, 3 = range-max tables
       {"roi_align_bwd_algo", 0},   // 0 = auto
   };
   return m;
@@ -29,6 +30,19 @@ int tuning(const char* key, int dflt) {
   auto& m = tuning_map();
   auto it = m.find(key);
   return it == m.end() ? dflt : it->second;
+}
+
+int num_sms() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      cached = kNumSMs;
+  }
+  return cached;
 }
 
 }  // namespace jtsm

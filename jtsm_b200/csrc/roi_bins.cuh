@@ -48,14 +48,36 @@ struct PoolWorkspace {
   int* batch_idx;    // [R]
   int* first;        // [batch]   min roi index of image n   (INT-ish max if none)
   int* neg_last;     // [batch]   -(max roi index of image n)
+  int* ungrouped;    // [1]       != 0 when batch indices are not non-decreasing in r
+  // range-max-table kernel descriptors (roi_pool_rmq.cuh)
+  uint4* hdesc;      // [R * P]  {hs*W | hl*W << 16, qh | big << 2 | empty << 3 | len << 8, row_scale bits, batch}
+  uint2* wdesc;      // [R * P]  {ws | wl << 16,     qw | big << 2 | empty << 3 | len << 8}
 };
+
+// descriptor of one axis range [s, e): level q = floor(log2(len)) capped at 3, start of the last
+// window e - 2^q, `big` when two windows of the level do not cover the range.
+__device__ __forceinline__ void rmq_axis_desc(uint32_t packed, int mult, uint32_t& x, uint32_t& y) {
+  const int s = range_lo(packed), e = range_hi(packed);
+  const int len = e - s;
+  if (len <= 0) {
+    x = 0;
+    y = 8u;
+    return;
+  }
+  const int q = min(3, 31 - __clz(len));
+  const int big = len > (2 << q);
+  x = (uint32_t)(s * mult) | ((uint32_t)((e - (1 << q)) * mult) << 16);
+  y = (uint32_t)q | ((uint32_t)big << 2) | ((uint32_t)len << 8);
+}
 
 inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w, int sets) {
   size_t b = 0;
   b += align_up((size_t)sets * num_rois * pooled_h * 4, 256);
   b += align_up((size_t)sets * num_rois * pooled_w * 4, 256);
   b += align_up((size_t)num_rois * 4, 256);
-  b += align_up((size_t)batch * 4 * 2, 256);
+  b += align_up((size_t)batch * 4 * 2 + 16, 256);
+  b += align_up((size_t)num_rois * pooled_h * 16, 256);
+  b += align_up((size_t)num_rois * pooled_w * 8, 256);
   return b + 256;
 }
 
@@ -67,6 +89,10 @@ inline PoolWorkspace carve_pool_workspace(void* ws, int batch, int num_rois, int
   w.batch_idx = (int*)p; p += align_up((size_t)num_rois * 4, 256);
   w.first = (int*)p;
   w.neg_last = w.first + batch;
+  w.ungrouped = w.neg_last + batch;
+  p += align_up((size_t)batch * 4 * 2 + 16, 256);
+  w.hdesc = (uint4*)p; p += align_up((size_t)num_rois * pooled_h * 16, 256);
+  w.wdesc = (uint2*)p;
   return w;
 }
 

@@ -16,6 +16,7 @@
 //   * threads map to consecutive (roi, bin) outputs, so for a fixed channel a
 //     warp writes contiguous 4*P*P-byte runs of the [R, C, P, P] output.
 #include "roi_bins.cuh"
+#include "roi_pool_rmq.cuh"
 
 namespace jtsm {
 
@@ -24,6 +25,7 @@ namespace jtsm {
 // ---------------------------------------------------------------------------
 __global__ void roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch,
                                      int height, int width, float scale, int PH, int PW,
+                                     const float* __restrict__ row_scale, int want_desc,
                                      PoolWorkspace ws) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= num_rois) return;
@@ -36,6 +38,22 @@ __global__ void roi_pool_prep_kernel(const float* __restrict__ rois, int num_roi
   for (int p = 0; p < PW; ++p) ws.wbins[(size_t)r * PW + p] = bin_range(p, rc.sw, roi_w, PW, width);
   const bool ok = (b >= 0 && b < batch);
   ws.batch_idx[r] = ok ? b : -1;
+  if (r > 0 && (int)rois[(size_t)(r - 1) * 5] > b) *ws.ungrouped = 1;
+  if (want_desc) {  // descriptors of the range-max-table kernel (plane size < 65535 checked by the caller)
+    const float rs = row_scale ? row_scale[r] : 1.f;
+    for (int p = 0; p < PH; ++p) {
+      uint4 d;
+      rmq_axis_desc(ws.hbins[(size_t)r * PH + p], width, d.x, d.y);
+      d.z = __float_as_uint(rs);
+      d.w = (uint32_t)(ok ? b : -1);
+      ws.hdesc[(size_t)r * PH + p] = d;
+    }
+    for (int p = 0; p < PW; ++p) {
+      uint2 d;
+      rmq_axis_desc(ws.wbins[(size_t)r * PW + p], 1, d.x, d.y);
+      ws.wdesc[(size_t)r * PW + p] = d;
+    }
+  }
   if (ok) {
     atomicMin(ws.first + b, r);
     atomicMin(ws.neg_last + b, -r);
@@ -192,6 +210,79 @@ roi_pool_bwd_red_kernel(const T* __restrict__ grad_output, long long sn, long lo
   }
 }
 
+
+// ---------------------------------------------------------------------------
+// backward, contiguous fast path: one CTA row per RoI, 4 consecutive outputs per thread
+// (128-bit gradient load + 64/128-bit argmax load), no integer division (magic multiply),
+// one RED.ADD.F32 per non-empty bin into the L2-resident gradient map.
+// ---------------------------------------------------------------------------
+template <typename A> struct Arg4;
+template <> struct Arg4<unsigned short> {
+  static __device__ __forceinline__ void load(const unsigned short* p, int (&a)[4]) {
+    const uint2 v = *reinterpret_cast<const uint2*>(p);
+    a[0] = Arg<unsigned short>::dec((unsigned short)(v.x & 0xFFFFu));
+    a[1] = Arg<unsigned short>::dec((unsigned short)(v.x >> 16));
+    a[2] = Arg<unsigned short>::dec((unsigned short)(v.y & 0xFFFFu));
+    a[3] = Arg<unsigned short>::dec((unsigned short)(v.y >> 16));
+  }
+};
+template <> struct Arg4<int> {
+  static __device__ __forceinline__ void load(const int* p, int (&a)[4]) {
+    const int4 v = *reinterpret_cast<const int4*>(p);
+    a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w;
+  }
+};
+template <typename T> struct Grad4;
+template <> struct Grad4<float> {
+  static __device__ __forceinline__ void load(const float* p, float (&g)[4]) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    g[0] = v.x; g[1] = v.y; g[2] = v.z; g[3] = v.w;
+  }
+};
+template <> struct Grad4<__nv_bfloat16> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&g)[4]) {
+    const uint2 v = *reinterpret_cast<const uint2*>(p);
+    g[0] = __uint_as_float(v.x << 16); g[1] = __uint_as_float(v.x & 0xFFFF0000u);
+    g[2] = __uint_as_float(v.y << 16); g[3] = __uint_as_float(v.y & 0xFFFF0000u);
+  }
+};
+template <> struct Grad4<__half> {
+  static __device__ __forceinline__ void load(const __half* p, float (&g)[4]) {
+    const uint2 v = *reinterpret_cast<const uint2*>(p);
+    const __half2 lo = *reinterpret_cast<const __half2*>(&v.x), hi = *reinterpret_cast<const __half2*>(&v.y);
+    g[0] = __low2float(lo); g[1] = __high2float(lo); g[2] = __low2float(hi); g[3] = __high2float(hi);
+  }
+};
+
+template <typename T, typename A>
+__global__ void __launch_bounds__(256)
+roi_pool_bwd_vec4_kernel(const T* __restrict__ grad_output, const float* __restrict__ rois,
+                         const A* __restrict__ argmax, int batch, int channels, int hw, int PP,
+                         unsigned magic_pp, const float* __restrict__ row_scale,
+                         float* __restrict__ grad_acc) {
+  const int r = blockIdx.x;
+  const int b = (int)__ldg(rois + (size_t)r * 5);
+  if (b < 0 || b >= batch) return;
+  const float rs = row_scale ? __ldg(row_scale + r) : 1.f;
+  const int cpp = channels * PP;
+  const T* g_r = grad_output + (size_t)r * cpp;
+  const A* a_r = argmax + (size_t)r * cpp;
+  float* acc_b = grad_acc + (size_t)b * channels * hw;
+  for (int i = (blockIdx.y * 256 + threadIdx.x) * 4; i < cpp; i += gridDim.y * 1024) {
+    int a[4];
+    float g[4];
+    Arg4<A>::load(a_r + i, a);
+    Grad4<T>::load(g_r + i, g);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (a[j] >= 0) {
+        const int c = (int)__umulhi((unsigned)(i + j), magic_pp);
+        atomicAdd(acc_b + (size_t)c * hw + a[j], __fmul_rn(g[j], rs));
+      }
+    }
+  }
+}
+
 template <typename T>
 __global__ void convert_from_f32_kernel(const float* __restrict__ src, T* __restrict__ dst, size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
@@ -226,10 +317,36 @@ template <typename T, typename A>
 int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, int width,
                         int num_rois, int PH, int PW, const PoolWorkspace& ws,
                         const float* row_scale, void* output, void* argmax, cudaStream_t st) {
+  const int planes = batch * channels;
+  // 1) range-max-table kernel: plane + 10 index tables in shared memory, persistent CTAs
+  const int hw = height * width;
+  const size_t rmq_smem = rmq_smem_bytes(hw);
+  const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
+  if ((algo == 0 || algo == 3) && hw < 65535 && rmq_smem <= 227 * 1024 && !tuning("roi_pool_force_gmem", 0)) {
+    auto k = roi_pool_fwd_rmq_kernel<T, A>;
+    static bool rmq_attr = false;
+    if (!rmq_attr) {
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      rmq_attr = true;
+    }
+    const int per_sm = (int)((227 * 1024) / (rmq_smem + 1024)) >= 2 ? 2 : 1;  // 1024-thread CTAs
+    const int max_grid = num_sms() * per_sm;
+    int chunks = tuning("roi_pool_splits", 0);
+    if (chunks <= 0) {
+      chunks = (16 * max_grid + planes - 1) / planes;
+      const int cap = num_rois / 64 > 1 ? num_rois / 64 : 1;
+      chunks = chunks > cap ? cap : (chunks < 1 ? 1 : chunks);
+    }
+    const int items = planes * chunks;
+    const int grid = items < max_grid ? items : max_grid;
+    k<<<grid, kRmqThreads, rmq_smem, st>>>((const T*)input, channels, height, width, PH, PW, chunks, items,
+                                            ws, (T*)output, (A*)argmax);
+    count_launch();
+    return cuda_status();
+  }
   const int pitch = (width & 1) ? width : width + 1;
   const size_t smem = (size_t)height * pitch * sizeof(float);
-  const int planes = batch * channels;
-  if (smem <= kMaxPlaneSmem && !tuning("roi_pool_force_gmem", 0)) {
+  if (smem <= kMaxPlaneSmem && algo != 2 && !tuning("roi_pool_force_gmem", 0)) {
     auto k = roi_pool_fwd_kernel<T, A, kFwdThreads>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -252,10 +369,12 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
 }
 
 int run_prep(const float* rois, int num_rois, int batch, int height, int width, float scale, int PH,
-             int PW, const PoolWorkspace& ws, cudaStream_t st) {
+             int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st) {
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
+  cudaMemsetAsync(ws.ungrouped, 0, sizeof(int), st);
+  const int want_desc = (long long)height * width < 65535;
   roi_pool_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width,
-                                                              scale, PH, PW, ws);
+                                                              scale, PH, PW, row_scale, want_desc, ws);
   count_launch();
   return cuda_status();
 }
@@ -285,7 +404,7 @@ extern "C" int jtsm_roi_pool_forward(const void* input, const float* rois, int d
     return JTSM_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 1);
-  int rc = run_prep(rois, num_rois, batch, height, width, spatial_scale, pooled_h, pooled_w, ws, st);
+  int rc = run_prep(rois, num_rois, batch, height, width, spatial_scale, pooled_h, pooled_w, row_scale, ws, st);
   if (rc != JTSM_OK) return rc;
   JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
                         rc = launch_roi_pool_fwd<T, A>(input, batch, channels, height, width,
@@ -328,15 +447,34 @@ extern "C" int jtsm_roi_pool_backward(const void* grad_output, long long stride_
   int rc = JTSM_OK;
   if (total > 0) {
     if (!grad_output || !rois || !argmax) return JTSM_ERR_INVALID_ARGUMENT;
-    long long blocks = (total + 255) / 256;
-    const long long cap = (long long)kNumSMs * 8 * 4;
-    if (blocks > cap) blocks = cap;
-    JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
-                          roi_pool_bwd_red_kernel<T, A><<<(int)blocks, 256, 0, st>>>(
-                              (const T*)grad_output, stride_n, stride_c, stride_h, stride_w, rois,
-                              (const A*)argmax, batch, channels, height * width, num_rois, pooled_h,
-                              pooled_w, row_scale, acc);
-                        }));
+    const int PP = pooled_h * pooled_w;
+    const long long cpp = (long long)channels * PP;
+    const bool contiguous = stride_w == 1 && stride_h == pooled_w && stride_c == PP && stride_n == cpp;
+    const bool vec_ok = contiguous && cpp % 4 == 0 && cpp < (1ll << 31) / 49 &&
+                        ((uintptr_t)grad_output % 16 == 0) && ((uintptr_t)argmax % 16 == 0) &&
+                        tuning("roi_pool_bwd_algo", 0) != 1;
+    if (vec_ok) {
+      const unsigned magic_pp = (unsigned)((0x100000000ull + PP - 1) / PP);
+      int ysplit = (int)((cpp + 1023) / 1024);
+      const int want = (4 * num_sms() * 8 + num_rois - 1) / num_rois;  // enough CTAs when R is small
+      if (ysplit > want) ysplit = want < 1 ? 1 : want;
+      dim3 grid(num_rois, ysplit);
+      JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
+                            roi_pool_bwd_vec4_kernel<T, A><<<grid, 256, 0, st>>>(
+                                (const T*)grad_output, rois, (const A*)argmax, batch, channels,
+                                height * width, PP, magic_pp, row_scale, acc);
+                          }));
+    } else {
+      long long blocks = (total + 255) / 256;
+      const long long cap = (long long)kNumSMs * 8 * 4;
+      if (blocks > cap) blocks = cap;
+      JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
+                            roi_pool_bwd_red_kernel<T, A><<<(int)blocks, 256, 0, st>>>(
+                                (const T*)grad_output, stride_n, stride_c, stride_h, stride_w, rois,
+                                (const A*)argmax, batch, channels, height * width, num_rois, pooled_h,
+                                pooled_w, row_scale, acc);
+                          }));
+    }
     count_launch();
     rc = cuda_status();
     if (rc != JTSM_OK) return rc;

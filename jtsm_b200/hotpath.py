@@ -8,7 +8,7 @@ Used by bench.py and by the parity tests; stages are enabled as their kernels ex
 """
 import torch
 
-from . import ops, synth
+from . import heads, ops, synth
 
 
 class HotPathStep:
@@ -26,7 +26,20 @@ class HotPathStep:
             feat=wl["feat"].to(self.dtype).contiguous().pin_memory(),
             rois=wl["rois"].contiguous().pin_memory(),
             objectness=wl["objectness"].contiguous().pin_memory(),
+            mil_cls=wl["mil_cls"].contiguous().pin_memory(),
+            mil_det=wl["mil_det"].contiguous().pin_memory(),
         )
+        for k, t in enumerate(wl["ref_logits"]):
+            host["ref_logits%d" % k] = t.contiguous().pin_memory()
+        for k, t in enumerate(wl["ref_deltas"]):
+            host["ref_deltas%d" % k] = t.contiguous().pin_memory()
+        cfg = self.cfg
+        self.counts = [int(b.shape[0]) for b in wl["boxes"]]
+        self.labels = wl["labels"]
+        oh = torch.zeros(len(self.counts), cfg["K"])
+        for i, l in enumerate(self.labels):
+            oh[i, l] = 1.0
+        host["labels_onehot"] = oh.pin_memory()
         # gradient handed over by fc6's backward lives on the device in the real system
         host["_grad_pooled"] = synth.expand_grad_tile(wl["grad_tile"].to(self.dev), wl["rois"].shape[0]).to(self.dtype)
         return host
@@ -34,6 +47,9 @@ class HotPathStep:
     def upload(self, host):
         res = {k: (v.to(self.dev, non_blocking=True) if not k.startswith("_") else v) for k, v in host.items()}
         res["row_scale"] = res["objectness"] + 1.0
+        res["proposals"] = res["rois"][:, 1:].contiguous()
+        res["ref_logits"] = [res["ref_logits%d" % k] for k in range(self.cfg["Kr"])]
+        res["ref_deltas"] = [res["ref_deltas%d" % k] for k in range(self.cfg["Kr"])] if self.cfg["reg"] else []
         return res
 
     def h2d_bytes(self, host):
@@ -43,7 +59,11 @@ class HotPathStep:
         return self._d2h
 
     def stages(self):
-        return ["roi_pool_fwd(x objectness)", "roi_pool_bwd"]
+        st = ["roi_pool_fwd(x objectness)", "wsddn_fwd+bce", "wsddn_bwd"]
+        st += ["refine_assign", "refine_ce_fwd_bwd_softmax", "apply_deltas"] * self.cfg["Kr"]
+        if self.cfg["reg"]:
+            st += ["refine_box_reg"] * self.cfg["Kr"]
+        return st + ["roi_pool_bwd"]
 
     def dominant_kernel(self):
         return "roi_pool_fwd_kernel"
@@ -61,13 +81,19 @@ class HotPathStep:
         pooled, argmax = ops.roi_pool_forward(x, rois, self.scale, self.P, row_scale=d["row_scale"], argmax_dtype=adt)
         if time_dominant:
             e1.record()
+        cfg = self.cfg
+        h = heads.head_step(d["mil_cls"], d["mil_det"], d["ref_logits"], d["ref_deltas"], d["proposals"], self.counts,
+                            self.labels, cfg["K"], d["labels_onehot"], reg=cfg["reg"])
         grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=d["row_scale"])
-        self.last = dict(pooled=pooled, grad_feat=grad_feat)
+        self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
         return (e0, e1) if time_dominant else None
 
     def run_from_host(self, host):
         d = self.upload(host)
         self.run(d)
-        out = self.last["grad_feat"].to("cpu")
-        self._d2h = out.numel() * out.element_size()
+        h = self.last["heads"]
+        res = [self.last["grad_feat"], torch.cat([v.reshape(1) for v in h["losses"].values()])]
+        res += [b["gt_classes"] for b in h["branches"]]
+        out = [t.to("cpu") for t in res]  # blocking D2H: gradient to the backbone, losses, pseudo-labels
+        self._d2h = sum(t.numel() * t.element_size() for t in out)
         return out

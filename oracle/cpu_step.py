@@ -14,7 +14,7 @@ import torch
 
 from jtsm_b200 import synth
 
-from . import capi
+from . import capi, ref_heads
 
 
 def auto_sample_rois(wl, kind, budget_s=15.0):
@@ -39,7 +39,12 @@ def time_step(wl, sample_rois, threads, kind):
     P = (cfg["P"], cfg["P"])
     g = synth.expand_grad_tile(wl["grad_tile"], r)
     scale = (wl["objectness"][:r] + 1.0)
-    desc = "first %d of %d proposals of image 0 of %s (pool fwd+bwd), %d threads" % (r, cfg["R"], wl["name"], threads)
+    desc = "first %d of %d proposals of image 0 of %s (pool fwd+bwd, MIL, %d refine branches, all gradients), %d threads" % (
+        r, cfg["R"], wl["name"], cfg["Kr"], threads)
+    torch.set_num_threads(threads)
+    head_in = dict(mil_cls=wl["mil_cls"][:r], mil_det=wl["mil_det"][:r], ref_logits=[x[:r] for x in wl["ref_logits"]],
+                   ref_deltas=[x[:r] for x in wl["ref_deltas"]], proposal_boxes=[rois[:, 1:].contiguous()],
+                   labels=wl["labels"][:1], num_classes=cfg["K"], reg=cfg["reg"])
     if kind == "reference":
         import torchvision
 
@@ -48,8 +53,9 @@ def time_step(wl, sample_rois, threads, kind):
         xg = x.clone().requires_grad_()
         out = torchvision.ops.roi_pool(xg, rois, P, cfg["scale"]) * scale.view(-1, 1, 1, 1)
         out.backward(g)
+        ref_heads.head_step(**head_in)
         t = time.perf_counter() - t0
-        return t, r, desc + ", torchvision CPU roi_pool"
+        return t, r, desc + ", torchvision CPU roi_pool + eager PyTorch heads (the reference's MODEL.DEVICE=cpu path)"
     xn, rn, gn = x.numpy(), rois.numpy(), (g * scale.view(-1, 1, 1, 1)).numpy()
     capi.lib()
     chunks = [(i * r // threads, (i + 1) * r // threads) for i in range(threads)]
@@ -62,5 +68,6 @@ def time_step(wl, sample_rois, threads, kind):
     with ThreadPoolExecutor(threads) as ex:
         parts = list(ex.map(work, chunks))
     gi = np.sum(parts, axis=0)
+    ref_heads.head_step(**head_in)
     t = time.perf_counter() - t0
-    return t, r, desc + ", oracle C port"
+    return t, r, desc + ", oracle C port (pool) + eager restatement (heads)"
