@@ -45,6 +45,7 @@ def parse():
     ap.add_argument("--config", default="c2")
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-sample-rois", type=int, default=0, help="0 = auto (about 10-30 s)")
     return ap.parse_args()
 
@@ -121,7 +122,6 @@ def make_workload(name, rank, dtype):
     w = synth.step_case(name, sweep_index=rank)
     if dtype == "bf16":
         w["feat"] = w["feat"].bfloat16()
-        w["grad_pooled_seed"] = w["grad_pooled_seed"]
     return w
 
 
@@ -169,42 +169,55 @@ def run_b200(a):
             torch.cuda.synchronize()
 
     # ---------------- device-resident timing (value) ----------------
-    for _ in range(max(a.warmup, 3)):
-        step.run(resident)
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    use_graph = not a.no_graph
+    if use_graph:
+        step.capture(resident)
+        run_step = step.replay
+    else:
+        run_step = lambda: step.run(resident)
+    for _ in range(max(a.warmup, 3)):
+        run_step()
+    barrier()
     lc0 = _lib.launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
-    kev = []
     barrier()
     t_wall0 = time.perf_counter()
     for i in range(a.steps):
         flush.zero_()
         ev[i][0].record()
-        kev.append(step.run(resident, time_dominant=True))
+        run_step()
         ev[i][1].record()
     barrier()
     t_wall = time.perf_counter() - t_wall0
-    launches = _lib.launch_count() - lc0
-    clocks = sampler.stop() if rank == 0 else None
+    launches = step.launches_per_step * a.steps if use_graph else _lib.launch_count() - lc0
     dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
+    # dominant kernel: CUDA events around its launch, same inputs, L2 flushed, eager (events cannot be
+    # recorded inside a captured graph)
+    kev = []
+    for i in range(a.steps):
+        flush.zero_()
+        kev.append(step.run(resident, time_dominant=True))
+    barrier()
     dom_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / len(kev)
 
     # ---------------- end-to-end from host buffers (e2e) ----------------
+    from_host = step.replay_from_host if use_graph else step.run_from_host
     for _ in range(3):
-        step.run_from_host(host)
+        from_host(host)
     barrier()
     ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     for i in range(a.steps):
         flush.zero_()
         ev2[i][0].record()
-        step.run_from_host(host)  # ends with a blocking D2H of the results
+        from_host(host)  # ends with a blocking D2H of the results
         ev2[i][1].record()
     barrier()
     e2e_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev2)
 
+    clocks = sampler.stop() if rank == 0 else None
     tm = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
@@ -222,7 +235,8 @@ def run_b200(a):
             "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
                        "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
                        "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool",
-                       "l2": "flushed (256 MiB write) between timed steps", "stages": step.stages()},
+                       "l2": "flushed (256 MiB write) between timed steps", "stages": step.stages(),
+                       "launch": "cuda_graph_replay" if use_graph else "eager"},
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes()},
             "gpu_launches": int(launches),

@@ -11,7 +11,11 @@
 // shuffles; column reductions are per-lane online (max, sum-exp) accumulators combined across
 // the 32 warps through shared memory in a fixed order -> bit-reproducible run to run.
 // The whole head is 2 launches (fwd+loss, bwd) instead of ~25.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace jtsm {
 
@@ -66,6 +70,61 @@ __device__ __forceinline__ float bce_elem(float y, float t) {
 __device__ __forceinline__ float bce_grad(float y, float t) {
   return (y - t) / fmaxf((1.f - y) * y, 1e-12f);
 }
+// ---------------------------------------------------------------------------------------------
+// A thread-block cluster of kMilCluster CTAs owns one image (a single CTA was issue bound:
+// 94 us at R=2000, K=20 -- profiles/r1c).  CTA j takes rows r0 + j*32 + warp, stride 32*cluster.
+// Column partials are combined warp -> CTA in shared memory, then CTA -> cluster through
+// distributed shared memory, always in a fixed order (bit-reproducible run to run).
+// Dynamic shared memory layout (floats): part[kMilWarps][K][2] | xchg[K][2] | fin[K][2]
+// ---------------------------------------------------------------------------------------------
+constexpr int kMilCluster = 8;
+
+// Combine this CTA's per-warp (max, sumexp) partials and then the cluster's; result in fin[k][0..1].
+__device__ __forceinline__ void cluster_combine_lse(cg::cluster_group& cluster, float* part, float* xchg, float* fin,
+                                                    int K) {
+  __syncthreads();
+  for (int k = threadIdx.x; k < K; k += kMilThreads) {
+    OnlineLse a = {-INFINITY, 0.f};
+    for (int w = 0; w < kMilWarps; ++w) {
+      OnlineLse b = {part[(w * K + k) * 2 + 0], part[(w * K + k) * 2 + 1]};
+      lse_merge(a, b);
+    }
+    xchg[k * 2 + 0] = a.m;
+    xchg[k * 2 + 1] = a.s;
+  }
+  cluster.sync();
+  const unsigned nr = cluster.num_blocks();
+  for (int k = threadIdx.x; k < K; k += kMilThreads) {
+    OnlineLse a = {-INFINITY, 0.f};
+    for (unsigned j = 0; j < nr; ++j) {
+      const float* rx = cluster.map_shared_rank(xchg, j);
+      OnlineLse b = {rx[k * 2 + 0], rx[k * 2 + 1]};
+      lse_merge(a, b);
+    }
+    fin[k * 2 + 0] = a.m;
+    fin[k * 2 + 1] = a.s;
+  }
+  cluster.sync();  // everyone has read xchg before it is reused; fin visible CTA-wide
+}
+
+// Same for plain sums: part[kMilWarps][K] -> fin[k]
+__device__ __forceinline__ void cluster_combine_sum(cg::cluster_group& cluster, float* part, float* xchg, float* fin,
+                                                    int K) {
+  __syncthreads();
+  for (int k = threadIdx.x; k < K; k += kMilThreads) {
+    float t = 0.f;
+    for (int w = 0; w < kMilWarps; ++w) t += part[w * K + k];
+    xchg[k] = t;
+  }
+  cluster.sync();
+  const unsigned nr = cluster.num_blocks();
+  for (int k = threadIdx.x; k < K; k += kMilThreads) {
+    float t = 0.f;
+    for (unsigned j = 0; j < nr; ++j) t += cluster.map_shared_rank(xchg, j)[k];
+    fin[k] = t;
+  }
+  cluster.sync();
+}
 
 template <int KT>
 __global__ void __launch_bounds__(kMilThreads)
@@ -75,16 +134,23 @@ wsddn_fwd_kernel(const float* __restrict__ C, const float* __restrict__ D,
                  float* __restrict__ img_scores, float* __restrict__ col_stats,
                  float* __restrict__ loss, float* __restrict__ grad_img,
                  float* __restrict__ img_loss_partial, unsigned int* __restrict__ ticket) {
-  extern __shared__ float sm[];  // [kMilWarps][K][2]
-  const int n = blockIdx.x;
+  extern __shared__ float sm[];
+  cg::cluster_group cluster = cg::this_cluster();
+  float* part = sm;
+  float* xchg = sm + kMilWarps * K * 2;
+  float* fin = xchg + K * 2;
+  const int n = blockIdx.x / cluster.num_blocks();
+  const int rank = cluster.block_rank();
+  const int row_stride = kMilWarps * cluster.num_blocks();
   const int r0 = seg[n], r1 = seg[n + 1];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rbeg = r0 + rank * kMilWarps + warp;
 
   // ---- pass A: column (max, sum-exp) of D over the image's rows
   OnlineLse col[KT];
 #pragma unroll
   for (int t = 0; t < KT; ++t) col[t] = {-INFINITY, 0.f};
-  for (int r = r0 + warp; r < r1; r += kMilWarps) {
+  for (int r = rbeg; r < r1; r += row_stride) {
 #pragma unroll
     for (int t = 0; t < KT; ++t) {
       const int k = lane + 32 * t;
@@ -95,37 +161,29 @@ wsddn_fwd_kernel(const float* __restrict__ C, const float* __restrict__ D,
   for (int t = 0; t < KT; ++t) {
     const int k = lane + 32 * t;
     if (k < K) {
-      sm[(warp * K + k) * 2 + 0] = col[t].m;
-      sm[(warp * K + k) * 2 + 1] = col[t].s;
+      part[(warp * K + k) * 2 + 0] = col[t].m;
+      part[(warp * K + k) * 2 + 1] = col[t].s;
     }
   }
-  __syncthreads();
-  // every warp combines the 32 partials of its lanes' columns in the same fixed order
+  cluster_combine_lse(cluster, part, xchg, fin, K);
   float cmax[KT], cinv[KT];
 #pragma unroll
   for (int t = 0; t < KT; ++t) {
     const int k = lane + 32 * t;
-    OnlineLse a = {-INFINITY, 0.f};
-    if (k < K) {
-      for (int w = 0; w < kMilWarps; ++w) {
-        OnlineLse b = {sm[(w * K + k) * 2 + 0], sm[(w * K + k) * 2 + 1]};
-        lse_merge(a, b);
-      }
-    }
-    cmax[t] = a.m;
-    cinv[t] = a.s > 0.f ? 1.f / a.s : 0.f;
-    if (k < K && warp == 0) {
-      col_stats[((size_t)n * K + k) * 3 + 0] = a.m;
-      col_stats[((size_t)n * K + k) * 3 + 1] = a.s;
+    cmax[t] = k < K ? fin[k * 2 + 0] : 0.f;
+    const float cs = k < K ? fin[k * 2 + 1] : 0.f;
+    cinv[t] = cs > 0.f ? 1.f / cs : 0.f;
+    if (k < K && warp == 0 && rank == 0) {
+      col_stats[((size_t)n * K + k) * 3 + 0] = cmax[t];
+      col_stats[((size_t)n * K + k) * 3 + 1] = cs;
     }
   }
-  __syncthreads();
 
   // ---- pass B: scores = softmax_row(C) * softmax_col(D); column sums
   float ysum[KT];
 #pragma unroll
   for (int t = 0; t < KT; ++t) ysum[t] = 0.f;
-  for (int r = r0 + warp; r < r1; r += kMilWarps) {
+  for (int r = rbeg; r < r1; r += row_stride) {
     float c[KT], d[KT];
 #pragma unroll
     for (int t = 0; t < KT; ++t) {
@@ -147,20 +205,21 @@ wsddn_fwd_kernel(const float* __restrict__ C, const float* __restrict__ D,
       }
     }
   }
+  __syncthreads();  // fin (pass A) fully consumed before part is overwritten? part != fin; keeps phases tidy
 #pragma unroll
   for (int t = 0; t < KT; ++t) {
     const int k = lane + 32 * t;
-    if (k < K) sm[warp * K + k] = ysum[t];
+    if (k < K) part[warp * K + k] = ysum[t];
   }
-  __syncthreads();
+  cluster_combine_sum(cluster, part, xchg, fin, K);
+  if (rank != 0) return;
   float bce_part = 0.f;
   if (warp == 0) {
 #pragma unroll
     for (int t = 0; t < KT; ++t) {
       const int k = lane + 32 * t;
       if (k < K) {
-        float y = 0.f;
-        for (int w = 0; w < kMilWarps; ++w) y += sm[w * K + k];
+        const float y = fin[k];
         col_stats[((size_t)n * K + k) * 3 + 2] = y;
         const float yc = fminf(fmaxf(y, 1e-6f), 1.f - 1e-6f);
         img_scores[(size_t)n * K + k] = yc;
@@ -201,10 +260,17 @@ wsddn_bwd_kernel(const float* __restrict__ C, const float* __restrict__ D,
                  const int* __restrict__ seg, int K, const float* __restrict__ grad_scores,
                  const float* __restrict__ grad_img, const float* __restrict__ grad_loss,
                  float* __restrict__ dC, float* __restrict__ dD) {
-  extern __shared__ float sm[];  // [kMilWarps][K]
-  const int n = blockIdx.x;
+  extern __shared__ float sm[];
+  cg::cluster_group cluster = cg::this_cluster();
+  float* part = sm;
+  float* xchg = sm + kMilWarps * K * 2;
+  float* fin = xchg + K * 2;
+  const int n = blockIdx.x / cluster.num_blocks();
+  const int rank = cluster.block_rank();
+  const int row_stride = kMilWarps * cluster.num_blocks();
   const int r0 = seg[n], r1 = seg[n + 1];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rbeg = r0 + rank * kMilWarps + warp;
   const float gl = grad_loss ? *grad_loss : 1.f;
   float gimg[KT], cmax[KT], cinv[KT], colsg[KT];
 #pragma unroll
@@ -217,34 +283,30 @@ wsddn_bwd_kernel(const float* __restrict__ C, const float* __restrict__ D,
     // sum_r s_rk * gimg_k = gimg_k * ysum_k
     colsg[t] = k < K ? gimg[t] * col_stats[((size_t)n * K + k) * 3 + 2] : 0.f;
   }
-  if (grad_scores) {  // uniform branch: extra column reduction of s * grad_scores
-    float part[KT];
+  if (grad_scores) {  // uniform branch: extra column reduction of s * grad_scores over the cluster
+    float p[KT];
 #pragma unroll
-    for (int t = 0; t < KT; ++t) part[t] = 0.f;
-    for (int r = r0 + warp; r < r1; r += kMilWarps) {
+    for (int t = 0; t < KT; ++t) p[t] = 0.f;
+    for (int r = rbeg; r < r1; r += row_stride) {
 #pragma unroll
       for (int t = 0; t < KT; ++t) {
         const int k = lane + 32 * t;
-        if (k < K) part[t] += scores[(size_t)r * K + k] * grad_scores[(size_t)r * K + k];
+        if (k < K) p[t] += scores[(size_t)r * K + k] * grad_scores[(size_t)r * K + k];
       }
     }
 #pragma unroll
     for (int t = 0; t < KT; ++t) {
       const int k = lane + 32 * t;
-      if (k < K) sm[warp * K + k] = part[t];
+      if (k < K) part[warp * K + k] = p[t];
     }
-    __syncthreads();
+    cluster_combine_sum(cluster, part, xchg, fin, K);
 #pragma unroll
     for (int t = 0; t < KT; ++t) {
       const int k = lane + 32 * t;
-      if (k < K) {
-        float tot = 0.f;
-        for (int w = 0; w < kMilWarps; ++w) tot += sm[w * K + k];
-        colsg[t] += tot;
-      }
+      if (k < K) colsg[t] += fin[k];
     }
   }
-  for (int r = r0 + warp; r < r1; r += kMilWarps) {
+  for (int r = rbeg; r < r1; r += row_stride) {
     float c[KT];
 #pragma unroll
     for (int t = 0; t < KT; ++t) {
@@ -278,6 +340,24 @@ wsddn_bwd_kernel(const float* __restrict__ C, const float* __restrict__ D,
   }
 }
 
+// cluster launch helper
+template <typename Kern, typename... Args>
+inline cudaError_t launch_cluster(Kern k, int num_images, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(num_images * kMilCluster));
+  cfg.blockDim = dim3(kMilThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kMilCluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, k, args...);
+}
+
 }  // namespace jtsm
 
 using namespace jtsm;
@@ -303,13 +383,12 @@ extern "C" int jtsm_wsddn_forward(const float* cls_logits, const float* det_logi
   unsigned int* ticket = (unsigned int*)p;
   float* partial = (float*)(p + 16);
   cudaMemsetAsync(ticket, 0, 4, st);
-  const size_t smem = (size_t)kMilWarps * num_classes * 2 * sizeof(float);
+  const size_t smem = ((size_t)kMilWarps * num_classes * 2 + 4 * num_classes) * sizeof(float);
   JTSM_DISPATCH_KT(num_classes, KT, {
     auto k = wsddn_fwd_kernel<KT>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k<<<num_images, kMilThreads, smem, st>>>(cls_logits, det_logits, seg_offsets, num_images, num_classes,
-                                              labels_onehot, mean_loss, scores, img_scores, col_stats, loss,
-                                              grad_img, partial, ticket);
+    launch_cluster(k, num_images, smem, st, cls_logits, det_logits, seg_offsets, num_images, num_classes,
+                   labels_onehot, mean_loss, scores, img_scores, col_stats, loss, grad_img, partial, ticket);
   });
   count_launch();
   return cuda_status();
@@ -327,11 +406,12 @@ extern "C" int jtsm_wsddn_backward(const float* cls_logits, const float* det_log
   if (!cls_logits || !det_logits || !scores || !col_stats || !seg_offsets || !grad_cls || !grad_det)
     return JTSM_ERR_INVALID_ARGUMENT;
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t smem = (size_t)kMilWarps * num_classes * sizeof(float);
+  const size_t smem = ((size_t)kMilWarps * num_classes * 2 + 4 * num_classes) * sizeof(float);
   JTSM_DISPATCH_KT(num_classes, KT, {
-    wsddn_bwd_kernel<KT><<<num_images, kMilThreads, smem, st>>>(
-        cls_logits, det_logits, scores, col_stats, seg_offsets, num_classes, grad_scores, grad_img,
-        grad_loss, grad_cls, grad_det);
+    auto k = wsddn_bwd_kernel<KT>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    launch_cluster(k, num_images, smem, st, cls_logits, det_logits, scores, col_stats, seg_offsets, num_classes,
+                   grad_scores, grad_img, grad_loss, grad_cls, grad_det);
   });
   count_launch();
   return cuda_status();

@@ -190,18 +190,25 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
   if (threadIdx.x == 3) atomicAdd(counters + num_images * 3, s_cnt[3]);  // integer: order independent
 }
 
-// Deterministic grid-wide float sum: per-CTA partial -> last CTA adds partials in index order.
+// Deterministic grid-wide float sum: per-CTA partial -> the last CTA to arrive adds the partials
+// with warp 0 (lane l takes partials l, l+32, ... in order, then a fixed shuffle tree).
+// Called by every thread of the CTA; `cta_value` is read from thread 0.
 __device__ __forceinline__ void grid_sum_finalize(float cta_value, float* partials, unsigned int* ticket,
                                                   float* out, float divisor, float multiplier) {
-  // call from thread 0 of every CTA
-  partials[blockIdx.x] = cta_value;
-  __threadfence();
-  const unsigned int done = atomicAdd(ticket, 1u);
-  if (done == gridDim.x - 1) {
+  __shared__ int s_last;
+  if (threadIdx.x == 0) {
+    partials[blockIdx.x] = cta_value;
     __threadfence();
-    float tot = 0.f;
-    for (unsigned int i = 0; i < gridDim.x; ++i) tot += ((volatile float*)partials)[i];
-    *out = tot / divisor * multiplier;
+    s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last || threadIdx.x >= 32) return;
+  __threadfence();
+  float t = 0.f;
+  for (unsigned int i = threadIdx.x; i < gridDim.x; i += 32) t += ((volatile float*)partials)[i];
+  t = warp_sum(t);
+  if (threadIdx.x == 0) {
+    *out = t / divisor * multiplier;
     *ticket = 0u;
   }
 }
@@ -296,7 +303,7 @@ refine_ce_kernel(const float* __restrict__ logits, int Kc, const long long* __re
     atomicAdd(&s_acc[3], a_fn);
   }
   const float cta = block_sum_256(part, s_red);
-  if (threadIdx.x == 0) grid_sum_finalize(cta, partials, ticket, loss, valid, loss_scale);
+  grid_sum_finalize(cta, partials, ticket, loss, valid, loss_scale);
   if (acc && threadIdx.x < 4) atomicAdd(acc + threadIdx.x, s_acc[threadIdx.x]);
 }
 
@@ -398,7 +405,7 @@ refine_box_reg_kernel(const float* __restrict__ deltas, int boxes_per_row,
     if (grad_deltas) grad_deltas[e] = grad;
   }
   const float cta = block_sum_256(part, s_red);
-  if (threadIdx.x == 0) grid_sum_finalize(cta, partials, ticket, loss, (float)num_rois, loss_scale);
+  grid_sum_finalize(cta, partials, ticket, loss, (float)num_rois, loss_scale);
 }
 
 // Box2BoxTransform.apply_deltas; box_regression.py:73-109.  One thread per (row, class) box.

@@ -21,6 +21,7 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposals, num_preds_per
     out = dict(losses={"loss_cls": fwd["loss"]}, scores=fwd["scores"], img_scores=fwd["img_scores"], branches=[])
     prev_scores, prev_boxes = fwd["scores"], proposals
     grads_l, grads_d = [], []
+    boxes_noreg = None
     for k, logits in enumerate(ref_logits):
         tw = 1.0 if term_weights is None else float(term_weights[k])
         a = ops.refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int,
@@ -38,8 +39,10 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposals, num_preds_per
             boxes = ops.apply_deltas(ref_deltas[k], proposals, bbox_reg_weights)
         else:
             # zero deltas: predict_boxes still round-trips through (ctr, size) (fast_rcnn_oicr.py:684-709)
-            boxes = ops.apply_deltas(torch.zeros(proposals.shape[0], 4, device=proposals.device), proposals,
-                                     bbox_reg_weights)
+            if boxes_noreg is None:
+                boxes_noreg = ops.apply_deltas(torch.zeros(proposals.shape[0], 4, device=proposals.device),
+                                               proposals, bbox_reg_weights)
+            boxes = boxes_noreg
         a.update(probs=ce["probs"], boxes=boxes, acc=ce["acc"])
         out["branches"].append(a)
         prev_scores, prev_boxes = ce["probs"], boxes

@@ -88,6 +88,51 @@ class HotPathStep:
         self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
         return (e0, e1) if time_dominant else None
 
+    # ------------------------------------------------------------------ CUDA graph of the step
+    def capture(self, d):
+        """Capture one step over the device-resident inputs `d` into a CUDA graph (all launches go
+        through the C ABI on the capturing stream; allocations come from the graph's private pool).
+        Afterwards `replay()` re-runs it; the outputs in `self.last` are the graph's static buffers."""
+        from . import _lib
+
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):  # warm caches (segment tables, function attributes) outside the capture
+                self.run(d)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        before = _lib.launch_count()
+        with torch.cuda.graph(self.graph):
+            self.run(d)
+        self.launches_per_step = _lib.launch_count() - before
+        self.static_inputs = d
+        self.graph_last = self.last  # the graph's static output buffers
+        return self.graph
+
+    def replay(self):
+        self.graph.replay()
+
+    def results(self, last=None):
+        last = last or self.last
+        h = last["heads"]
+        res = [last["grad_feat"], torch.cat([v.reshape(1) for v in h["losses"].values()])]
+        return res + [b["gt_classes"] for b in h["branches"]]
+
+    def replay_from_host(self, host):
+        """H2D of the step's inputs into the graph's static buffers, replay, blocking D2H of the results."""
+        d = self.static_inputs
+        for k, v in host.items():
+            if not k.startswith("_"):
+                d[k].copy_(v, non_blocking=True)
+        d["row_scale"].copy_(d["objectness"] + 1.0)
+        d["proposals"].copy_(d["rois"][:, 1:])
+        self.graph.replay()
+        out = [t.to("cpu") for t in self.results(self.graph_last)]
+        self._d2h = sum(t.numel() * t.element_size() for t in out)
+        return out
+
     def run_from_host(self, host):
         d = self.upload(host)
         self.run(d)

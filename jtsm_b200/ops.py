@@ -225,12 +225,28 @@ def refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_cl
     thr = list(iou_thresholds)
     lab = list(iou_labels)
     assert len(thr) in (1, 2) and len(lab) == len(thr) + 1
-    f = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
-    i64 = lambda *s: torch.zeros(s, dtype=torch.int64, device=dev)
-    out = dict(pgt_boxes=f(ctot, 4), pgt_classes=i64(ctot), pgt_scores=f(ctot), pgt_weights=f(ctot),
-               matched_idx=i64(r), matched_iou=f(r) if want_iou else None, gt_classes=i64(r), gt_weights=f(r),
-               gt_scores=f(r), gt_boxes=f(r, 4), loss_weights=f(r),
-               counters=torch.zeros(n * 3 + 1, dtype=torch.int32, device=dev), pgt_offsets=coff)
+    # one zero-filled arena per dtype instead of 13 small fills
+    fl = torch.zeros(ctot * 6 + r * 8 + (r if want_iou else 0), dtype=torch.float32, device=dev)
+    il = torch.zeros(ctot + 2 * r, dtype=torch.int64, device=dev)
+    fo, io = [0], [0]
+
+    def f(*shape):
+        n_ = 1
+        for v in shape:
+            n_ *= v
+        t = fl[fo[0]:fo[0] + n_].view(*shape)
+        fo[0] += n_
+        return t
+
+    def i64(*shape):
+        t = il[io[0]:io[0] + shape[0]]
+        io[0] += shape[0]
+        return t
+
+    out = dict(pgt_boxes=f(ctot, 4), gt_boxes=f(r, 4), pgt_scores=f(ctot), pgt_weights=f(ctot),
+               matched_iou=f(r) if want_iou else None, gt_weights=f(r), gt_scores=f(r), loss_weights=f(r),
+               pgt_classes=i64(ctot), matched_idx=i64(r), gt_classes=i64(r),
+               counters=torch.empty(n * 3 + 1, dtype=torch.int32, device=dev), pgt_offsets=coff)
     with torch.cuda.device(dev):
         check(lib().jtsm_refine_assign(
             _ptr(S), S.shape[1], _ptr(Bx), bpr, _ptr(P), _ptr(seg), n, r, num_classes, _ptr(coff), _ptr(cids), cmax,
