@@ -98,6 +98,31 @@ JTSM_API int jtsm_roi_pool_backward(
     size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------
+ * RoIAlign (bilinear average pooling, adaptive sampling grid).
+ * Replaces roi_align_forward / roi_align_backward of detectron2._C
+ *   (detectron2/layers/csrc/ROIAlign/ROIAlign.h:54-61,86-97, bound at vision.cpp:96-97, called from
+ *   detectron2/layers/roi_align.py:31-33,44-56) and torchvision.ops.roi_align (roi_align.py:5-15).
+ * Same argument meaning: sampling_ratio <= 0 -> ceil(roi_size / pooled) samples per bin axis;
+ * aligned != 0 -> half-pixel shift and no minimum RoI size.
+ * workspace: jtsm_roi_align_workspace_bytes(dtype, batch, channels, height, width, num_rois, backward).
+ * Backward takes explicit grad_output strides (ROIAlign_cpu.cpp:478-482) and overwrites grad_input.
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_roi_align_workspace_bytes(int dtype, int batch, int channels, int height,
+                                               int width, int num_rois, int backward);
+JTSM_API int jtsm_roi_align_forward(const void* input, const float* rois, int dtype, int batch,
+                                    int channels, int height, int width, int num_rois,
+                                    float spatial_scale, int pooled_h, int pooled_w,
+                                    int sampling_ratio, int aligned, void* output, void* workspace,
+                                    size_t workspace_bytes, void* stream);
+JTSM_API int jtsm_roi_align_backward(const void* grad_output, long long stride_n,
+                                     long long stride_c, long long stride_h, long long stride_w,
+                                     const float* rois, int dtype, int batch, int channels,
+                                     int height, int width, int num_rois, float spatial_scale,
+                                     int pooled_h, int pooled_w, int sampling_ratio, int aligned,
+                                     void* grad_input, void* workspace, size_t workspace_bytes,
+                                     void* stream);
+
+/* ------------------------------------------------------------------------
  * WSDDN two-stream MIL head: per image  scores = softmax(C, dim=1) * softmax(D, dim=0),
  * image scores = clamp(sum_r scores, 1e-6, 1-1e-6), loss = BCE(image scores, one-hot).
  * Replaces the eager composition in

@@ -376,3 +376,48 @@ def batched_nms(boxes, scores, idxs, iou_threshold):
 def nms(boxes, scores, iou_threshold):
     """torchvision.ops.nms signature."""
     return batched_nms(boxes, scores, None, iou_threshold)
+
+
+# --------------------------------------------------------------------------- RoIAlign
+def roi_align_forward(input, rois, spatial_scale, pooled_height, pooled_width, sampling_ratio, aligned):
+    """Same signature as detectron2._C.roi_align_forward (ROIAlign.h:54-61)."""
+    _require_cuda(input, rois)
+    assert rois.dim() == 2 and rois.size(1) == 5
+    n, c, h, w = input.shape
+    r = rois.size(0)
+    input = input.contiguous()
+    rois = _rois_f32(rois)
+    output = torch.empty((r, c, int(pooled_height), int(pooled_width)), dtype=input.dtype, device=input.device)
+    if r == 0 or c == 0:
+        return output
+    L = lib()
+    dt = _dtype_code(input)
+    wsb = L.jtsm_roi_align_workspace_bytes(dt, n, c, h, w, r, 0)
+    ws = _workspace(wsb, input.device)
+    with torch.cuda.device(input.device):
+        check(L.jtsm_roi_align_forward(_ptr(input), _ptr(rois), dt, n, c, h, w, r, float(spatial_scale),
+                                       int(pooled_height), int(pooled_width), int(sampling_ratio), int(bool(aligned)),
+                                       _ptr(output), _ptr(ws), wsb, _stream()), "roi_align_forward")
+    return output
+
+
+def roi_align_backward(grad, rois, spatial_scale, pooled_height, pooled_width, batch_size, channels, height, width,
+                       sampling_ratio, aligned):
+    """Same signature as detectron2._C.roi_align_backward (ROIAlign.h:86-97)."""
+    _require_cuda(grad, rois)
+    n, c, h, w = int(batch_size), int(channels), int(height), int(width)
+    r = rois.size(0)
+    rois = _rois_f32(rois)
+    grad_input = torch.empty((n, c, h, w), dtype=grad.dtype, device=grad.device)
+    if grad_input.numel() == 0:
+        return grad_input
+    L = lib()
+    dt = _dtype_code(grad)
+    wsb = L.jtsm_roi_align_workspace_bytes(dt, n, c, h, w, r, 1)
+    ws = _workspace(wsb, grad.device)
+    sn, sc, sh, sw = grad.stride() if grad.numel() else (0, 0, 0, 0)
+    with torch.cuda.device(grad.device):
+        check(L.jtsm_roi_align_backward(_ptr(grad), sn, sc, sh, sw, _ptr(rois), dt, n, c, h, w, r, float(spatial_scale),
+                                        int(pooled_height), int(pooled_width), int(sampling_ratio), int(bool(aligned)),
+                                        _ptr(grad_input), _ptr(ws), wsb, _stream()), "roi_align_backward")
+    return grad_input
