@@ -123,6 +123,39 @@ JTSM_API int jtsm_roi_align_backward(const void* grad_output, long long stride_n
                                      void* stream);
 
 /* ------------------------------------------------------------------------
+ * ROILoopPool: three RoIPool-style max-pools per RoI -- the RoI, the "frame" (RoI minus the inner
+ * rectangle shrunk by context_ratio) and the "context" (outer rectangle grown by context_ratio,
+ * minus the RoI).  Replaces wsl._C.roi_loop_pool_forward (projects/WSL/wsl/layers/csrc/
+ * ROILoopPool/ROILoopPool.h:48-53, ROILoopPool_cuda.cu:10-204; context_ratio = 1.8 at :309).
+ * output / argmax (int32, -1 = none) are [3 * num_rois, channels, pooled_h, pooled_w]: rows [0,R) RoI,
+ * [R,2R) frame, [2R,3R) context.  maxval starts at 0 as in the reference (input assumed >= 0).
+ * Backward (ROILoopPool.h:67-77, _cuda.cu:207-248) = jtsm_roi_pool_backward over 3R rows with
+ * rois repeated three times.
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_roi_loop_pool_workspace_bytes(int batch, int num_rois, int pooled_h,
+                                                   int pooled_w);
+JTSM_API int jtsm_roi_loop_pool_forward(const void* input, const float* rois, int dtype, int batch,
+                                        int channels, int height, int width, int num_rois,
+                                        float spatial_scale, float context_ratio, int pooled_h,
+                                        int pooled_w, void* output, int* argmax, void* workspace,
+                                        size_t workspace_bytes, void* stream);
+/* ------------------------------------------------------------------------
+ * MOIPool: RoI max-pool restricted to cells covered by a superpixel that is switched on for the RoI.
+ * Replaces wsl._C.moi_pool_forward (projects/WSL/wsl/layers/csrc/MOIPool/MOIPool.h:52-59,
+ * MOIPool_cuda.cu:139-215 mask, :218-294 pool).  oh_labels int32 [num_rois, len_labels],
+ * superpixels int32 [batch, height_sp, width_sp].  Returns output AND argmax (int32; consumed by
+ * roi_heads_jtsm.py:615-630).  Backward (MOIPool.h:85-95) = jtsm_roi_pool_backward.
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width, int num_rois,
+                                              int pooled_h, int pooled_w);
+JTSM_API int jtsm_moi_pool_forward(const void* input, const float* rois, const int* oh_labels,
+                                   int len_labels, const int* superpixels, int height_sp,
+                                   int width_sp, int dtype, int batch, int channels, int height,
+                                   int width, int num_rois, float spatial_scale, int pooled_h,
+                                   int pooled_w, void* output, int* argmax, void* workspace,
+                                   size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
  * WSDDN two-stream MIL head: per image  scores = softmax(C, dim=1) * softmax(D, dim=0),
  * image scores = clamp(sum_r scores, 1e-6, 1-1e-6), loss = BCE(image scores, one-hot).
  * Replaces the eager composition in

@@ -1,0 +1,379 @@
+// The WSL project's own pooling ops for sm_100a: ROILoopPool (RoI / frame / context triple max-pool)
+// and MOIPool (superpixel-masked RoI max-pool).
+//
+// Reference (CUDA only; the CPU entry points raise, ROILoopPool.h:62, MOIPool.h:74):
+//   projects/WSL/wsl/layers/csrc/ROILoopPool/ROILoopPool_cuda.cu:10-204 (forward), :207-248 (backward),
+//     host wrappers :252-386 (context_ratio = 1.8 at :309);  Python: wsl/layers/roi_loop_pool.py:9-58
+//   projects/WSL/wsl/layers/csrc/MOIPool/MOIPool_cuda.cu:139-215 (MoIForward mask), :218-294
+//     (MoIPoolForward2), :297-338 (backward);  Python: wsl/layers/moi_pool.py:10-88
+//
+// Design: channel-independent geometry (integer rectangles, bin edges, the superpixel mask) is
+// computed once per call; the max-pool itself runs one CTA per (image, channel) plane with the plane
+// staged in shared memory (read from HBM once), threads over (RoI, bin).  Backward of both ops is the
+// shared max-pool backward (jtsm_roi_pool_backward) over the saved argmax.
+#include "roi_bins.cuh"
+
+namespace jtsm {
+
+struct LoopRects {  // integer rectangles of one RoI (ROILoopPool_cuda.cu:35-104,146-170)
+  int in0[4];       // inner rect (sw, sh, ew, eh) excluded from the frame pool
+  int in1[4];       // RoI rect excluded from the context pool
+};
+
+__device__ __forceinline__ float clampf_(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+
+// prep: bin tables for set 0 (RoI rect) and set 1 (outer rect) + exclusion rectangles
+__global__ void loop_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, int H, int W,
+                                      float scale, float ratio, int PH, int PW, PoolWorkspace ws,
+                                      LoopRects* __restrict__ rects) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= num_rois) return;
+  const float* q = rois + (size_t)r * 5;
+  const int b = (int)q[0];
+  const float x1 = q[1], y1 = q[2], x2 = q[3], y2 = q[4];
+  const float rw = __fsub_rn(x2, x1), rh = __fsub_rn(y2, y1);
+  const float iw = __fdiv_rn(rw, ratio), ih = __fdiv_rn(rh, ratio);
+  const float ow = __fmul_rn(rw, ratio), oh = __fmul_rn(rh, ratio);
+  const float irw = __fsub_rn(rw, iw), irh = __fsub_rn(rh, ih);
+  const float orw = __fsub_rn(ow, rw), orh = __fsub_rn(oh, rh);
+  const float lim_w = (float)(1.0 * W / (double)scale), lim_h = (float)(1.0 * H / (double)scale);
+  const float x1i = clampf_(__fadd_rn(x1, __fdiv_rn(irw, 2.f)), 0.f, lim_w);
+  const float y1i = clampf_(__fadd_rn(y1, __fdiv_rn(irh, 2.f)), 0.f, lim_h);
+  const float x2i = clampf_(__fsub_rn(x2, __fdiv_rn(irw, 2.f)), 0.f, lim_w);
+  const float y2i = clampf_(__fsub_rn(y2, __fdiv_rn(irh, 2.f)), 0.f, lim_h);
+  const float x1o = clampf_(__fsub_rn(x1, __fdiv_rn(orw, 2.f)), 0.f, lim_w);
+  const float y1o = clampf_(__fsub_rn(y1, __fdiv_rn(orh, 2.f)), 0.f, lim_h);
+  const float x2o = clampf_(__fadd_rn(x2, __fdiv_rn(orw, 2.f)), 0.f, lim_w);
+  const float y2o = clampf_(__fadd_rn(y2, __fdiv_rn(orh, 2.f)), 0.f, lim_h);
+  const RoiRect roi = roi_rect(x1, y1, x2, y2, scale);
+  const RoiRect inner = roi_rect(x1i, y1i, x2i, y2i, scale);
+  const RoiRect outer = roi_rect(x1o, y1o, x2o, y2o, scale);
+  LoopRects lr;
+  lr.in0[0] = inner.sw; lr.in0[1] = inner.sh; lr.in0[2] = inner.ew; lr.in0[3] = inner.eh;
+  lr.in1[0] = roi.sw; lr.in1[1] = roi.sh; lr.in1[2] = roi.ew; lr.in1[3] = roi.eh;
+  rects[r] = lr;
+  const size_t set_h = (size_t)num_rois * PH, set_w = (size_t)num_rois * PW;
+  {
+    const int w_ = max(roi.ew - roi.sw + 1, 1), h_ = max(roi.eh - roi.sh + 1, 1);
+    for (int p = 0; p < PH; ++p) ws.hbins[(size_t)r * PH + p] = bin_range(p, roi.sh, h_, PH, H);
+    for (int p = 0; p < PW; ++p) ws.wbins[(size_t)r * PW + p] = bin_range(p, roi.sw, w_, PW, W);
+  }
+  {
+    const int w_ = max(outer.ew - outer.sw + 1, 1), h_ = max(outer.eh - outer.sh + 1, 1);
+    for (int p = 0; p < PH; ++p) ws.hbins[set_h + (size_t)r * PH + p] = bin_range(p, outer.sh, h_, PH, H);
+    for (int p = 0; p < PW; ++p) ws.wbins[set_w + (size_t)r * PW + p] = bin_range(p, outer.sw, w_, PW, W);
+  }
+  const bool ok = b >= 0 && b < batch;
+  ws.batch_idx[r] = ok ? b : -1;
+  if (ok) {
+    atomicMin(ws.first + b, r);
+    atomicMin(ws.neg_last + b, -r);
+  }
+}
+
+constexpr int kWslThreads = 256;
+
+// value fetch from the staged plane or straight from global memory
+template <typename T, bool kSmem>
+__device__ __forceinline__ float plane_at(const float* plane_s, const T* src, int idx) {
+  return kSmem ? plane_s[idx] : Elem<T>::to_f(__ldg(src + idx));
+}
+
+template <typename T, bool kSmem>
+__global__ void __launch_bounds__(kWslThreads)
+loop_pool_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW, int splits,
+                     int num_rois, PoolWorkspace ws, const LoopRects* __restrict__ rects,
+                     T* __restrict__ output, int* __restrict__ argmax) {
+  extern __shared__ float plane_s[];
+  const int item = blockIdx.x;
+  const int s = item % splits;
+  const int nc = item / splits;
+  const int n = nc / channels;
+  const int c = nc - n * channels;
+  const int first = ws.first[n];
+  const int last = -ws.neg_last[n];
+  if (first > last) return;
+  const int len = last - first + 1;
+  const int r0 = first + (int)(((long long)len * s) / splits);
+  const int r1 = first + (int)(((long long)len * (s + 1)) / splits);
+  if (r0 >= r1) return;
+  const int hw = H * W;
+  const T* src = input + (size_t)nc * hw;
+  if (kSmem) {
+    for (int p = threadIdx.x; p < hw; p += kWslThreads) plane_s[p] = Elem<T>::to_f(src[p]);
+    __syncthreads();
+  }
+  const int PP = PH * PW;
+  const size_t set = (size_t)num_rois * channels * PP;
+  const size_t set_h = (size_t)num_rois * PH, set_w = (size_t)num_rois * PW;
+  const int total = (r1 - r0) * PP;
+  for (int i = threadIdx.x; i < total; i += kWslThreads) {
+    const int rl = i / PP;
+    const int bin = i - rl * PP;
+    const int ph = bin / PW, pw = bin - ph * PW;
+    const int r = r0 + rl;
+    if (ws.batch_idx[r] != n) continue;
+    const LoopRects lr = rects[r];
+    const size_t o = ((size_t)r * channels + c) * PP + bin;
+    // pass 0: RoI rect -> RoI max and frame max (cells not strictly inside the inner rect)
+    {
+      const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
+      float m = 0.f, mf = 0.f;  // maxval starts at 0 (ROILoopPool_cuda.cu:109-110)
+      int mi = -1, mfi = -1;
+      for (int h = range_lo(hb); h < range_hi(hb); ++h) {
+        const bool in_h = h > lr.in0[1] && h < lr.in0[3];
+        for (int w = range_lo(wb); w < range_hi(wb); ++w) {
+          const int idx = h * W + w;
+          const float v = plane_at<T, kSmem>(plane_s, src, idx);
+          if (v > m) { m = v; mi = idx; }
+          if (in_h && w > lr.in0[0] && w < lr.in0[2]) continue;
+          if (v > mf) { mf = v; mfi = idx; }
+        }
+      }
+      output[o] = Elem<T>::from_f(m);
+      argmax[o] = mi;
+      output[o + set] = Elem<T>::from_f(mf);
+      argmax[o + set] = mfi;
+    }
+    // pass 1: outer rect -> context max (cells not strictly inside the RoI rect)
+    {
+      const uint32_t hb = ws.hbins[set_h + (size_t)r * PH + ph], wb = ws.wbins[set_w + (size_t)r * PW + pw];
+      float mf = 0.f;
+      int mfi = -1;
+      for (int h = range_lo(hb); h < range_hi(hb); ++h) {
+        const bool in_h = h > lr.in1[1] && h < lr.in1[3];
+        for (int w = range_lo(wb); w < range_hi(wb); ++w) {
+          if (in_h && w > lr.in1[0] && w < lr.in1[2]) continue;
+          const int idx = h * W + w;
+          const float v = plane_at<T, kSmem>(plane_s, src, idx);
+          if (v > mf) { mf = v; mfi = idx; }
+        }
+      }
+      output[o + 2 * set] = Elem<T>::from_f(mf);
+      argmax[o + 2 * set] = mfi;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// MOIPool
+// ---------------------------------------------------------------------------------------------
+// mask[r, h, w] = 1 iff the cell lies in the RoI rectangle (inclusive ends) and some superpixel under the
+// cell's footprint is switched on for this RoI (MOIPool_cuda.cu:151-214).
+__global__ void __launch_bounds__(256)
+moi_mask_kernel(const float* __restrict__ rois, const int* __restrict__ oh_labels, int len_labels,
+                const int* __restrict__ superpixels, int Hs, int Ws, int batch, int H, int W, float scale,
+                int num_rois, unsigned char* __restrict__ mask) {
+  const int hw = H * W;
+  const int r = blockIdx.y;
+  const float* q = rois + (size_t)r * 5;
+  const int b = (int)q[0];
+  const RoiRect rc = roi_rect(q[1], q[2], q[3], q[4], scale);
+  const float ss = (float)(1.0 * H / (double)Hs);  // MOIPool_cuda.cu:175
+  const int* spp = superpixels + (size_t)b * Hs * Ws;
+  const int* ohl = oh_labels + (size_t)r * len_labels;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < hw; p += gridDim.x * blockDim.x) {
+    const int h = p / W, w = p - h * W;
+    unsigned char v = 0;
+    if (b >= 0 && b < batch && w >= rc.sw && w <= rc.ew && h >= rc.sh && h <= rc.eh) {
+      int hh0 = (int)floorf(__fdiv_rn((float)h, ss)), ww0 = (int)floorf(__fdiv_rn((float)w, ss));
+      int hh1 = (int)ceilf(__fdiv_rn((float)(h + 1), ss)), ww1 = (int)ceilf(__fdiv_rn((float)(w + 1), ss));
+      hh0 = min(max(hh0, 0), Hs); hh1 = min(max(hh1, 0), Hs);
+      ww0 = min(max(ww0, 0), Ws); ww1 = min(max(ww1, 0), Ws);
+      int prev = -1;
+      for (int hh = hh0; hh < hh1 && !v; ++hh)
+        for (int ww = ww0; ww < ww1; ++ww) {
+          const int id = __ldg(spp + (size_t)hh * Ws + ww);
+          if (id == prev) continue;
+          prev = id;
+          if (id >= 0 && id < len_labels && __ldg(ohl + id) == 1) {
+            v = 1;
+            break;
+          }
+        }
+    }
+    mask[(size_t)r * hw + p] = v;
+  }
+}
+
+template <typename T, bool kSmem>
+__global__ void __launch_bounds__(kWslThreads)
+moi_pool_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW, int splits,
+                    PoolWorkspace ws, const unsigned char* __restrict__ mask, T* __restrict__ output,
+                    int* __restrict__ argmax) {
+  extern __shared__ float plane_s[];
+  const int item = blockIdx.x;
+  const int s = item % splits;
+  const int nc = item / splits;
+  const int n = nc / channels;
+  const int c = nc - n * channels;
+  const int first = ws.first[n];
+  const int last = -ws.neg_last[n];
+  if (first > last) return;
+  const int len = last - first + 1;
+  const int r0 = first + (int)(((long long)len * s) / splits);
+  const int r1 = first + (int)(((long long)len * (s + 1)) / splits);
+  if (r0 >= r1) return;
+  const int hw = H * W;
+  const T* src = input + (size_t)nc * hw;
+  if (kSmem) {
+    for (int p = threadIdx.x; p < hw; p += kWslThreads) plane_s[p] = Elem<T>::to_f(src[p]);
+    __syncthreads();
+  }
+  const int PP = PH * PW;
+  const int total = (r1 - r0) * PP;
+  for (int i = threadIdx.x; i < total; i += kWslThreads) {
+    const int rl = i / PP;
+    const int bin = i - rl * PP;
+    const int ph = bin / PW, pw = bin - ph * PW;
+    const int r = r0 + rl;
+    if (ws.batch_idx[r] != n) continue;
+    const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
+    const unsigned char* mk = mask + (size_t)r * hw;
+    float m = -FLT_MAX;
+    int mi = -1;
+    for (int h = range_lo(hb); h < range_hi(hb); ++h)
+      for (int w = range_lo(wb); w < range_hi(wb); ++w) {
+        const int idx = h * W + w;
+        if (!__ldg(mk + idx)) continue;
+        const float v = plane_at<T, kSmem>(plane_s, src, idx);
+        if (v > m) { m = v; mi = idx; }
+      }
+    const size_t o = ((size_t)r * channels + c) * PP + bin;
+    output[o] = Elem<T>::from_f(mi == -1 ? 0.f : m);
+    argmax[o] = mi;
+  }
+}
+
+}  // namespace jtsm
+
+using namespace jtsm;
+
+namespace {
+int wsl_splits(int planes, int num_rois) {
+  long long s = (4LL * num_sms() * 4 + planes - 1) / planes;
+  const long long cap = num_rois / 32 > 1 ? num_rois / 32 : 1;
+  s = s > cap ? cap : (s < 1 ? 1 : s);
+  return (int)s;
+}
+}  // namespace
+
+namespace jtsm {
+__global__ void moi_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, int H, int W,
+                                float scale, int PH, int PW, PoolWorkspace ws) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= num_rois) return;
+  const float* q = rois + (size_t)r * 5;
+  const int b = (int)q[0];
+  const RoiRect rc = roi_rect(q[1], q[2], q[3], q[4], scale);
+  const int w_ = max(rc.ew - rc.sw + 1, 1), h_ = max(rc.eh - rc.sh + 1, 1);
+  for (int p = 0; p < PH; ++p) ws.hbins[(size_t)r * PH + p] = bin_range(p, rc.sh, h_, PH, H);
+  for (int p = 0; p < PW; ++p) ws.wbins[(size_t)r * PW + p] = bin_range(p, rc.sw, w_, PW, W);
+  const bool ok = b >= 0 && b < batch;
+  ws.batch_idx[r] = ok ? b : -1;
+  if (ok) {
+    atomicMin(ws.first + b, r);
+    atomicMin(ws.neg_last + b, -r);
+  }
+}
+}  // namespace jtsm
+
+extern "C" size_t jtsm_roi_loop_pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w) {
+  if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0) return 0;
+  return pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 2) +
+         align_up((size_t)num_rois * sizeof(LoopRects), 256) + 256;
+}
+
+extern "C" int jtsm_roi_loop_pool_forward(const void* input, const float* rois, int dtype, int batch,
+                                          int channels, int height, int width, int num_rois,
+                                          float spatial_scale, float context_ratio, int pooled_h,
+                                          int pooled_w, void* output, int* argmax, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 ||
+      pooled_h > 64 || pooled_w > 64 || !(context_ratio > 0.f))
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (height > 32767 || width > 32767) return JTSM_ERR_UNSUPPORTED;
+  if (num_rois == 0 || channels == 0) return JTSM_OK;
+  if (!input || !rois || !output || !argmax || !workspace || batch == 0 || height == 0 || width == 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (workspace_bytes < jtsm_roi_loop_pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w))
+    return JTSM_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 2);
+  LoopRects* rects = (LoopRects*)(((uintptr_t)workspace + pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 2) + 255) &
+                                  ~(uintptr_t)255);
+  cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
+  loop_pool_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width, spatial_scale,
+                                                                context_ratio, pooled_h, pooled_w, ws, rects);
+  count_launch();
+  const int planes = batch * channels;
+  const int splits = wsl_splits(planes, num_rois);
+  const size_t smem = (size_t)height * width * sizeof(float);
+  const bool use_smem = smem <= 200 * 1024;
+  JTSM_DISPATCH_DTYPE(dtype, T, {
+    if (use_smem) {
+      auto k = loop_pool_fwd_kernel<T, true>;
+      if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
+                                                     splits, num_rois, ws, rects, (T*)output, argmax);
+    } else {
+      loop_pool_fwd_kernel<T, false><<<planes * splits, kWslThreads, 0, st>>>(
+          (const T*)input, channels, height, width, pooled_h, pooled_w, splits, num_rois, ws, rects, (T*)output, argmax);
+    }
+  });
+  count_launch();
+  return cuda_status();
+}
+
+extern "C" size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width, int num_rois, int pooled_h,
+                                                int pooled_w) {
+  if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 || height < 0 || width < 0) return 0;
+  return pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 1) +
+         align_up((size_t)num_rois * height * width, 256) + 256;
+}
+
+extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const int* oh_labels, int len_labels,
+                                     const int* superpixels, int height_sp, int width_sp, int dtype, int batch,
+                                     int channels, int height, int width, int num_rois, float spatial_scale,
+                                     int pooled_h, int pooled_w, void* output, int* argmax, void* workspace,
+                                     size_t workspace_bytes, void* stream) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 ||
+      pooled_h > 64 || pooled_w > 64 || len_labels < 0 || height_sp <= 0 || width_sp <= 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (height > 32767 || width > 32767) return JTSM_ERR_UNSUPPORTED;
+  if (num_rois == 0 || channels == 0) return JTSM_OK;
+  if (!input || !rois || !oh_labels || !superpixels || !output || !argmax || !workspace || batch == 0 ||
+      height == 0 || width == 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (workspace_bytes < jtsm_moi_pool_workspace_bytes(batch, height, width, num_rois, pooled_h, pooled_w))
+    return JTSM_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 1);
+  unsigned char* mask = (unsigned char*)(((uintptr_t)workspace + pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 1) + 255) &
+                                         ~(uintptr_t)255);
+  cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
+  moi_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width, spatial_scale,
+                                                          pooled_h, pooled_w, ws);
+  const int hw = height * width;
+  dim3 mgrid((hw + 255) / 256 > 32 ? 32 : (hw + 255) / 256, num_rois);
+  moi_mask_kernel<<<mgrid, 256, 0, st>>>(rois, oh_labels, len_labels, superpixels, height_sp, width_sp, batch,
+                                         height, width, spatial_scale, num_rois, mask);
+  count_launch(2);
+  const int planes = batch * channels;
+  const int splits = wsl_splits(planes, num_rois);
+  const size_t smem = (size_t)hw * sizeof(float);
+  const bool use_smem = smem <= 200 * 1024;
+  JTSM_DISPATCH_DTYPE(dtype, T, {
+    if (use_smem) {
+      auto k = moi_pool_fwd_kernel<T, true>;
+      if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
+                                                     splits, ws, mask, (T*)output, argmax);
+    } else {
+      moi_pool_fwd_kernel<T, false><<<planes * splits, kWslThreads, 0, st>>>(
+          (const T*)input, channels, height, width, pooled_h, pooled_w, splits, ws, mask, (T*)output, argmax);
+    }
+  });
+  count_launch();
+  return cuda_status();
+}

@@ -421,3 +421,66 @@ def roi_align_backward(grad, rois, spatial_scale, pooled_height, pooled_width, b
                                         int(pooled_height), int(pooled_width), int(sampling_ratio), int(bool(aligned)),
                                         _ptr(grad_input), _ptr(ws), wsb, _stream()), "roi_align_backward")
     return grad_input
+
+
+# --------------------------------------------------------------------------- WSL pools
+def roi_loop_pool_forward(input, rois, spatial_scale, pooled_height, pooled_width, context_ratio=1.8):
+    """wsl._C.roi_loop_pool_forward (ROILoopPool.h:48-53) -> (output [3R,C,PH,PW], argmax int32)."""
+    _require_cuda(input, rois)
+    assert rois.dim() == 2 and rois.size(1) == 5
+    n, c, h, w = input.shape
+    r = rois.size(0)
+    ph, pw = int(pooled_height), int(pooled_width)
+    input = input.contiguous()
+    rois = _rois_f32(rois)
+    output = torch.empty((3 * r, c, ph, pw), dtype=input.dtype, device=input.device)
+    argmax = torch.empty((3 * r, c, ph, pw), dtype=torch.int32, device=input.device)
+    if r == 0 or c == 0:
+        return output, argmax
+    L = lib()
+    wsb = L.jtsm_roi_loop_pool_workspace_bytes(n, r, ph, pw)
+    ws = _workspace(wsb, input.device)
+    with torch.cuda.device(input.device):
+        check(L.jtsm_roi_loop_pool_forward(_ptr(input), _ptr(rois), _dtype_code(input), n, c, h, w, r,
+                                           float(spatial_scale), float(context_ratio), ph, pw, _ptr(output),
+                                           _ptr(argmax), _ptr(ws), wsb, _stream()), "roi_loop_pool_forward")
+    return output, argmax
+
+
+def roi_loop_pool_backward(grad, rois, argmax, spatial_scale, pooled_height, pooled_width, batch_size, channels,
+                           height, width):
+    """wsl._C.roi_loop_pool_backward (ROILoopPool.h:67-77): rows [R,2R) and [2R,3R) belong to RoI n % R."""
+    return roi_pool_backward(grad, rois.repeat(3, 1), argmax, (batch_size, channels, height, width),
+                             (pooled_height, pooled_width))
+
+
+def moi_pool_forward(input, rois, spatial_scale, pooled_height, pooled_width, oh_labels, superpixels):
+    """wsl._C.moi_pool_forward (MOIPool.h:52-59) -> (output [R,C,PH,PW], argmax int32)."""
+    _require_cuda(input, rois, oh_labels, superpixels)
+    assert rois.dim() == 2 and rois.size(1) == 5
+    n, c, h, w = input.shape
+    r = rois.size(0)
+    ph, pw = int(pooled_height), int(pooled_width)
+    input = input.contiguous()
+    rois = _rois_f32(rois)
+    oh = oh_labels.to(torch.int32).contiguous()
+    sp = superpixels.to(torch.int32).contiguous()
+    assert oh.dim() == 2 and oh.size(0) == r and sp.dim() == 3 and sp.size(0) == n
+    output = torch.empty((r, c, ph, pw), dtype=input.dtype, device=input.device)
+    argmax = torch.empty((r, c, ph, pw), dtype=torch.int32, device=input.device)
+    if r == 0 or c == 0:
+        return output, argmax
+    L = lib()
+    wsb = L.jtsm_moi_pool_workspace_bytes(n, h, w, r, ph, pw)
+    ws = _workspace(wsb, input.device)
+    with torch.cuda.device(input.device):
+        check(L.jtsm_moi_pool_forward(_ptr(input), _ptr(rois), _ptr(oh), oh.size(1), _ptr(sp), sp.size(1), sp.size(2),
+                                      _dtype_code(input), n, c, h, w, r, float(spatial_scale), ph, pw, _ptr(output),
+                                      _ptr(argmax), _ptr(ws), wsb, _stream()), "moi_pool_forward")
+    return output, argmax
+
+
+def moi_pool_backward(grad, rois, argmax, spatial_scale, pooled_height, pooled_width, batch_size, channels, height,
+                      width):
+    """wsl._C.moi_pool_backward (MOIPool.h:85-95)."""
+    return roi_pool_backward(grad, rois, argmax, (batch_size, channels, height, width), (pooled_height, pooled_width))

@@ -118,3 +118,23 @@ def expand_grad_tile(tile, num_rois):
     """grad_pooled[r] = tile[r % tile.shape[0]] (host or device)."""
     reps = (num_rois + tile.shape[0] - 1) // tile.shape[0]
     return tile.repeat(reps, 1, 1, 1)[:num_rois].contiguous()
+
+
+def superpixels(g, n, hs, ws, block=24):
+    """Blocky superpixel label images [n, hs, ws] int32 (ids 0..S-1, jittered block grid) -> (labels, S)."""
+    rows, cols = (hs + block - 1) // block, (ws + block - 1) // block
+    s = rows * cols
+    out = []
+    for _ in range(n):
+        perm = torch.randperm(s, generator=g).to(torch.int32).view(rows, cols)
+        jy = torch.randint(0, block // 2 + 1, (1,), generator=g).item()
+        jx = torch.randint(0, block // 2 + 1, (1,), generator=g).item()
+        yy = ((torch.arange(hs) + jy) // block).clamp(max=rows - 1)
+        xx = ((torch.arange(ws) + jx) // block).clamp(max=cols - 1)
+        out.append(perm[yy][:, xx])
+    return torch.stack(out).contiguous(), s
+
+
+def oh_labels(g, num_rois, s, p=0.35):
+    """oh_labels [R, S] int32: which superpixels are switched on for each RoI."""
+    return (torch.rand(num_rois, s, generator=g) < p).to(torch.int32)

@@ -1,0 +1,72 @@
+"""GPU parity of the WSL project's pooling ops (ROILoopPool, MOIPool) through the C ABI vs the CPU oracle
+restated from the reference CUDA kernels (the reference has no runnable CPU path and no test for these ops:
+parity unpinned by the reference itself; oracle properties are pinned in tests/test_oracle_pool.py).
+Forward values / argmax: bit-exact.  Backward: fp32 atomics -> rel 1e-5."""
+import numpy as np
+import pytest
+import torch
+
+from jtsm_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _case(seed, n, c, h, w, r):
+    g = synth.generator(seed)
+    x = synth.feature_map(g, n, c, h, w)
+    boxes = [synth.proposals(g, r, 600, 800) for _ in range(n)]
+    rois = synth.rois_from_boxes(boxes)
+    return g, x, rois[torch.randperm(rois.shape[0], generator=g)]
+
+
+@pytest.mark.parametrize("n,c,h,w,r,scale,pooled", [(1, 6, 38, 50, 80, 1 / 16.0, (7, 7)), (2, 4, 75, 100, 60, 1 / 8.0, (7, 7)),
+                                                   (1, 3, 75, 100, 40, 1 / 8.0, (3, 5)), (1, 2, 300, 400, 24, 1 / 2.0, (7, 7))])
+def test_roi_loop_pool_matches_oracle(cuda, oracle, n, c, h, w, r, scale, pooled):
+    from jtsm_b200 import ops
+    from jtsm_b200.layers import ROILoopPool
+
+    g, x, rois = _case(71, n, c, h, w, r)
+    ref, rarg = oracle.roi_loop_pool_forward(x.numpy(), rois.numpy(), scale, pooled)
+    out, arg = ops.roi_loop_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1])
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert np.array_equal(arg.cpu().numpy(), rarg)
+    # module + autograd: backward == shared max-pool backward over 3R rows
+    xg = x.to(cuda).requires_grad_()
+    y = ROILoopPool(pooled, scale)(xg, rois.to(cuda))
+    go = torch.randn(y.shape, generator=synth.generator(72))
+    y.backward(go.to(cuda))
+    gi_ref = oracle.max_pool_backward(go.numpy(), rarg, np.tile(rois.numpy(), (3, 1)), tuple(x.shape))
+    np.testing.assert_allclose(xg.grad.cpu().numpy(), gi_ref, rtol=1e-5, atol=1e-5 * float(np.abs(gi_ref).max()))
+
+
+@pytest.mark.parametrize("n,c,h,w,r,scale,pooled,block", [(1, 6, 38, 50, 80, 1 / 16.0, (7, 7), 24), (2, 4, 75, 100, 60, 1 / 8.0, (7, 7), 40),
+                                                         (1, 3, 75, 100, 40, 1 / 8.0, (14, 14), 12)])
+def test_moi_pool_matches_oracle(cuda, oracle, n, c, h, w, r, scale, pooled, block):
+    from jtsm_b200.layers import MOIPool
+
+    g, x, rois = _case(73, n, c, h, w, r)
+    sp, s = synth.superpixels(g, n, 600, 800, block)
+    oh = synth.oh_labels(g, rois.shape[0], s)
+    ref, rarg = oracle.moi_pool_forward(x.numpy(), rois.numpy(), oh.numpy(), sp.numpy(), scale, pooled)
+    xg = x.to(cuda).requires_grad_()
+    out, arg = MOIPool(pooled, scale)(xg, rois.to(cuda), oh.to(cuda), sp.to(cuda))
+    assert arg.dtype == torch.int32
+    assert np.array_equal(out.detach().cpu().numpy(), ref)
+    assert np.array_equal(arg.cpu().numpy(), rarg)
+    assert (rarg == -1).any() and (rarg >= 0).any()
+    go = torch.randn(out.shape, generator=synth.generator(74))
+    out.backward(go.to(cuda))
+    gi_ref = oracle.max_pool_backward(go.numpy(), rarg, rois.numpy(), tuple(x.shape))
+    np.testing.assert_allclose(xg.grad.cpu().numpy(), gi_ref, rtol=1e-5, atol=1e-5 * float(np.abs(gi_ref).max()))
+
+
+def test_wsl_pools_empty(cuda):
+    from jtsm_b200 import ops
+
+    x = torch.rand(1, 3, 8, 8, device=cuda)
+    out, arg = ops.roi_loop_pool_forward(x, torch.zeros(0, 5, device=cuda), 1.0, 7, 7)
+    assert out.shape == (0, 3, 7, 7) and arg.shape == (0, 3, 7, 7)
+    out, arg = ops.moi_pool_forward(x, torch.zeros(0, 5, device=cuda), 1.0, 7, 7,
+                                    torch.zeros(0, 4, dtype=torch.int32, device=cuda),
+                                    torch.zeros(1, 16, 16, dtype=torch.int32, device=cuda))
+    assert out.shape == (0, 3, 7, 7)
