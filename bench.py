@@ -39,7 +39,7 @@ UNIT = "RoIs/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="c2")
@@ -69,6 +69,11 @@ class ClockSampler:
         self.index = index
         self.proc = None
         self.lines = []
+        self.mark_at = 0
+
+    def mark(self):
+        """Samples from here on count as 'during the timed region' (falls back to all if none arrive)."""
+        self.mark_at = len(self.lines)
 
     def start(self):
         try:
@@ -94,7 +99,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for l in self.lines:
+        lines = self.lines[self.mark_at:] or self.lines
+        for l in lines:
             f = [t.strip() for t in l.split(",")]
             if len(f) < 6:
                 continue
@@ -153,6 +159,9 @@ def run_b200(a):
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()  # fail loudly if libjtsm_b200.so is missing
 
+    sampler = ClockSampler(local)  # started early: nvidia-smi needs ~1 s to deliver its first sample
+    if rank == 0:
+        sampler.start()
     wl = make_workload(a.config, rank, a.dtype)
     cfg = wl["cfg"]
     R = cfg["N"] * cfg["R"]
@@ -169,9 +178,6 @@ def run_b200(a):
             torch.cuda.synchronize()
 
     # ---------------- device-resident timing (value) ----------------
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     use_graph = not a.no_graph
     if use_graph:
         step.capture(resident)
@@ -184,6 +190,7 @@ def run_b200(a):
     lc0 = _lib.launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     barrier()
+    sampler.mark()
     t_wall0 = time.perf_counter()
     for i in range(a.steps):
         flush.zero_()

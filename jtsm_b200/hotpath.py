@@ -117,8 +117,13 @@ class HotPathStep:
     def results(self, last=None):
         last = last or self.last
         h = last["heads"]
-        res = [last["grad_feat"], torch.cat([v.reshape(1) for v in h["losses"].values()])]
-        return res + [b["gt_classes"] for b in h["branches"]]
+        # what the host consumes per step: losses, pseudo-labels and the logging counters.  The gradient
+        # w.r.t. the feature map stays on the device (it feeds the backbone's backward); a checksum of it
+        # is read back so the D2H depends on the whole step.
+        res = [torch.cat([v.reshape(1) for v in h["losses"].values()]), last["grad_feat"].sum().reshape(1)]
+        for b in h["branches"]:
+            res += [b["gt_classes"], b["counters"], b["acc"]]
+        return res
 
     def replay_from_host(self, host):
         """H2D of the step's inputs into the graph's static buffers, replay, blocking D2H of the results."""
@@ -136,9 +141,6 @@ class HotPathStep:
     def run_from_host(self, host):
         d = self.upload(host)
         self.run(d)
-        h = self.last["heads"]
-        res = [self.last["grad_feat"], torch.cat([v.reshape(1) for v in h["losses"].values()])]
-        res += [b["gt_classes"] for b in h["branches"]]
-        out = [t.to("cpu") for t in res]  # blocking D2H: gradient to the backbone, losses, pseudo-labels
+        out = [t.to("cpu") for t in self.results()]  # blocking D2H: losses, pseudo-labels, counters
         self._d2h = sum(t.numel() * t.element_size() for t in out)
         return out
