@@ -46,16 +46,17 @@ def pairwise_iou(b1, b2):
     wh = torch.min(b1[:, None, 2:], b2[:, 2:]) - torch.max(b1[:, None, :2], b2[:, :2])
     wh.clamp_(min=0)
     inter = wh.prod(dim=2)
-    return torch.where(inter > 0, inter / (area1[:, None] + area2 - inter), torch.zeros(1, dtype=inter.dtype))
+    return torch.where(inter > 0, inter / (area1[:, None] + area2 - inter), torch.zeros(1, dtype=inter.dtype, device=inter.device))
 
 
 def matcher(quality, thresholds=(0.5,), labels=(0, 1)):
     """Matcher.__call__ without low-quality matches.  detectron2/modeling/matcher.py:61-103."""
     if quality.numel() == 0:
         n = quality.size(1)
-        return torch.zeros(n, dtype=torch.int64), torch.full((n,), labels[0], dtype=torch.int8)
+        return (torch.zeros(n, dtype=torch.int64, device=quality.device),
+                torch.full((n,), labels[0], dtype=torch.int8, device=quality.device))
     vals, matches = quality.max(dim=0)
-    out = torch.full(matches.size(), 1, dtype=torch.int8)
+    out = torch.full(matches.size(), 1, dtype=torch.int8, device=quality.device)
     th = [-float("inf")] + list(thresholds) + [float("inf")]
     for l, low, high in zip(labels, th[:-1], th[1:]):
         out[(vals >= low) & (vals < high)] = l
@@ -134,7 +135,8 @@ def label_proposals(pgt, proposal_boxes, num_classes, thresholds=(0.5,), labels=
                     matched_iou=q.max(dim=0)[0])
     r = proposal_boxes.size(0)
     return dict(matched_idx=midx, gt_classes=torch.zeros_like(midx) + num_classes, gt_boxes=proposal_boxes,
-                gt_scores=torch.zeros(r), gt_weights=torch.zeros(r), matched_iou=torch.zeros(r))
+                gt_scores=proposal_boxes.new_zeros(r), gt_weights=proposal_boxes.new_zeros(r),
+                matched_iou=proposal_boxes.new_zeros(r))
 
 
 # ---------------------------------------------------------------- OICR losses (fast_rcnn_oicr.py)
@@ -177,9 +179,9 @@ def oicr_box_reg_loss(deltas, proposals, gt_boxes, gt_classes, gt_weights, num_c
     w, _ = oicr_weights(gt_classes, gt_weights)
     fg = torch.nonzero((gt_classes >= 0) & (gt_classes < num_classes), as_tuple=True)[0]
     if deltas.size(1) == 4:
-        cols = torch.arange(4)
+        cols = torch.arange(4, device=deltas.device)
     else:
-        cols = 4 * gt_classes[fg][:, None] + torch.arange(4)
+        cols = 4 * gt_classes[fg][:, None] + torch.arange(4, device=deltas.device)
     tgt = get_deltas(proposals, gt_boxes, weights)
     l = smooth_l1(deltas[fg[:, None], cols], tgt[fg], beta)
     if weighted:
@@ -201,7 +203,7 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposal_boxes, labels, 
     D = mil_det.clone().requires_grad_(need_grad)
     RL = [x.clone().requires_grad_(need_grad) for x in ref_logits]
     RD = [x.clone().requires_grad_(need_grad) for x in ref_deltas]
-    oh = torch.zeros(n, num_classes)
+    oh = torch.zeros(n, num_classes, device=mil_cls.device)
     for i, l in enumerate(labels):
         oh[i, l] = 1.0
     scores = wsddn_scores(C, D, num_preds)
@@ -223,7 +225,7 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposal_boxes, labels, 
             losses["loss_box_reg_r%d" % k] = oicr_box_reg_loss(RD[k], allp, gt_boxes, gt_classes, gt_weights,
                                                                num_classes, weighted=reg_weighted)
         probs = F.softmax(RL[k].detach(), dim=-1)
-        dl = RD[k].detach() if reg else torch.zeros(allp.shape[0], 4 * num_classes)
+        dl = RD[k].detach() if reg else torch.zeros(allp.shape[0], 4 * num_classes, device=allp.device)
         boxes = apply_deltas(dl, allp)
         prev_scores = list(probs.split(num_preds, dim=0))
         prev_boxes = list(boxes.split(num_preds, dim=0))
