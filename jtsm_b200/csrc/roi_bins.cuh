@@ -49,26 +49,32 @@ struct PoolWorkspace {
   int* first;        // [batch]   min roi index of image n   (INT-ish max if none)
   int* neg_last;     // [batch]   -(max roi index of image n)
   int* ungrouped;    // [1]       != 0 when batch indices are not non-decreasing in r
-  // range-max-table kernel descriptors (roi_pool_rmq.cuh)
-  uint4* hdesc;      // [R * P]  {hs*W | hl*W << 16, qh | big << 2 | empty << 3 | len << 8, row_scale bits, batch}
-  uint2* wdesc;      // [R * P]  {ws | wl << 16,     qw | big << 2 | empty << 3 | len << 8}
+  // range-max-table kernel descriptors (roi_pool_rmq.cuh); byte offsets into the table block
+  uint4* hdesc;      // [R * P]  {2*(hs*W + qh*hw), 2*(hl*W + qh*hw), row_scale bits, hgood << 28 | batch & 0xFFFFFF}
+  uint32_t* wdesc;   // [R * wstride]  2*(ws + 2*qw*hw) | 2*(wl - ws) << 20 | wgood << 28 ; wstride = rmq_wstride(P)
 };
 
 // descriptor of one axis range [s, e): level q = floor(log2(len)) capped at 3, start of the last
-// window e - 2^q, `big` when two windows of the level do not cover the range.
-__device__ __forceinline__ void rmq_axis_desc(uint32_t packed, int mult, uint32_t& x, uint32_t& y) {
+// window l = e - 2^q.  x/y = byte offsets of the two windows inside table slot q*slot_mult
+// (cell stride `mult`); `good` = 4-bit mask, 0 when the range is empty or two windows of the level
+// do not cover it: for the h axis the set of w levels stored next to q (|qh - qw| <= 1), for the
+// w axis the single bit 1 << q -- a bin takes the fast path iff hgood & wgood != 0.
+__device__ __forceinline__ void rmq_axis_desc(uint32_t packed, int mult, int slot_mult, int hw, bool h_axis,
+                                              uint32_t& x, uint32_t& y, uint32_t& good) {
   const int s = range_lo(packed), e = range_hi(packed);
   const int len = e - s;
-  if (len <= 0) {
-    x = 0;
-    y = 8u;
-    return;
-  }
+  x = y = good = 0;
+  if (len <= 0) return;
   const int q = min(3, 31 - __clz(len));
-  const int big = len > (2 << q);
-  x = (uint32_t)(s * mult) | ((uint32_t)((e - (1 << q)) * mult) << 16);
-  y = (uint32_t)q | ((uint32_t)big << 2) | ((uint32_t)len << 8);
+  if (len > (2 << q)) return;
+  const int base = q * slot_mult * hw;
+  x = 2u * (uint32_t)(s * mult + base);
+  y = 2u * (uint32_t)((e - (1 << q)) * mult + base);
+  good = h_axis ? ((0x7u << q) >> 1) & 0xFu : 1u << q;
 }
+
+// words per RoI in wdesc: PW rounded up to a multiple of 4 so a row loads as 128-bit words
+__host__ __device__ inline int rmq_wstride(int pooled_w) { return (pooled_w + 3) & ~3; }
 
 inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w, int sets) {
   size_t b = 0;
@@ -77,7 +83,7 @@ inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int po
   b += align_up((size_t)num_rois * 4, 256);
   b += align_up((size_t)batch * 4 * 2 + 16, 256);
   b += align_up((size_t)num_rois * pooled_h * 16, 256);
-  b += align_up((size_t)num_rois * pooled_w * 8, 256);
+  b += align_up((size_t)num_rois * rmq_wstride(pooled_w) * 4, 256);
   return b + 256;
 }
 
@@ -92,7 +98,7 @@ inline PoolWorkspace carve_pool_workspace(void* ws, int batch, int num_rois, int
   w.ungrouped = w.neg_last + batch;
   p += align_up((size_t)batch * 4 * 2 + 16, 256);
   w.hdesc = (uint4*)p; p += align_up((size_t)num_rois * pooled_h * 16, 256);
-  w.wdesc = (uint2*)p;
+  w.wdesc = (uint32_t*)p;
   return w;
 }
 

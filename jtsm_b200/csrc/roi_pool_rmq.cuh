@@ -1,4 +1,4 @@
-// RoIPool forward with per-plane 2-D range-max index tables ("rmq" kernel).
+// RoIPool forward with per-plane 2-D range-max index tables ("rmq" kernels).
 //
 // Why: the direct per-bin scan reads RoI-area x ~1.6 cells per (RoI, channel) -- 1.07 G shared
 // memory reads per step at config 2 -- and is LSU/issue bound at ~880 us (profiles/r1a), 20x off
@@ -14,27 +14,32 @@
 // (10 tables incl. identity, 24 B per cell in total with the fp32 plane -> 180 KB at 75x100);
 // more elongated bins use the nearest stored level and a few more windows.
 //
+// Table (kh, kw) lives in slot kh + 2 * kw, so the byte address of a look-up is the SUM of a
+// per-(RoI, ph) part 2*(h*W + kh*hw) and a per-(RoI, pw) part 2*(w + 2*kw*hw): the prep kernel
+// stores both parts (the w part packed in one word), and whether the pair of levels is a stored one is a single AND of two masks.
+//
 // One persistent CTA per SM walks a contiguous range of (plane, RoI-chunk) items, rebuilding the
-// tables only when the plane changes (~3.5 builds per CTA at config 2).
+// tables only when the plane changes (~3.5 builds per CTA at config 2); one thread per bin, lanes
+// along consecutive bins of a RoI.  (A one-thread-per-output-row variant with staged write-out
+// needed 2.5x fewer instructions but 25% more shared-memory wavefronts -- lanes on different rows
+// collide on banks -- and measured 418 us vs 362 us, so it is not kept: profiles/r1f.)
 #pragma once
 #include "roi_bins.cuh"
 
 namespace jtsm {
 
 constexpr int kRmqThreads = 1024;
-constexpr int kRmqTables = 10;   // slot = 3*min(kh,kw) + (kh-kw+1); slot 1 = identity, (3,3) -> 9
+constexpr int kRmqTables = 10;   // slot = kh + 2*kw for |kh-kw| <= 1, kh,kw in 0..3; slot 0 = identity
 constexpr int kRmqMaxLevel = 3;  // windows of 1,2,4,8 cells per axis
+constexpr unsigned kRmqGoodMask = 0xF0000000u;
 
 __host__ __device__ inline size_t rmq_smem_bytes(int hw) {
   return (size_t)hw * 4 + (size_t)kRmqTables * hw * 2 + 16;
 }
 
-__device__ __forceinline__ int rmq_slot(int kh, int kw) {
-  const int m = min(kh, kw);
-  return m == kRmqMaxLevel ? 9 : 3 * m + (kh - kw + 1);
-}
+__device__ __forceinline__ int rmq_slot(int kh, int kw) { return kh + 2 * kw; }
 
-// exact h = p / W for p < 65536 (magic = ceil(2^32 / W))
+// exact p / d for p < 2^32 / d (magic = ceil(2^32 / d))
 __device__ __forceinline__ int fast_div(int p, unsigned magic) { return (int)__umulhi((unsigned)p, magic); }
 
 // (value, index) candidate; better = larger value, then smaller index (= first in row-major order)
@@ -69,10 +74,41 @@ __device__ __forceinline__ void rmq_build_level(const float* plane, const unsign
   }
 }
 
-// Slow path of one bin (elongated or > 16-cell ranges): nearest stored level, as many windows as needed.
-__device__ __noinline__ RmqCand rmq_query_generic(const float* plane, const unsigned short* tabs, int hw, int W,
-                                                  int hs, int lh, int wst, int lw) {
-  const int he = hs + lh, wen = wst + lw;
+// plane (fp32) + the 10 tables of one (image, channel) plane; all threads of the CTA call it.
+template <typename T>
+__device__ __forceinline__ void rmq_build_plane(const T* __restrict__ src, float* plane, unsigned short* tabs,
+                                                int hw, int W, unsigned magic_w) {
+#define TAB(s) (tabs + (size_t)(s) * hw)
+  for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
+    plane[p] = Elem<T>::to_f(src[p]);
+    TAB(0)[p] = (unsigned short)p;  // identity level (0,0)
+  }
+  __syncthreads();
+  rmq_build_level<false>(plane, TAB(0), TAB(2), hw, W, magic_w, 1);  // (0,1)
+  rmq_build_level<true>(plane, TAB(0), TAB(1), hw, W, magic_w, 1);   // (1,0)
+  __syncthreads();
+  rmq_build_level<true>(plane, TAB(2), TAB(3), hw, W, magic_w, 1);   // (1,1)
+  __syncthreads();
+  rmq_build_level<false>(plane, TAB(3), TAB(5), hw, W, magic_w, 2);  // (1,2)
+  rmq_build_level<true>(plane, TAB(3), TAB(4), hw, W, magic_w, 2);   // (2,1)
+  __syncthreads();
+  rmq_build_level<true>(plane, TAB(5), TAB(6), hw, W, magic_w, 2);   // (2,2)
+  __syncthreads();
+  rmq_build_level<false>(plane, TAB(6), TAB(8), hw, W, magic_w, 4);  // (2,3)
+  rmq_build_level<true>(plane, TAB(6), TAB(7), hw, W, magic_w, 4);   // (3,2)
+  __syncthreads();
+  rmq_build_level<true>(plane, TAB(8), TAB(9), hw, W, magic_w, 4);   // (3,3)
+  __syncthreads();
+#undef TAB
+}
+
+// Slow path of one bin (empty, elongated or > 16-cell ranges) from the packed [start, end) ranges:
+// nearest stored level, as many windows as needed.  Empty bin -> value 0, index 0xFFFFFFFF.
+__device__ __noinline__ RmqCand rmq_query_slow(const float* plane, const unsigned short* tabs, int hw, int W,
+                                               uint32_t hb, uint32_t wb) {
+  const int hs = range_lo(hb), he = range_hi(hb), wst = range_lo(wb), wen = range_hi(wb);
+  const int lh = he - hs, lw = wen - wst;
+  if (lh <= 0 || lw <= 0) return {0.f, 0xFFFFFFFFu};
   const int qh = min(kRmqMaxLevel, 31 - __clz(lh));
   const int qw = min(kRmqMaxLevel, 31 - __clz(lw));
   const int kh = min(qh, qw + 1), kw = min(qw, qh + 1);
@@ -92,6 +128,40 @@ __device__ __noinline__ RmqCand rmq_query_generic(const float* plane, const unsi
   return best;
 }
 
+// 2 x 2 windows of a stored level: byte offsets a0/a1 (h part) + b0, b0 + db (w part) into the tables.
+__device__ __forceinline__ RmqCand rmq_query_fast(const float* plane, const unsigned short* tabs, unsigned a0,
+                                                  unsigned a1, unsigned b0, unsigned db) {
+  const char* tb = (const char*)tabs;
+  const unsigned ia = *(const unsigned short*)(tb + (a0 + b0));
+  const unsigned ib = *(const unsigned short*)(tb + (a0 + b0 + db));
+  const unsigned ic = *(const unsigned short*)(tb + (a1 + b0));
+  const unsigned id = *(const unsigned short*)(tb + (a1 + b0 + db));
+  return rmq_best(rmq_best(rmq_load(plane, ia), rmq_load(plane, ib)),
+                  rmq_best(rmq_load(plane, ic), rmq_load(plane, id)));
+}
+
+struct RmqItem {
+  int n, c, r0, nr;
+};
+// (plane, chunk) item -> image, channel and RoI range; nr = 0 when the image has no RoIs
+__device__ __forceinline__ RmqItem rmq_item(int item, int chunks, int channels, const PoolWorkspace& ws, int& nc) {
+  RmqItem it;
+  nc = item / chunks;
+  const int chunk = item - nc * chunks;
+  it.n = nc / channels;
+  it.c = nc - it.n * channels;
+  const int first = ws.first[it.n];
+  const int last = -ws.neg_last[it.n];
+  it.r0 = 0;
+  it.nr = 0;
+  if (first <= last) {
+    const int len = last - first + 1;
+    it.r0 = first + (int)(((long long)len * chunk) / chunks);
+    it.nr = first + (int)(((long long)len * (chunk + 1)) / chunks) - it.r0;
+  }
+  return it;
+}
+
 template <typename T, typename A>
 __global__ void __launch_bounds__(kRmqThreads, 1)
 roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW,
@@ -101,10 +171,9 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
   const int hw = H * W;
   float* plane = (float*)smem_raw;
   unsigned short* tabs = (unsigned short*)(plane + hw);
-#define TAB(s) (tabs + (size_t)(s) * hw)
   const unsigned magic_w = (unsigned)((0x100000000ull + W - 1) / W);
   const unsigned magic_pw = (unsigned)((0x100000000ull + PW - 1) / PW);
-  const int PP = PH * PW;
+  const int PP = PH * PW, wstride = rmq_wstride(PW);
   const int step_r = kRmqThreads / PP, step_b = kRmqThreads - step_r * PP;
   const int rl_init = threadIdx.x / PP, bin_init = threadIdx.x - rl_init * PP;
   const bool ungrouped = *ws.ungrouped != 0;
@@ -116,51 +185,24 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
   int cur_plane = -1;
 
   for (int item = i0; item < i1; ++item) {
-    const int nc = item / chunks;
-    const int chunk = item - nc * chunks;
-    const int n = nc / channels;
-    const int c = nc - n * channels;
+    int nc;
+    const RmqItem it = rmq_item(item, chunks, channels, ws, nc);
     if (nc != cur_plane) {
       __syncthreads();  // previous item's queries are done with the old tables
       cur_plane = nc;
-      const T* src = input + (size_t)nc * hw;
-      for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
-        plane[p] = Elem<T>::to_f(src[p]);
-        TAB(1)[p] = (unsigned short)p;  // identity level (0,0)
-      }
-      __syncthreads();
-      rmq_build_level<false>(plane, TAB(1), TAB(0), hw, W, magic_w, 1);  // (0,1)
-      rmq_build_level<true>(plane, TAB(1), TAB(2), hw, W, magic_w, 1);   // (1,0)
-      __syncthreads();
-      rmq_build_level<true>(plane, TAB(0), TAB(4), hw, W, magic_w, 1);   // (1,1)
-      __syncthreads();
-      rmq_build_level<false>(plane, TAB(4), TAB(3), hw, W, magic_w, 2);  // (1,2)
-      rmq_build_level<true>(plane, TAB(4), TAB(5), hw, W, magic_w, 2);   // (2,1)
-      __syncthreads();
-      rmq_build_level<true>(plane, TAB(3), TAB(7), hw, W, magic_w, 2);   // (2,2)
-      __syncthreads();
-      rmq_build_level<false>(plane, TAB(7), TAB(6), hw, W, magic_w, 4);  // (2,3)
-      rmq_build_level<true>(plane, TAB(7), TAB(8), hw, W, magic_w, 4);   // (3,2)
-      __syncthreads();
-      rmq_build_level<true>(plane, TAB(6), TAB(9), hw, W, magic_w, 4);   // (3,3)
-      __syncthreads();
+      rmq_build_plane(input + (size_t)nc * hw, plane, tabs, hw, W, magic_w);
     }
-    const int first = ws.first[n];
-    const int last = -ws.neg_last[n];
-    if (first > last) continue;
-    const int len = last - first + 1;
-    const int r0 = first + (int)(((long long)len * chunk) / chunks);
-    const int nr = first + (int)(((long long)len * (chunk + 1)) / chunks) - r0;
     const size_t cpp = (size_t)channels * PP;
-    T* out_c = output + (size_t)c * PP;
-    A* arg_c = argmax + (size_t)c * PP;
+    T* out_c = output + (size_t)it.c * PP;
+    A* arg_c = argmax + (size_t)it.c * PP;
+    const unsigned nkey = (unsigned)it.n & 0xFFFFFFu;
     int rl = rl_init, bin = bin_init;
-    while (rl < nr) {
-      const int r = r0 + rl;
+    while (rl < it.nr) {
+      const int r = it.r0 + rl;
       const int ph = fast_div(bin, magic_pw);
       const int pw = bin - ph * PW;
       const uint4 hd = __ldg(ws.hdesc + (size_t)r * PH + ph);
-      const uint2 wd = __ldg(ws.wdesc + (size_t)r * PW + pw);
+      const unsigned wd = __ldg(ws.wdesc + (size_t)r * wstride + pw);
       const size_t o = (size_t)r * cpp + bin;
       // advance (r, bin) by kRmqThreads outputs without a division
       bin += step_b;
@@ -169,32 +211,18 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
         bin -= PP;
         ++rl;
       }
-      if (ungrouped && (int)hd.w != n) continue;
-      const unsigned fl = hd.y | wd.y;
-      float m = 0.f;
-      int mi = -1;
-      if (!(fl & 8u)) {  // non-empty bin
-        const int qh = hd.y & 3, qw = wd.y & 3;
-        RmqCand best;
-        if (!(fl & 4u) && abs(qh - qw) <= 1) {  // 2 x 2 windows of a stored level
-          const unsigned short* tab = TAB(rmq_slot(qh, qw));
-          const unsigned h0 = hd.x & 0xFFFFu, h1 = hd.x >> 16, w0 = wd.x & 0xFFFFu, w1 = wd.x >> 16;
-          const unsigned ia = tab[h0 + w0], ib = tab[h0 + w1], ic = tab[h1 + w0], id = tab[h1 + w1];
-          best = rmq_best(rmq_best(rmq_load(plane, ia), rmq_load(plane, ib)),
-                          rmq_best(rmq_load(plane, ic), rmq_load(plane, id)));
-        } else {
-          const int hs = fast_div((int)(hd.x & 0xFFFFu), magic_w);
-          best = rmq_query_generic(plane, tabs, hw, W, hs, (int)(hd.y >> 8), (int)(wd.x & 0xFFFFu), (int)(wd.y >> 8));
-        }
-        m = best.v;
-        mi = (int)best.i;
+      if (ungrouped && (hd.w & 0xFFFFFFu) != nkey) continue;
+      RmqCand best;
+      if (hd.w & wd & kRmqGoodMask) {
+        best = rmq_query_fast(plane, tabs, hd.x, hd.y, wd & 0xFFFFFu, (wd >> 20) & 0x1Fu);
+      } else {
+        best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)r * PH + ph),
+                              __ldg(ws.wbins + (size_t)r * PW + pw));
       }
-      m = __fmul_rn(m, __uint_as_float(hd.z));
-      out_c[o] = Elem<T>::from_f(m);
-      arg_c[o] = Arg<A>::enc(mi);
+      out_c[o] = Elem<T>::from_f(__fmul_rn(best.v, __uint_as_float(hd.z)));
+      arg_c[o] = Arg<A>::enc((int)best.i);
     }
   }
-#undef TAB
 }
 
 }  // namespace jtsm
