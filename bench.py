@@ -248,7 +248,7 @@ def run_b200(a):
                     "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes()},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": step.dominant_kernel(), "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "peak_source": peak_src, "traffic": step.ncu_traffic(),
+                         "frac": ach / peak, "peak_source": peak_src, "traffic": step.ncu_traffic(wl["name"] if a.dtype == "fp32" else None),
                          "algorithmic_bytes_per_launch": ab["pool_fwd"], "avg_launch_ms": dom_ms,
                          "step_algorithmic_bytes": ab["step"],
                          "step_frac": ab["step"] / (dev_ms / a.steps * 1e-3) / 1e9 / peak},

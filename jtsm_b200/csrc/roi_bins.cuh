@@ -49,32 +49,35 @@ struct PoolWorkspace {
   int* first;        // [batch]   min roi index of image n   (INT-ish max if none)
   int* neg_last;     // [batch]   -(max roi index of image n)
   int* ungrouped;    // [1]       != 0 when batch indices are not non-decreasing in r
-  // range-max-table kernel descriptors (roi_pool_rmq.cuh); byte offsets into the table block
-  uint4* hdesc;      // [R * P]  {2*(hs*W + qh*hw), 2*(hl*W + qh*hw), row_scale bits, hgood << 28 | batch & 0xFFFFFF}
-  uint32_t* wdesc;   // [R * wstride]  2*(ws + 2*qw*hw) | 2*(wl - ws) << 20 | wgood << 28 ; wstride = rmq_wstride(P)
+  // range-max-table kernel (roi_pool_rmq.cuh), channel independent
+  uint32_t* bdesc;   // [R * PH * PW]  one word per output bin
+  float* rscale;     // [R]            row scale (1 when the caller passes none)
+  int* slow_count;   // [1]            number of bins without a fast descriptor
+  int* slow_list;    // [R * PH * PW]  their ids (r * PH*PW + bin), in no particular order
 };
 
-// descriptor of one axis range [s, e): level q = floor(log2(len)) capped at 3, start of the last
-// window l = e - 2^q.  x/y = byte offsets of the two windows inside table slot q*slot_mult
-// (cell stride `mult`); `good` = 4-bit mask, 0 when the range is empty or two windows of the level
-// do not cover it: for the h axis the set of w levels stored next to q (|qh - qw| <= 1), for the
-// w axis the single bit 1 << q -- a bin takes the fast path iff hgood & wgood != 0.
-__device__ __forceinline__ void rmq_axis_desc(uint32_t packed, int mult, int slot_mult, int hw, bool h_axis,
-                                              uint32_t& x, uint32_t& y, uint32_t& good) {
-  const int s = range_lo(packed), e = range_hi(packed);
-  const int len = e - s;
-  x = y = good = 0;
-  if (len <= 0) return;
-  const int q = min(3, 31 - __clz(len));
-  if (len > (2 << q)) return;
-  const int base = q * slot_mult * hw;
-  x = 2u * (uint32_t)(s * mult + base);
-  y = 2u * (uint32_t)((e - (1 << q)) * mult + base);
-  good = h_axis ? ((0x7u << q) >> 1) & 0xFu : 1u << q;
+// Per-bin descriptor of the range-max-table kernel.  Table (kh, kw) sits in slot kh + 2*kw of the
+// table block, so the 4 look-ups of a bin are base, base + db, base + dh, base + dh + db (bytes):
+//   bits  0..17  base = 2 * (hs*W + ws + slot*hw)        (plane + tables <= 227 KB -> < 2^18)
+//   bits 18..21  hl - hs   (dh = 2 * W * that)
+//   bits 22..26  db = 2 * (wl - ws)
+//   bit  31      fast path; 0 = empty bin or a shape the stored levels do not cover with 2 x 2
+//                windows (the kernel then re-derives the ranges from hbins / wbins)
+__device__ __forceinline__ bool rmq_axis(uint32_t packed, int& s, int& last, int& q) {
+  s = range_lo(packed);
+  const int len = range_hi(packed) - s;
+  if (len <= 0) return false;
+  q = min(3, 31 - __clz(len));
+  last = range_hi(packed) - (1 << q);
+  return len <= (2 << q);
 }
-
-// words per RoI in wdesc: PW rounded up to a multiple of 4 so a row loads as 128-bit words
-__host__ __device__ inline int rmq_wstride(int pooled_w) { return (pooled_w + 3) & ~3; }
+__device__ __forceinline__ uint32_t rmq_bin_desc(uint32_t hb, uint32_t wb, int W, int hw) {
+  int hs = 0, hl = 0, qh = 0, wst = 0, wl = 0, qw = 0;
+  const bool okh = rmq_axis(hb, hs, hl, qh), okw = rmq_axis(wb, wst, wl, qw);
+  if (!(okh && okw && abs(qh - qw) <= 1)) return 0u;
+  return 0x80000000u | (2u * (uint32_t)(hs * W + wst + (qh + 2 * qw) * hw)) | ((uint32_t)(hl - hs) << 18) |
+         ((2u * (uint32_t)(wl - wst)) << 22);
+}
 
 inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w, int sets) {
   size_t b = 0;
@@ -82,8 +85,8 @@ inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int po
   b += align_up((size_t)sets * num_rois * pooled_w * 4, 256);
   b += align_up((size_t)num_rois * 4, 256);
   b += align_up((size_t)batch * 4 * 2 + 16, 256);
-  b += align_up((size_t)num_rois * pooled_h * 16, 256);
-  b += align_up((size_t)num_rois * rmq_wstride(pooled_w) * 4, 256);
+  b += 2 * align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
+  b += align_up((size_t)num_rois * 4, 256);
   return b + 256;
 }
 
@@ -96,9 +99,11 @@ inline PoolWorkspace carve_pool_workspace(void* ws, int batch, int num_rois, int
   w.first = (int*)p;
   w.neg_last = w.first + batch;
   w.ungrouped = w.neg_last + batch;
+  w.slow_count = w.ungrouped + 1;
   p += align_up((size_t)batch * 4 * 2 + 16, 256);
-  w.hdesc = (uint4*)p; p += align_up((size_t)num_rois * pooled_h * 16, 256);
-  w.wdesc = (uint32_t*)p;
+  w.bdesc = (uint32_t*)p; p += align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
+  w.rscale = (float*)p; p += align_up((size_t)num_rois * 4, 256);
+  w.slow_list = (int*)p;
   return w;
 }
 

@@ -23,43 +23,41 @@ namespace jtsm {
 // ---------------------------------------------------------------------------
 // prep: bin tables + per-image RoI index range
 // ---------------------------------------------------------------------------
-__global__ void roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch,
-                                     int height, int width, float scale, int PH, int PW,
-                                     const float* __restrict__ row_scale, int want_desc,
-                                     PoolWorkspace ws) {
-  const int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= num_rois) return;
-  const float* q = rois + (size_t)r * 5;
-  const int b = (int)q[0];
-  const RoiRect rc = roi_rect(q[1], q[2], q[3], q[4], scale);
-  const int roi_w = max(rc.ew - rc.sw + 1, 1);
-  const int roi_h = max(rc.eh - rc.sh + 1, 1);
-  for (int p = 0; p < PH; ++p) ws.hbins[(size_t)r * PH + p] = bin_range(p, rc.sh, roi_h, PH, height);
-  for (int p = 0; p < PW; ++p) ws.wbins[(size_t)r * PW + p] = bin_range(p, rc.sw, roi_w, PW, width);
-  const bool ok = (b >= 0 && b < batch);
-  ws.batch_idx[r] = ok ? b : -1;
-  if (r > 0 && (int)rois[(size_t)(r - 1) * 5] > b) *ws.ungrouped = 1;
-  if (want_desc) {  // descriptors of the range-max-table kernel (plane size < 65535 checked by the caller)
-    const float rs = row_scale ? row_scale[r] : 1.f;
-    const int hw = height * width;
-    for (int p = 0; p < PH; ++p) {
-      uint4 d;
-      uint32_t good;
-      rmq_axis_desc(ws.hbins[(size_t)r * PH + p], width, 1, hw, true, d.x, d.y, good);
-      d.z = __float_as_uint(rs);
-      d.w = (good << 28) | ((uint32_t)(ok ? b : -1) & 0xFFFFFFu);
-      ws.hdesc[(size_t)r * PH + p] = d;
-    }
-    const int wstride = rmq_wstride(PW);
-    for (int p = 0; p < wstride; ++p) {
-      uint32_t x = 0, y = 0, good = 0;
-      if (p < PW) rmq_axis_desc(ws.wbins[(size_t)r * PW + p], 1, 2, hw, false, x, y, good);
-      ws.wdesc[(size_t)r * wstride + p] = x | ((y - x) << 20) | (good << 28);  // x < 2^20, y - x <= 16
+// One CTA per kPrepRois RoIs: the first kPrepRois threads compute the bin-edge tables of one RoI each,
+// then all threads turn them into the per-bin descriptors of the range-max-table kernel.
+constexpr int kPrepRois = 32, kPrepThreads = 256;
+__global__ void __launch_bounds__(kPrepThreads)
+roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, int height, int width, float scale,
+                     int PH, int PW, const float* __restrict__ row_scale, int want_desc, PoolWorkspace ws) {
+  const int r_base = blockIdx.x * kPrepRois;
+  const int r = r_base + threadIdx.x;
+  if (threadIdx.x < kPrepRois && r < num_rois) {
+    const float* q = rois + (size_t)r * 5;
+    const int b = (int)q[0];
+    const RoiRect rc = roi_rect(q[1], q[2], q[3], q[4], scale);
+    const int roi_w = max(rc.ew - rc.sw + 1, 1);
+    const int roi_h = max(rc.eh - rc.sh + 1, 1);
+    for (int p = 0; p < PH; ++p) ws.hbins[(size_t)r * PH + p] = bin_range(p, rc.sh, roi_h, PH, height);
+    for (int p = 0; p < PW; ++p) ws.wbins[(size_t)r * PW + p] = bin_range(p, rc.sw, roi_w, PW, width);
+    const bool ok = (b >= 0 && b < batch);
+    ws.batch_idx[r] = ok ? b : -1;
+    if (r > 0 && (int)rois[(size_t)(r - 1) * 5] > b) *ws.ungrouped = 1;
+    if (want_desc) ws.rscale[r] = row_scale ? row_scale[r] : 1.f;
+    if (ok) {
+      atomicMin(ws.first + b, r);
+      atomicMin(ws.neg_last + b, -r);
     }
   }
-  if (ok) {
-    atomicMin(ws.first + b, r);
-    atomicMin(ws.neg_last + b, -r);
+  if (!want_desc) return;  // uniform
+  __syncthreads();         // the CTA's bin tables are visible to all its threads
+  const int hw = height * width, PP = PH * PW;
+  const int n_local = min(kPrepRois, num_rois - r_base);
+  for (int j = threadIdx.x; j < n_local * PP; j += kPrepThreads) {
+    const int rl = j / PP, bin = j - rl * PP, ph = bin / PW, pw = bin - ph * PW;
+    const int rr = r_base + rl;
+    const uint32_t d = rmq_bin_desc(ws.hbins[(size_t)rr * PH + ph], ws.wbins[(size_t)rr * PW + pw], width, hw);
+    ws.bdesc[(size_t)rr * PP + bin] = d;
+    if (d == 0u) ws.slow_list[atomicAdd(ws.slow_count, 1)] = rr * PP + bin;  // ~2% of the bins
   }
 }
 
@@ -316,6 +314,15 @@ namespace {
 constexpr int kFwdThreads = 256;
 constexpr size_t kMaxPlaneSmem = 200 * 1024;
 
+// The range-max-table kernel applies when plane + tables fit in shared memory (hw <= 9685, which also
+// keeps every descriptor field inside its bits), the batch index fits 11 bits and output offsets 32 bits.
+bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
+  const long long hw = (long long)height * width;
+  const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
+  return (algo == 0 || algo == 3) && !tuning("roi_pool_force_gmem", 0) && hw < 65535 &&
+         rmq_smem_bytes((int)hw) <= 227 * 1024 && (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL;
+}
+
 int pick_splits(int planes, int num_rois, int ctas_per_sm) {
   // enough CTAs for ~4 waves, but keep >= 64 RoIs per CTA so the plane load amortises
   const int forced = tuning("roi_pool_splits", 0);
@@ -336,8 +343,8 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
   // 1) range-max-table kernel: plane + 10 index tables in shared memory, persistent CTAs
   const int hw = height * width;
   const size_t rmq_smem = rmq_smem_bytes(hw);
-  const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
-  if ((algo == 0 || algo == 3) && hw < 65535 && rmq_smem <= 227 * 1024 && !tuning("roi_pool_force_gmem", 0)) {
+  const int algo = tuning("roi_pool_fwd_algo", 0);
+  if (rmq_eligible(batch, channels, height, width, num_rois, PH, PW)) {
     const size_t smem = rmq_smem;
     static bool rmq_attr = false;
     if (!rmq_attr) {
@@ -383,13 +390,13 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
   return cuda_status();
 }
 
-int run_prep(const float* rois, int num_rois, int batch, int height, int width, float scale, int PH,
-             int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st) {
+int run_prep(const float* rois, int num_rois, int batch, int channels, int height, int width, float scale,
+             int PH, int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st) {
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
-  cudaMemsetAsync(ws.ungrouped, 0, sizeof(int), st);
-  const int want_desc = (long long)height * width < 65535;
-  roi_pool_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width,
-                                                              scale, PH, PW, row_scale, want_desc, ws);
+  cudaMemsetAsync(ws.ungrouped, 0, 2 * sizeof(int), st);  // ungrouped flag + slow-bin counter
+  const int want_desc = rmq_eligible(batch, channels, height, width, num_rois, PH, PW);
+  roi_pool_prep_kernel<<<(num_rois + kPrepRois - 1) / kPrepRois, kPrepThreads, 0, st>>>(
+      rois, num_rois, batch, height, width, scale, PH, PW, row_scale, want_desc, ws);
   count_launch();
   return cuda_status();
 }
@@ -419,7 +426,8 @@ extern "C" int jtsm_roi_pool_forward(const void* input, const float* rois, int d
     return JTSM_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 1);
-  int rc = run_prep(rois, num_rois, batch, height, width, spatial_scale, pooled_h, pooled_w, row_scale, ws, st);
+  int rc = run_prep(rois, num_rois, batch, channels, height, width, spatial_scale, pooled_h, pooled_w, row_scale,
+                    ws, st);
   if (rc != JTSM_OK) return rc;
   JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
                         rc = launch_roi_pool_fwd<T, A>(input, batch, channels, height, width,

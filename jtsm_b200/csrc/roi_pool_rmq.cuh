@@ -12,17 +12,19 @@
 // covered by 2 x 2 overlapping windows of the level floor(log2(len)); the answer is the best of
 // the 4 candidates (value desc, then index asc).  Only levels with |kh - kw| <= 1 are stored
 // (10 tables incl. identity, 24 B per cell in total with the fp32 plane -> 180 KB at 75x100);
-// more elongated bins use the nearest stored level and a few more windows.
+// more elongated (or empty, or > 16-cell) bins -- ~2% -- go through a list the prep kernel makes
+// and a slow path after the main loop, so no warp of the main loop diverges.
 //
-// Table (kh, kw) lives in slot kh + 2 * kw, so the byte address of a look-up is the SUM of a
-// per-(RoI, ph) part 2*(h*W + kh*hw) and a per-(RoI, pw) part 2*(w + 2*kw*hw): the prep kernel
-// stores both parts (the w part packed in one word), and whether the pair of levels is a stored one is a single AND of two masks.
+// Everything channel independent about a bin -- the byte offset of its first look-up, the two
+// window strides and whether it is a fast bin -- is one 32-bit descriptor written by the prep
+// kernel (roi_bins.cuh) and read with one coalesced load, one round ahead; the look-up chain of
+// the main loop is branch free and indexes only with 32-bit offsets from the kernel arguments.
 //
 // One persistent CTA per SM walks a contiguous range of (plane, RoI-chunk) items, rebuilding the
 // tables only when the plane changes (~3.5 builds per CTA at config 2); one thread per bin, lanes
-// along consecutive bins of a RoI.  (A one-thread-per-output-row variant with staged write-out
-// needed 2.5x fewer instructions but 25% more shared-memory wavefronts -- lanes on different rows
-// collide on banks -- and measured 418 us vs 362 us, so it is not kept: profiles/r1f.)
+// along consecutive bins of a RoI.  The variants tried and dropped (thread per output row with
+// staged write-out, 16-byte per-bin descriptors, two bins per thread) and what each measured are
+// in profiles/r1f_roi_pool_fwd_experiments.md.
 #pragma once
 #include "roi_bins.cuh"
 
@@ -31,7 +33,6 @@ namespace jtsm {
 constexpr int kRmqThreads = 1024;
 constexpr int kRmqTables = 10;   // slot = kh + 2*kw for |kh-kw| <= 1, kh,kw in 0..3; slot 0 = identity
 constexpr int kRmqMaxLevel = 3;  // windows of 1,2,4,8 cells per axis
-constexpr unsigned kRmqGoodMask = 0xF0000000u;
 
 __host__ __device__ inline size_t rmq_smem_bytes(int hw) {
   return (size_t)hw * 4 + (size_t)kRmqTables * hw * 2 + 16;
@@ -53,51 +54,47 @@ __device__ __forceinline__ RmqCand rmq_best(const RmqCand a, const RmqCand b) {
   return take_b ? b : a;
 }
 
-template <bool kVertical>
+// One doubling step: dst[p] = better of src[p] and src[p + off].  No bounds logic: a partner past
+// the end of the plane is clamped to the last cell, and an entry whose window would leave its row
+// or the plane is simply never queried -- every query window lies inside its bin (and every valid
+// entry is built from two valid halves), so only entries of in-plane windows have to be right.
 __device__ __forceinline__ void rmq_build_level(const float* plane, const unsigned short* src,
-                                                unsigned short* dst, int hw, int W, unsigned magic_w, int half) {
+                                                unsigned short* dst, int hw, int off) {
+  const int last = hw - 1;
+#pragma unroll 4
   for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
     const unsigned a = src[p];
-    unsigned r = a;
-    bool has;
-    if (kVertical) {
-      has = p + half * W < hw;
-    } else {
-      const int w = p - fast_div(p, magic_w) * W;
-      has = w + half < W;
-    }
-    if (has) {
-      const unsigned b = src[p + (kVertical ? half * W : half)];
-      if (b != a) r = rmq_best(rmq_load(plane, a), rmq_load(plane, b)).i;
-    }
-    dst[p] = (unsigned short)r;
+    const unsigned b = src[min(p + off, last)];
+    const float va = plane[a], vb = plane[b];
+    const bool take_b = (vb > va) || (vb == va && b < a);
+    dst[p] = (unsigned short)(take_b ? b : a);
   }
 }
 
 // plane (fp32) + the 10 tables of one (image, channel) plane; all threads of the CTA call it.
 template <typename T>
 __device__ __forceinline__ void rmq_build_plane(const T* __restrict__ src, float* plane, unsigned short* tabs,
-                                                int hw, int W, unsigned magic_w) {
+                                                int hw, int W) {
 #define TAB(s) (tabs + (size_t)(s) * hw)
   for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
     plane[p] = Elem<T>::to_f(src[p]);
     TAB(0)[p] = (unsigned short)p;  // identity level (0,0)
   }
   __syncthreads();
-  rmq_build_level<false>(plane, TAB(0), TAB(2), hw, W, magic_w, 1);  // (0,1)
-  rmq_build_level<true>(plane, TAB(0), TAB(1), hw, W, magic_w, 1);   // (1,0)
+  rmq_build_level(plane, TAB(0), TAB(2), hw, 1);      // (0,1)
+  rmq_build_level(plane, TAB(0), TAB(1), hw, W);      // (1,0)
   __syncthreads();
-  rmq_build_level<true>(plane, TAB(2), TAB(3), hw, W, magic_w, 1);   // (1,1)
+  rmq_build_level(plane, TAB(2), TAB(3), hw, W);      // (1,1)
   __syncthreads();
-  rmq_build_level<false>(plane, TAB(3), TAB(5), hw, W, magic_w, 2);  // (1,2)
-  rmq_build_level<true>(plane, TAB(3), TAB(4), hw, W, magic_w, 2);   // (2,1)
+  rmq_build_level(plane, TAB(3), TAB(5), hw, 2);      // (1,2)
+  rmq_build_level(plane, TAB(3), TAB(4), hw, 2 * W);  // (2,1)
   __syncthreads();
-  rmq_build_level<true>(plane, TAB(5), TAB(6), hw, W, magic_w, 2);   // (2,2)
+  rmq_build_level(plane, TAB(5), TAB(6), hw, 2 * W);  // (2,2)
   __syncthreads();
-  rmq_build_level<false>(plane, TAB(6), TAB(8), hw, W, magic_w, 4);  // (2,3)
-  rmq_build_level<true>(plane, TAB(6), TAB(7), hw, W, magic_w, 4);   // (3,2)
+  rmq_build_level(plane, TAB(6), TAB(8), hw, 4);      // (2,3)
+  rmq_build_level(plane, TAB(6), TAB(7), hw, 4 * W);  // (3,2)
   __syncthreads();
-  rmq_build_level<true>(plane, TAB(8), TAB(9), hw, W, magic_w, 4);   // (3,3)
+  rmq_build_level(plane, TAB(8), TAB(9), hw, 4 * W);  // (3,3)
   __syncthreads();
 #undef TAB
 }
@@ -128,14 +125,14 @@ __device__ __noinline__ RmqCand rmq_query_slow(const float* plane, const unsigne
   return best;
 }
 
-// 2 x 2 windows of a stored level: byte offsets a0/a1 (h part) + b0, b0 + db (w part) into the tables.
-__device__ __forceinline__ RmqCand rmq_query_fast(const float* plane, const unsigned short* tabs, unsigned a0,
-                                                  unsigned a1, unsigned b0, unsigned db) {
-  const char* tb = (const char*)tabs;
-  const unsigned ia = *(const unsigned short*)(tb + (a0 + b0));
-  const unsigned ib = *(const unsigned short*)(tb + (a0 + b0 + db));
-  const unsigned ic = *(const unsigned short*)(tb + (a1 + b0));
-  const unsigned id = *(const unsigned short*)(tb + (a1 + b0 + db));
+// 2 x 2 windows of a stored level: byte offsets base, +db, +dh, +dh+db into the table block.
+__device__ __forceinline__ RmqCand rmq_query_fast(const float* plane, const unsigned short* tabs, unsigned base,
+                                                  unsigned dh, unsigned db) {
+  const char* tb = (const char*)tabs + base;
+  const unsigned ia = *(const unsigned short*)(tb);
+  const unsigned ib = *(const unsigned short*)(tb + db);
+  const unsigned ic = *(const unsigned short*)(tb + dh);
+  const unsigned id = *(const unsigned short*)(tb + dh + db);
   return rmq_best(rmq_best(rmq_load(plane, ia), rmq_load(plane, ib)),
                   rmq_best(rmq_load(plane, ic), rmq_load(plane, id)));
 }
@@ -171,12 +168,14 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
   const int hw = H * W;
   float* plane = (float*)smem_raw;
   unsigned short* tabs = (unsigned short*)(plane + hw);
-  const unsigned magic_w = (unsigned)((0x100000000ull + W - 1) / W);
-  const unsigned magic_pw = (unsigned)((0x100000000ull + PW - 1) / PW);
-  const int PP = PH * PW, wstride = rmq_wstride(PW);
-  const int step_r = kRmqThreads / PP, step_b = kRmqThreads - step_r * PP;
-  const int rl_init = threadIdx.x / PP, bin_init = threadIdx.x - rl_init * PP;
+  const int PP = PH * PW, cpp = channels * PP;
+  const unsigned w2 = 2u * (unsigned)W;
   const bool ungrouped = *ws.ungrouped != 0;
+  // (RoI, bin) of this thread's output and the step of one round (kRmqThreads outputs); the output
+  // offset rl * cpp + bin is stepped along with them
+  const int step_r = kRmqThreads / PP, step_b = kRmqThreads - step_r * PP;
+  const int step_o = step_r * cpp + step_b, wrap_o = cpp - PP;
+  const int rl_init = threadIdx.x / PP, bin_init = threadIdx.x - rl_init * PP;
 
   // contiguous item range of this CTA
   const int per = num_items / gridDim.x, rem = num_items % gridDim.x;
@@ -190,37 +189,54 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
     if (nc != cur_plane) {
       __syncthreads();  // previous item's queries are done with the old tables
       cur_plane = nc;
-      rmq_build_plane(input + (size_t)nc * hw, plane, tabs, hw, W, magic_w);
+      rmq_build_plane(input + (size_t)nc * hw, plane, tabs, hw, W);
     }
-    const size_t cpp = (size_t)channels * PP;
-    T* out_c = output + (size_t)it.c * PP;
-    A* arg_c = argmax + (size_t)it.c * PP;
-    const unsigned nkey = (unsigned)it.n & 0xFFFFFFu;
-    int rl = rl_init, bin = bin_init;
-    while (rl < it.nr) {
-      const int r = it.r0 + rl;
-      const int ph = fast_div(bin, magic_pw);
-      const int pw = bin - ph * PW;
-      const uint4 hd = __ldg(ws.hdesc + (size_t)r * PH + ph);
-      const unsigned wd = __ldg(ws.wdesc + (size_t)r * wstride + pw);
-      const size_t o = (size_t)r * cpp + bin;
-      // advance (r, bin) by kRmqThreads outputs without a division
+    // All indices are 32-bit offsets from the kernel's own pointer arguments (the launcher checks the
+    // sizes), so the loop carries five integers and no 64-bit pointers.
+    unsigned i = (unsigned)(it.r0 * PP) + threadIdx.x;           // bin id
+    const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
+    unsigned r = (unsigned)(it.r0 + rl_init);                    // RoI of bin i
+    int bin = bin_init;                                          // i - r * PP
+    unsigned o = (r * (unsigned)channels + (unsigned)it.c) * (unsigned)PP + (unsigned)bin;  // output element
+    // descriptor and row scale are loaded one round ahead (they come from L2: little L1 is left next to
+    // 180+ KB of shared memory), so their latency hides behind the look-ups of the current round
+    unsigned xn = 0u;
+    float scn = 0.f;
+    if (i < i_end) xn = __ldg(ws.bdesc + i), scn = __ldg(ws.rscale + r);
+    while (i < i_end) {
+      const unsigned x = xn;  // x = 0: slow bin, left to the list below (the look-ups then run on offset 0)
+      const float sc = scn;
+      bool act = (int)x < 0;
+      if (ungrouped && act) act = __ldg(ws.batch_idx + r) == it.n;
+      const unsigned o_cur = o;
+      i += kRmqThreads;
       bin += step_b;
-      rl += step_r;
-      if (bin >= PP) {
-        bin -= PP;
-        ++rl;
+      r += step_r;
+      o += step_o;
+      if (bin >= PP) bin -= PP, ++r, o += wrap_o;
+      if (i < i_end) xn = __ldg(ws.bdesc + i), scn = __ldg(ws.rscale + r);
+      const RmqCand best = rmq_query_fast(plane, tabs, x & 0x3FFFFu, ((x >> 18) & 15u) * w2, (x >> 22) & 31u);
+      const float v = __fmul_rn(best.v, sc);
+      if (act) {
+        output[o_cur] = Elem<T>::from_f(v);
+        argmax[o_cur] = Arg<A>::enc((int)best.i);
       }
-      if (ungrouped && (hd.w & 0xFFFFFFu) != nkey) continue;
-      RmqCand best;
-      if (hd.w & wd & kRmqGoodMask) {
-        best = rmq_query_fast(plane, tabs, hd.x, hd.y, wd & 0xFFFFFu, (wd >> 20) & 0x1Fu);
-      } else {
-        best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)r * PH + ph),
-                              __ldg(ws.wbins + (size_t)r * PW + pw));
-      }
-      out_c[o] = Elem<T>::from_f(__fmul_rn(best.v, __uint_as_float(hd.z)));
-      arg_c[o] = Arg<A>::enc((int)best.i);
+    }
+    // the few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%), listed by the prep
+    // kernel so that no warp of the main loop diverges into the long path; the list is short, every
+    // item filters it for its own RoI range
+    const int ns = __ldg(ws.slow_count);
+    for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
+      const int id = __ldg(ws.slow_list + j);
+      const int rr = id / PP, b = id - rr * PP;
+      if (rr < it.r0 || rr >= it.r0 + it.nr) continue;
+      if (ungrouped && __ldg(ws.batch_idx + rr) != it.n) continue;
+      const int ph = b / PW, pw = b - ph * PW;
+      const RmqCand best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)rr * PH + ph),
+                                          __ldg(ws.wbins + (size_t)rr * PW + pw));
+      const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)it.c) * (unsigned)PP + (unsigned)b;
+      output[so] = Elem<T>::from_f(__fmul_rn(best.v, __ldg(ws.rscale + rr)));
+      argmax[so] = Arg<A>::enc((int)best.i);
     }
   }
 }

@@ -66,10 +66,18 @@ class HotPathStep:
         return st + ["roi_pool_bwd"]
 
     def dominant_kernel(self):
-        return "roi_pool_fwd_kernel"
+        return "roi_pool_fwd_rmq_kernel"
 
-    def ncu_traffic(self):
-        return None
+    def ncu_traffic(self, name=None):
+        """DRAM bytes per launch of the dominant kernel from the committed ncu capture of this
+        configuration (profiles/traffic.json), or None when there is none."""
+        import json
+        import os
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
+        if name is None or not os.path.exists(path):
+            return None
+        rec = json.load(open(path)).get(name)
+        return rec["dram_bytes_per_launch"] if rec else None
 
     # ------------------------------------------------------------------ the step
     def run(self, d, time_dominant=False):
