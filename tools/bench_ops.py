@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--tv", action="store_true")
     ap.add_argument("--tune", nargs="*", default=[])
     ap.add_argument("--dtype", default="fp32")
+    ap.add_argument("--ops", default="pool", help="pool | all")
     a = ap.parse_args()
     for kv in a.tune:
         k, v = kv.split("=")
@@ -66,6 +67,30 @@ def main():
         o = torchvision.ops.roi_pool(xg, rois_d, P, cfg["scale"])
         med, _ = timeit(lambda: torch.autograd.grad(o, xg, g, retain_graph=True), a.iters, flush)
         res["tv_roi_pool_bwd_us"] = med
+    if a.ops == "all":
+        n, c, h, w = x.shape
+        ph = pw = cfg["P"]
+        for sr in (2, 0):
+            med, _ = timeit(lambda: ops.roi_align_forward(x, rois_d, cfg["scale"], ph, pw, sr, True), a.iters, flush)
+            res["roi_align_fwd_sr%d_us" % sr] = med
+            med, _ = timeit(lambda: ops.roi_align_backward(g, rois_d, cfg["scale"], ph, pw, n, c, h, w, sr, True), a.iters, flush)
+            res["roi_align_bwd_sr%d_us" % sr] = med
+            if a.tv:
+                import torchvision
+                med, _ = timeit(lambda: torchvision.ops.roi_align(x, rois_d, P, cfg["scale"], sr, True), a.iters, flush)
+                res["tv_roi_align_fwd_sr%d_us" % sr] = med
+                xg = x.clone().requires_grad_()
+                o = torchvision.ops.roi_align(xg, rois_d, P, cfg["scale"], sr, True)
+                med, _ = timeit(lambda: torch.autograd.grad(o, xg, g, retain_graph=True), a.iters, flush)
+                res["tv_roi_align_bwd_sr%d_us" % sr] = med
+        med, _ = timeit(lambda: ops.roi_loop_pool_forward(x, rois_d, cfg["scale"], ph, pw), a.iters, flush)
+        res["roi_loop_pool_fwd_us"] = med
+        gen = torch.Generator().manual_seed(5)
+        sp, S = synth.superpixels(gen, n, cfg["img_h"], cfg["img_w"])
+        oh = synth.oh_labels(gen, rois.shape[0], S)
+        sp_d, oh_d = sp.to(dev), oh.to(dev)
+        med, _ = timeit(lambda: ops.moi_pool_forward(x, rois_d, cfg["scale"], ph, pw, oh_d, sp_d), a.iters, flush)
+        res["moi_pool_fwd_us"] = med
     print(json.dumps(res))
 
 
