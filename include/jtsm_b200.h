@@ -215,6 +215,18 @@ JTSM_API int jtsm_refine_assign(
     float* pgt_weights, long long* matched_idx, float* matched_iou, long long* gt_classes,
     float* gt_weights, float* gt_scores, float* gt_boxes, float* loss_weights, int* counters,
     void* stream);
+/* label_and_sample_proposals with caller-supplied pseudo-gt seeds (roi_heads.py:263-370) -- the second half of
+ * jtsm_refine_assign for seed sets it does not build itself: get_pgt_mist (roi_heads_oicr.py:549-591: top 15% per
+ * class + class-agnostic NMS), thresholded / top-k > 1 get_pgt_top_k, or annotated boxes.
+ * pgt_* [total seeds] DEVICE, seeds of image n at [seed_offsets[n], seed_offsets[n+1]) (int32 DEVICE);
+ * max_seeds_per_image bounds the shared-memory staging (<= 6400).  Outputs as jtsm_refine_assign. */
+JTSM_API int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_classes, const float* pgt_scores,
+                               const float* pgt_weights, const int* seed_offsets, int max_seeds_per_image,
+                               const float* proposals, const int* seg_offsets, int num_images, int num_rois,
+                               int num_classes, float iou_t0, float iou_t1, int label0, int label1, int label2,
+                               int num_thresholds, long long* matched_idx, float* matched_iou,
+                               long long* gt_classes, float* gt_weights, float* gt_scores, float* gt_boxes,
+                               float* loss_weights, int* counters, void* stream);
 JTSM_API size_t jtsm_refine_workspace_bytes(void);
 /* Weighted softmax cross-entropy, forward + backward + probabilities in one launch
  * (OICROutputs.softmax_cross_entropy_loss + _log_accuracy, fast_rcnn_oicr.py:252-298; predict_probs :744-762):

@@ -73,8 +73,19 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
   const bool has_gt = (G > 0) && (r1 > r0);  // top_k = min(num_pred, 1)
+  const bool given = prev_scores == nullptr;  // seeds supplied by the caller (jtsm_refine_match)
+  if (given) {
+    for (int g = threadIdx.x; g < G; g += kAssignThreads) {
+      const float4 b = *(const float4*)(pgt_boxes + (size_t)(g0 + g) * 4);
+      seeds[g] = b;
+      s_area[g] = box_area(b.x, b.y, b.z, b.w);
+      s_weight[g] = pgt_weights[g0 + g];
+      s_score[g] = pgt_scores[g0 + g];
+      s_cls[g] = (int)pgt_classes[g0 + g];
+    }
+  }
 
-  for (int g = 0; g < G && has_gt; ++g) {
+  for (int g = 0; g < G && has_gt && !given; ++g) {
     const int cls = (int)cls_ids[g0 + g];
     float bv = -INFINITY;
     int bi = 0x7fffffff;
@@ -504,6 +515,39 @@ extern "C" int jtsm_refine_assign(
       img_cls_offsets, img_cls_ids, img_scores, mp, pgt_boxes, pgt_classes, pgt_scores, pgt_weights,
       matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes, loss_weights, counters,
       num_images);
+  count_launch();
+  return cuda_status();
+}
+
+extern "C" int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_classes, const float* pgt_scores,
+                                 const float* pgt_weights, const int* seed_offsets, int max_seeds_per_image,
+                                 const float* proposals, const int* seg_offsets, int num_images, int num_rois,
+                                 int num_classes, float iou_t0, float iou_t1, int label0, int label1, int label2,
+                                 int num_thresholds, long long* matched_idx, float* matched_iou,
+                                 long long* gt_classes, float* gt_weights, float* gt_scores, float* gt_boxes,
+                                 float* loss_weights, int* counters, void* stream) {
+  if (num_images < 0 || num_rois < 0 || num_classes <= 0 || num_thresholds < 1 || num_thresholds > 2 ||
+      max_seeds_per_image < 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (!counters) return JTSM_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(counters, 0, ((size_t)num_images * 3 + 1) * sizeof(int), st);
+  if (num_images == 0) return JTSM_OK;
+  if (!seg_offsets || !seed_offsets || !matched_idx || !gt_classes || !gt_weights || !gt_scores || !gt_boxes ||
+      !loss_weights)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (max_seeds_per_image > 0 && (!pgt_boxes || !pgt_classes || !pgt_scores || !pgt_weights))
+    return JTSM_ERR_INVALID_ARGUMENT;
+  const size_t smem = (size_t)max_seeds_per_image * (16 + 4 * 4) + 16;
+  if (smem > 200 * 1024) return JTSM_ERR_UNSUPPORTED;
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(refine_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  MatcherParams mp{iou_t0, iou_t1, label0, label1, label2, num_thresholds};
+  refine_assign_kernel<<<num_images, kAssignThreads, smem, st>>>(
+      nullptr, 0, nullptr, 1, proposals, seg_offsets, num_classes, seed_offsets, nullptr, nullptr, mp,
+      const_cast<float*>(pgt_boxes), const_cast<long long*>(pgt_classes), const_cast<float*>(pgt_scores),
+      const_cast<float*>(pgt_weights), matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes,
+      loss_weights, counters, num_images);
   count_launch();
   return cuda_status();
 }

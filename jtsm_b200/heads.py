@@ -50,3 +50,70 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposals, num_preds_per
         out["grad_cls"], out["grad_det"] = ops.wsddn_backward(fwd)
         out["grad_ref_logits"], out["grad_ref_deltas"] = grads_l, grads_d
     return out
+
+
+# --------------------------------------------------------------------------- pseudo-gt variants beyond top-1
+def get_pgt_top_k(prev_scores, prev_boxes, num_preds_per_image, gt_classes_img_int, img_scores, num_classes, top_k=1,
+                  thres=0.0):
+    """get_pgt_top_k for any top_k / thres (roi_heads_oicr.py:675-811) on device tensors.
+    prev_scores [R, K or K+1], prev_boxes [R,4] or [R,4K] (all images concatenated), img_scores [N,K].
+    -> (scores [G], boxes [G,4], classes [G] int64, weights [G], seeds_per_image list[int]); the top-1, thres = 0
+    case is fused into ops.refine_assign -- this is the general path (torch.topk + gathers, no host sync
+    unless thres > 0)."""
+    outs, counts = [], []
+    sc_split = prev_scores.split(num_preds_per_image, dim=0)
+    bx_split = prev_boxes.split(num_preds_per_image, dim=0)
+    for i, (ps, pb, gt_int) in enumerate(zip(sc_split, bx_split, gt_classes_img_int)):
+        n = ps.shape[0]
+        gt_int = gt_int.to(ps.device)
+        g = gt_int.numel()
+        if top_k >= 1:
+            k = min(n, int(top_k))
+        elif top_k > 0:
+            k = max(int(n * top_k), 1)
+        else:
+            k = min(n, 1)
+        if pb.numel() == n * 4:
+            pb = pb.view(n, 1, 4).expand(n, num_classes, 4)
+        pb = pb.reshape(n, num_classes, 4).index_select(1, gt_int)
+        sc, idx = torch.topk(ps.index_select(1, gt_int), k, dim=0)
+        bx = torch.gather(pb, 0, idx.unsqueeze(2).expand(k, g, 4))
+        cl = gt_int.unsqueeze(0).expand(k, g)
+        wt = img_scores[i:i + 1].index_select(1, gt_int).expand(k, g)
+        if thres > 0:
+            mask = sc.ge(thres)
+            mask[0:1, :] = True
+            sc, cl, wt, bx = sc[mask], cl[mask], wt[mask], bx[mask.unsqueeze(2).expand(k, g, 4)]
+        outs.append((sc.reshape(-1), bx.reshape(-1, 4), cl.reshape(-1), wt.reshape(-1)))
+        counts.append(int(outs[-1][0].numel()))
+    cat = [torch.cat([o[j] for o in outs]) for j in range(4)]
+    return cat[0], cat[1], cat[2], cat[3], counts
+
+
+def get_pgt_mist(prev_scores, prev_boxes, num_preds_per_image, gt_classes_img_int, img_scores, num_classes,
+                 top_pro=0.15, nms_thresh=0.2):
+    """get_pgt_mist (roi_heads_oicr.py:549-591): top `top_pro` per image class, then class-agnostic NMS per image
+    with the sm_100a NMS kernel.  gt_weights = seed scores, as the reference returns them (:579-581)."""
+    sc, bx, cl, _, counts = get_pgt_top_k(prev_scores, prev_boxes, num_preds_per_image, gt_classes_img_int, img_scores,
+                                          num_classes, top_k=top_pro)
+    keeps, kept = [], []
+    off = 0
+    for c in counts:  # one NMS per image; the keep count is the only host read (the reference indexes by keep too)
+        keep = ops.batched_nms(bx[off:off + c], sc[off:off + c], None, nms_thresh)
+        keeps.append(keep + off)
+        kept.append(int(keep.numel()))
+        off += c
+    keep = torch.cat(keeps) if keeps else torch.zeros(0, dtype=torch.int64, device=sc.device)
+    return sc[keep], bx[keep], cl[keep], sc[keep], kept
+
+
+def refine_labels_mist(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int, img_scores,
+                       num_classes, top_pro=0.15, iou_thresholds=(0.5,), iou_labels=(0, 1), want_iou=False):
+    """One refinement branch's targets with WSL.REFINE_MIST (roi_heads_oicr.py:418-427): mist seeds ->
+    label_and_sample_proposals.  Returns the ops.refine_match dict plus the seeds."""
+    sc, bx, cl, wt, kept = get_pgt_mist(prev_scores, prev_boxes, num_preds_per_image, gt_classes_img_int, img_scores,
+                                        num_classes, top_pro)
+    out = ops.refine_match(bx, cl, sc, wt, kept, proposals, num_preds_per_image, num_classes, iou_thresholds,
+                           iou_labels, want_iou)
+    out.update(pgt_scores=sc, pgt_boxes=bx, pgt_classes=cl, pgt_weights=wt, seeds_per_image=kept)
+    return out

@@ -259,6 +259,40 @@ def refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_cl
     return out
 
 
+def refine_match(pgt_boxes, pgt_classes, pgt_scores, pgt_weights, seeds_per_image, proposals, num_preds_per_image,
+                 num_classes, iou_thresholds=(0.5,), iou_labels=(0, 1), want_iou=False):
+    """label_and_sample_proposals for caller-supplied pseudo-gt seeds (roi_heads.py:263-370): seeds of all images
+    concatenated ([G,4], [G] int64, [G], [G]) with `seeds_per_image` counts (host ints).  Same outputs as
+    refine_assign (without the pgt_* it did not build)."""
+    _require_cuda(pgt_boxes, proposals)
+    P = _f32c(proposals)
+    dev = P.device
+    r, n = P.shape[0], len(num_preds_per_image)
+    assert len(seeds_per_image) == n
+    gb, gs, gw = _f32c(pgt_boxes).view(-1, 4), _f32c(pgt_scores).view(-1), _f32c(pgt_weights).view(-1)
+    gc = pgt_classes.to(torch.int64).contiguous().view(-1)
+    g_total = int(sum(seeds_per_image))
+    assert gb.shape[0] == g_total and gc.numel() == g_total and gs.numel() == g_total and gw.numel() == g_total
+    seg = segment_offsets(num_preds_per_image, dev)
+    soff = segment_offsets(seeds_per_image, dev)
+    thr, lab = list(iou_thresholds), list(iou_labels)
+    assert len(thr) in (1, 2) and len(lab) == len(thr) + 1
+    fl = torch.zeros(r * 8 + (r if want_iou else 0), dtype=torch.float32, device=dev)
+    il = torch.zeros(2 * r, dtype=torch.int64, device=dev)
+    out = dict(gt_boxes=fl[:4 * r].view(r, 4), gt_weights=fl[4 * r:5 * r], gt_scores=fl[5 * r:6 * r],
+               loss_weights=fl[6 * r:7 * r], matched_iou=fl[8 * r:9 * r] if want_iou else None,
+               matched_idx=il[:r], gt_classes=il[r:], counters=torch.empty(n * 3 + 1, dtype=torch.int32, device=dev))
+    with torch.cuda.device(dev):
+        check(lib().jtsm_refine_match(
+            _ptr(gb), _ptr(gc), _ptr(gs), _ptr(gw), _ptr(soff), max([0] + [int(v) for v in seeds_per_image]), _ptr(P),
+            _ptr(seg), n, r, num_classes, float(thr[0]), float(thr[1]) if len(thr) > 1 else 0.0, int(lab[0]), int(lab[1]),
+            int(lab[2]) if len(lab) > 2 else 0, len(thr), _ptr(out["matched_idx"]), _ptr(out["matched_iou"]),
+            _ptr(out["gt_classes"]), _ptr(out["gt_weights"]), _ptr(out["gt_scores"]), _ptr(out["gt_boxes"]),
+            _ptr(out["loss_weights"]), _ptr(out["counters"]), _stream()), "refine_match")
+    out["valid_count"] = out["counters"][n * 3:]
+    return out
+
+
 def refine_ce(logits, gt_classes, loss_weights, valid_count, grad_loss=None, loss_scale=1.0, want_probs=True,
               want_grad=True, want_acc=True):
     """Weighted CE fwd+bwd + softmax (fast_rcnn_oicr.py:282-298, 744-762) -> dict(loss, probs, grad_logits, acc)."""

@@ -120,6 +120,50 @@ def get_pgt_top1(prev_boxes, prev_scores, gt_classes_img_int, pred_class_img_log
     return out
 
 
+def get_pgt_top_k(prev_boxes, prev_scores, gt_classes_img_int, pred_class_img_logits, num_classes, top_k=1, thres=0.0):
+    """General get_pgt_top_k (roi_heads_oicr.py:675-811): top_k >= 1 -> min(R_i, int(top_k)); 0 < top_k < 1 ->
+    max(int(R_i * top_k), 1); seeds flattened k-major ([top_k, G] -> reshape(-1)); thres > 0 keeps row 0 and the
+    rows with score >= thres (:756-785).  -> per image (scores, boxes [.,4], classes int64, weights)."""
+    out = []
+    for i, (pb, ps, gt_int) in enumerate(zip(prev_boxes, prev_scores, gt_classes_img_int)):
+        n = pb.size(0)
+        if pb.numel() == n * 4:
+            pb = pb.unsqueeze(1).expand(n, num_classes, 4)
+        pb = pb.reshape(-1, num_classes, 4)
+        ps = torch.index_select(ps, 1, gt_int)
+        pb = torch.index_select(pb, 1, gt_int)
+        if top_k >= 1:
+            k = min(n, int(top_k))
+        elif top_k > 0:
+            k = max(int(n * top_k), 1)
+        else:
+            k = min(n, 1)
+        g = gt_int.numel()
+        sc, idx = torch.topk(ps, k, dim=0)
+        bx = torch.gather(pb, 0, idx.unsqueeze(2).expand(k, g, 4))
+        cl = gt_int.unsqueeze(0).expand(k, g)
+        wt = torch.index_select(pred_class_img_logits[i:i + 1], 1, gt_int).expand(k, g)
+        if thres > 0:
+            mask = sc.ge(thres)
+            mask = torch.cat([torch.full_like(mask[0:1, :], True), mask[1:, :]], dim=0)
+            sc, cl, wt = sc[mask], cl[mask], wt[mask]
+            bx = bx[mask.unsqueeze(2).expand(k, g, 4)]
+        out.append((sc.reshape(-1), bx.reshape(-1, 4), cl.reshape(-1), wt.reshape(-1)))
+    return out
+
+
+def get_pgt_mist(prev_boxes, prev_scores, gt_classes_img_int, pred_class_img_logits, num_classes, top_pro=0.15):
+    """roi_heads_oicr.py:549-591: top `top_pro` fraction per image class, class-agnostic NMS at 0.2 over all of an
+    image's candidates, keep order = descending score.  As in the reference (:579-581 zips pgt_scores twice) the
+    returned gt_weights ARE the seed scores."""
+    out = []
+    for sc, bx, cl, _ in get_pgt_top_k(prev_boxes, prev_scores, gt_classes_img_int, pred_class_img_logits, num_classes,
+                                       top_k=top_pro, thres=0.0):
+        keep = batched_nms(bx, sc, torch.zeros_like(cl), 0.2)
+        out.append((sc[keep], bx[keep], cl[keep], sc[keep]))
+    return out
+
+
 def label_proposals(pgt, proposal_boxes, num_classes, thresholds=(0.5,), labels=(0, 1)):
     """label_and_sample_proposals + _sample_proposals (no sub-sampling) for one image.
     roi_heads.py:222-254, 263-370.  -> dict(matched_idx, gt_classes, gt_boxes, gt_scores, gt_weights)."""

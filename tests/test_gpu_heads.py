@@ -214,3 +214,29 @@ def test_head_step_config2_vs_oracle(cuda):
     close(out["grad_cls"], ref["grad_cls"], "grad_cls", atol=1e-8)
     for a, b in zip(out["grad_ref_logits"], ref["grad_ref_logits"]):
         close(a, b, "grad_ref_logits", atol=1e-9)
+
+
+@pytest.mark.parametrize("counts,k,top_pro", [((2000,), 20, 0.15), ((700, 1, 1300), 12, 0.10), ((3,), 5, 0.15)])
+def test_mist_seeds_and_matching_bit_exact(cuda, counts, k, top_pro):
+    """WSL.REFINE_MIST targets (get_pgt_mist + label_and_sample_proposals) on the GPU vs the restatement:
+    seeds (top fraction per class, class-agnostic NMS 0.2) and every per-proposal label bit for bit."""
+    from jtsm_b200 import heads
+    from oracle import ref_heads
+
+    g = synth.generator(41)
+    boxes = [synth.proposals(g, c, 600, 800) for c in counts]
+    labels = synth.image_labels(g, len(counts), k)
+    r = sum(counts)
+    scores = torch.rand(r, k + 1, generator=g)
+    img = torch.rand(len(counts), k, generator=g)
+    allp = torch.cat(boxes)
+    want = ref_heads.get_pgt_mist(boxes, list(scores.split(list(counts))), labels, img, k, top_pro)
+    got = heads.refine_labels_mist(scores.to(cuda), allp.to(cuda), allp.to(cuda), list(counts), labels, img.to(cuda), k,
+                                   top_pro, want_iou=True)
+    assert got["seeds_per_image"] == [int(w[0].numel()) for w in want]
+    assert torch.equal(got["pgt_scores"].cpu(), torch.cat([w[0] for w in want]))
+    assert torch.equal(got["pgt_boxes"].cpu(), torch.cat([w[1] for w in want]))
+    assert torch.equal(got["pgt_classes"].cpu(), torch.cat([w[2] for w in want]))
+    labs = [ref_heads.label_proposals(w, b, k) for w, b in zip(want, boxes)]
+    for key in ("gt_classes", "gt_weights", "gt_scores", "gt_boxes", "matched_idx", "matched_iou"):
+        assert torch.equal(got[key].cpu(), torch.cat([l[key] for l in labs])), key

@@ -94,3 +94,44 @@ def test_box2box_round_trip_and_reference():
     assert torch.equal(d, t.get_deltas(src, dst))
     assert torch.equal(ref_heads.apply_deltas(d, src), t.apply_deltas(d, src))
     assert torch.allclose(ref_heads.apply_deltas(d, src), dst, atol=1e-3)
+
+
+@pytest.mark.parametrize("mode", ["top_k3", "top_frac_thres", "mist"])
+def test_pgt_variants_match_reference(mode):
+    """General get_pgt_top_k (top_k > 1, fractional top_k + thres) and get_pgt_mist of the restatement vs the
+    reference's own methods run in place (roi_heads_oicr.py:549-591, 675-811), then label_and_sample_proposals."""
+    from oracle import ref_drive  # noqa: F401  (installs the stubs)
+
+    g = synth.generator(31)
+    counts, K = (120, 90), 7
+    boxes = [synth.proposals(g, c, 600, 800) for c in counts]
+    labels = synth.image_labels(g, len(counts), K)
+    scores = torch.rand(sum(counts), K + 1, generator=g)
+    img = torch.rand(len(counts), K, generator=g)
+    m = ref_loader.install()
+    Boxes, Instances = m["boxes"].Boxes, m["instances"].Instances
+    proposals = []
+    for b in boxes:
+        inst = Instances((600, 800))
+        inst.proposal_boxes = Boxes(b.clone())
+        inst.objectness_logits = torch.zeros(b.shape[0])
+        proposals.append(inst)
+    self_, f = ref_loader.make_self(K, labels, img)
+    pb = [p.proposal_boxes for p in proposals]
+    if mode == "top_k3":
+        targets = f["get_pgt_top_k"](self_, pb, scores, proposals, top_k=3)
+        mine = ref_heads.get_pgt_top_k(boxes, list(scores.split(list(counts))), labels, img, K, top_k=3)
+    elif mode == "top_frac_thres":
+        targets = f["get_pgt_top_k"](self_, pb, scores, proposals, top_k=0.1, thres=0.9)
+        mine = ref_heads.get_pgt_top_k(boxes, list(scores.split(list(counts))), labels, img, K, top_k=0.1, thres=0.9)
+    else:
+        targets = f["get_pgt_mist"](self_, pb, scores, proposals)
+        mine = ref_heads.get_pgt_mist(boxes, list(scores.split(list(counts))), labels, img, K)
+    for t, (sc, bx, cl, wt) in zip(targets, mine):
+        assert torch.equal(t.gt_scores, sc) and torch.equal(t.gt_boxes.tensor, bx)
+        assert torch.equal(t.gt_classes, cl) and torch.equal(t.gt_weights, wt)
+    props = f["label_and_sample_proposals"](self_, proposals, targets)
+    for p, seeds, b in zip(props, mine, boxes):
+        lab = ref_heads.label_proposals(seeds, b, K)
+        assert torch.equal(p.gt_classes, lab["gt_classes"]) and torch.equal(p.gt_weights, lab["gt_weights"])
+        assert torch.equal(p.gt_boxes.tensor, lab["gt_boxes"])
