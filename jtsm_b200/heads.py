@@ -13,19 +13,25 @@ from . import ops
 def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposals, num_preds_per_image, gt_classes_img_int,
               num_classes, labels_onehot, mean_loss=True, reg=False, reg_weighted=True, iou_thresholds=(0.5,),
               iou_labels=(0, 1), need_grad=True, term_weights=None, smooth_l1_beta=0.0,
-              bbox_reg_weights=(10.0, 10.0, 5.0, 5.0)):
+              bbox_reg_weights=(10.0, 10.0, 5.0, 5.0), refine_mist=False, mist_top_pro=0.15):
     """proposals: [R,4] (all images concatenated).  Returns dict(losses, scores, img_scores, branches[...],
     grad_cls, grad_det, grad_ref_logits, grad_ref_deltas).  Launches: 1 (MIL fwd+loss) + 1 (MIL bwd)
-    + per branch 2 (assign, CE fwd/bwd/softmax) [+ 2 with box regression]."""
+    + per branch 2 (assign, CE fwd/bwd/softmax) [+ 2 with box regression].
+    refine_mist: WSL.REFINE_MIST targets (roi_heads_oicr.py:418-424) -- seeds from get_pgt_mist, branch 0 weighted x3
+    unless term_weights is given; that path reads the per-image seed counts on the host (not graph-capturable)."""
     fwd = ops.wsddn_forward(mil_cls, mil_det, num_preds_per_image, labels_onehot, mean_loss)
     out = dict(losses={"loss_cls": fwd["loss"]}, scores=fwd["scores"], img_scores=fwd["img_scores"], branches=[])
     prev_scores, prev_boxes = fwd["scores"], proposals
     grads_l, grads_d = [], []
     boxes_noreg = None
     for k, logits in enumerate(ref_logits):
-        tw = 1.0 if term_weights is None else float(term_weights[k])
-        a = ops.refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int,
-                              fwd["img_scores"], num_classes, iou_thresholds, iou_labels, want_iou=True)
+        tw = (3.0 if refine_mist and k == 0 else 1.0) if term_weights is None else float(term_weights[k])
+        if refine_mist:
+            a = refine_labels_mist(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int,
+                                   fwd["img_scores"], num_classes, mist_top_pro, iou_thresholds, iou_labels, want_iou=True)
+        else:
+            a = ops.refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int,
+                                  fwd["img_scores"], num_classes, iou_thresholds, iou_labels, want_iou=True)
         ce = ops.refine_ce(logits, a["gt_classes"], a["loss_weights"], a["valid_count"], loss_scale=tw,
                            want_grad=need_grad)
         out["losses"]["loss_cls_r%d" % k] = ce["loss"]

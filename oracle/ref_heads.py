@@ -235,7 +235,8 @@ def oicr_box_reg_loss(deltas, proposals, gt_boxes, gt_classes, gt_weights, num_c
 
 # ---------------------------------------------------------------- the whole head step
 def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposal_boxes, labels, num_classes, mean_loss=True,
-              reg=False, reg_weighted=True, thresholds=(0.5,), iou_labels=(0, 1), need_grad=True):
+              reg=False, reg_weighted=True, thresholds=(0.5,), iou_labels=(0, 1), need_grad=True, refine_mist=False,
+              mist_top_pro=0.15):
     """One training pass of the head math of OICRROIHeads._forward_box (roi_heads_oicr.py:404-449):
     WSDDN scores + BCE, then per refinement branch: pseudo-gt -> labels -> weighted CE (+ box reg)
     -> softmax / decoded boxes for the next branch.  Returns losses, per-branch labels, and
@@ -259,15 +260,19 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposal_boxes, labels, 
     allp = torch.cat(proposal_boxes, dim=0)
     branches = []
     for k in range(len(RL)):
-        pgt = get_pgt_top1(prev_boxes, prev_scores, labels, img_det, num_classes)
+        if refine_mist:  # roi_heads_oicr.py:418-424 (term weight 3 on the first branch)
+            pgt = get_pgt_mist(prev_boxes, prev_scores, labels, img_det, num_classes, mist_top_pro)
+        else:
+            pgt = get_pgt_top1(prev_boxes, prev_scores, labels, img_det, num_classes)
+        tw = 3.0 if refine_mist and k == 0 else 1.0
         lab = [label_proposals(p, b, num_classes, thresholds, iou_labels) for p, b in zip(pgt, proposal_boxes)]
         gt_classes = torch.cat([l["gt_classes"] for l in lab])
         gt_weights = torch.cat([l["gt_weights"] for l in lab])
         gt_boxes = torch.cat([l["gt_boxes"] for l in lab])
-        losses["loss_cls_r%d" % k] = oicr_ce_loss(RL[k], gt_classes, gt_weights)
+        losses["loss_cls_r%d" % k] = oicr_ce_loss(RL[k], gt_classes, gt_weights) * tw
         if reg:
             losses["loss_box_reg_r%d" % k] = oicr_box_reg_loss(RD[k], allp, gt_boxes, gt_classes, gt_weights,
-                                                               num_classes, weighted=reg_weighted)
+                                                               num_classes, weighted=reg_weighted) * tw
         probs = F.softmax(RL[k].detach(), dim=-1)
         dl = RD[k].detach() if reg else torch.zeros(allp.shape[0], 4 * num_classes, device=allp.device)
         boxes = apply_deltas(dl, allp)
