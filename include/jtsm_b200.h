@@ -145,6 +145,10 @@ JTSM_API int jtsm_roi_loop_pool_forward(const void* input, const float* rois, in
  * MOIPool_cuda.cu:139-215 mask, :218-294 pool).  oh_labels int32 [num_rois, len_labels],
  * superpixels int32 [batch, height_sp, width_sp].  Returns output AND argmax (int32; consumed by
  * roi_heads_jtsm.py:615-630).  Backward (MOIPool.h:85-95) = jtsm_roi_pool_backward.
+ * Fused epilogue of the JTSM heads (roi_heads_jtsm.py:615-633), optional: out = (out * mask_scale[r]) * row_scale[r]
+ * with mask_scale[r] = P*P / (#bins of RoI r whose arg-max is not -1, + 1) when `mask_scale` != 0 and row_scale =
+ * objectness_logits + 1 (NULL = 1).  scale_out float[3 * num_rois] (required when either is on): mask scales,
+ * row scales, products -- pass scale_out + 2*num_rois as row_scale to jtsm_roi_pool_backward.
  * ------------------------------------------------------------------------ */
 JTSM_API size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width, int num_rois,
                                               int pooled_h, int pooled_w);
@@ -152,7 +156,8 @@ JTSM_API int jtsm_moi_pool_forward(const void* input, const float* rois, const i
                                    int len_labels, const int* superpixels, int height_sp,
                                    int width_sp, int dtype, int batch, int channels, int height,
                                    int width, int num_rois, float spatial_scale, int pooled_h,
-                                   int pooled_w, void* output, int* argmax, void* workspace,
+                                   int pooled_w, const float* row_scale, int mask_scale,
+                                   float* scale_out, void* output, int* argmax, void* workspace,
                                    size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------

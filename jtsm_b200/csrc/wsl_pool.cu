@@ -199,8 +199,9 @@ moi_mask_kernel(const float* __restrict__ rois, const int* __restrict__ oh_label
 template <typename T, bool kSmem>
 __global__ void __launch_bounds__(kWslThreads)
 moi_pool_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW, int splits,
-                    PoolWorkspace ws, const unsigned char* __restrict__ mask, T* __restrict__ output,
-                    int* __restrict__ argmax) {
+                    PoolWorkspace ws, const unsigned char* __restrict__ mask,
+                    const float* __restrict__ scales /* [2R]: mask scale, row scale; or NULL */, int num_rois,
+                    T* __restrict__ output, int* __restrict__ argmax) {
   extern __shared__ float plane_s[];
   const int item = blockIdx.x;
   const int s = item % splits;
@@ -240,8 +241,48 @@ moi_pool_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int
         if (v > m) { m = v; mi = idx; }
       }
     const size_t o = ((size_t)r * channels + c) * PP + bin;
-    output[o] = Elem<T>::from_f(mi == -1 ? 0.f : m);
+    float v = mi == -1 ? 0.f : m;
+    if (scales) v = __fmul_rn(__fmul_rn(v, scales[r]), scales[num_rois + r]);  // (f * mask_scale) * (objectness + 1)
+    output[o] = Elem<T>::from_f(v);
     argmax[o] = mi;
+  }
+}
+
+// Per-RoI scales of the JTSM heads (roi_heads_jtsm.py:615-633), fused into the pooling epilogue:
+//   mask_scale = P*P * 1 / (#bins with at least one switched-on cell + 1)   -- the bins whose arg-max is not -1
+//   row scale  = objectness_logits + 1 (caller supplied)
+// scales[r] = mask scale (1 if off), scales[R + r] = row scale (1 if none), scales[2R + r] = their product
+// (what the backward multiplies by).  One warp per RoI.
+__global__ void moi_scale_kernel(int num_rois, int W, int hw, int PH, int PW, PoolWorkspace ws,
+                                 const unsigned char* __restrict__ mask, const float* __restrict__ row_scale,
+                                 int use_mask_scale, float* __restrict__ scales) {
+  const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (r >= num_rois) return;
+  int valid = 0;
+  if (use_mask_scale) {
+    const unsigned char* mk = mask + (size_t)r * hw;
+    for (int bin = lane; bin < PH * PW; bin += 32) {
+      const int ph = bin / PW, pw = bin - ph * PW;
+      const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
+      bool any = false;
+      for (int h = range_lo(hb); h < range_hi(hb) && !any; ++h)
+        for (int w = range_lo(wb); w < range_hi(wb); ++w)
+          if (mk[h * W + w]) {
+            any = true;
+            break;
+          }
+      valid += any;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) valid += __shfl_xor_sync(0xffffffffu, valid, o);
+  }
+  if (lane == 0) {
+    const float ms = use_mask_scale ? __fmul_rn((float)(PH * PW), __frcp_rn((float)valid + 1.f)) : 1.f;
+    const float rs = row_scale ? row_scale[r] : 1.f;
+    scales[r] = ms;
+    scales[num_rois + r] = rs;
+    scales[2 * (size_t)num_rois + r] = __fmul_rn(ms, rs);
   }
 }
 
@@ -335,7 +376,8 @@ extern "C" size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width
 extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const int* oh_labels, int len_labels,
                                      const int* superpixels, int height_sp, int width_sp, int dtype, int batch,
                                      int channels, int height, int width, int num_rois, float spatial_scale,
-                                     int pooled_h, int pooled_w, void* output, int* argmax, void* workspace,
+                                     int pooled_h, int pooled_w, const float* row_scale, int mask_scale,
+                                     float* scale_out, void* output, int* argmax, void* workspace,
                                      size_t workspace_bytes, void* stream) {
   if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 ||
       pooled_h > 64 || pooled_w > 64 || len_labels < 0 || height_sp <= 0 || width_sp <= 0)
@@ -359,6 +401,14 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
   moi_mask_kernel<<<mgrid, 256, 0, st>>>(rois, oh_labels, len_labels, superpixels, height_sp, width_sp, batch,
                                          height, width, spatial_scale, num_rois, mask);
   count_launch(2);
+  const float* scales = nullptr;
+  if (row_scale || mask_scale) {
+    if (!scale_out) return JTSM_ERR_INVALID_ARGUMENT;  // [3 * num_rois]: the backward needs the product
+    moi_scale_kernel<<<(num_rois + 7) / 8, 256, 0, st>>>(num_rois, width, hw, pooled_h, pooled_w, ws, mask, row_scale,
+                                                        mask_scale, scale_out);
+    count_launch();
+    scales = scale_out;
+  }
   const int planes = batch * channels;
   const int splits = wsl_splits(planes, num_rois);
   const size_t smem = (size_t)hw * sizeof(float);
@@ -368,10 +418,11 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
       auto k = moi_pool_fwd_kernel<T, true>;
       if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
-                                                     splits, ws, mask, (T*)output, argmax);
+                                                     splits, ws, mask, scales, num_rois, (T*)output, argmax);
     } else {
       moi_pool_fwd_kernel<T, false><<<planes * splits, kWslThreads, 0, st>>>(
-          (const T*)input, channels, height, width, pooled_h, pooled_w, splits, ws, mask, (T*)output, argmax);
+          (const T*)input, channels, height, width, pooled_h, pooled_w, splits, ws, mask, scales, num_rois,
+          (T*)output, argmax);
     }
   });
   count_launch();

@@ -488,8 +488,11 @@ def roi_loop_pool_backward(grad, rois, argmax, spatial_scale, pooled_height, poo
                              (pooled_height, pooled_width))
 
 
-def moi_pool_forward(input, rois, spatial_scale, pooled_height, pooled_width, oh_labels, superpixels):
-    """wsl._C.moi_pool_forward (MOIPool.h:52-59) -> (output [R,C,PH,PW], argmax int32)."""
+def moi_pool_forward(input, rois, spatial_scale, pooled_height, pooled_width, oh_labels, superpixels, row_scale=None,
+                     mask_scale=False, return_scales=False):
+    """wsl._C.moi_pool_forward (MOIPool.h:52-59) -> (output [R,C,PH,PW], argmax int32).
+    row_scale [R] / mask_scale: the JTSM heads' per-RoI factors (roi_heads_jtsm.py:615-633) fused into the
+    epilogue; return_scales adds the [3,R] tensor (mask scales, row scales, products) for the backward."""
     _require_cuda(input, rois, oh_labels, superpixels)
     assert rois.dim() == 2 and rois.size(1) == 5
     n, c, h, w = input.shape
@@ -502,19 +505,24 @@ def moi_pool_forward(input, rois, spatial_scale, pooled_height, pooled_width, oh
     assert oh.dim() == 2 and oh.size(0) == r and sp.dim() == 3 and sp.size(0) == n
     output = torch.empty((r, c, ph, pw), dtype=input.dtype, device=input.device)
     argmax = torch.empty((r, c, ph, pw), dtype=torch.int32, device=input.device)
+    fused = row_scale is not None or mask_scale
+    scales = torch.ones((3, r), dtype=torch.float32, device=input.device) if fused else None
+    rs = _f32c(row_scale) if row_scale is not None else None
     if r == 0 or c == 0:
-        return output, argmax
+        return (output, argmax, scales) if return_scales else (output, argmax)
     L = lib()
     wsb = L.jtsm_moi_pool_workspace_bytes(n, h, w, r, ph, pw)
     ws = _workspace(wsb, input.device)
     with torch.cuda.device(input.device):
         check(L.jtsm_moi_pool_forward(_ptr(input), _ptr(rois), _ptr(oh), oh.size(1), _ptr(sp), sp.size(1), sp.size(2),
-                                      _dtype_code(input), n, c, h, w, r, float(spatial_scale), ph, pw, _ptr(output),
-                                      _ptr(argmax), _ptr(ws), wsb, _stream()), "moi_pool_forward")
-    return output, argmax
+                                      _dtype_code(input), n, c, h, w, r, float(spatial_scale), ph, pw, _ptr(rs),
+                                      int(bool(mask_scale)), _ptr(scales), _ptr(output), _ptr(argmax), _ptr(ws), wsb,
+                                      _stream()), "moi_pool_forward")
+    return (output, argmax, scales) if return_scales else (output, argmax)
 
 
 def moi_pool_backward(grad, rois, argmax, spatial_scale, pooled_height, pooled_width, batch_size, channels, height,
-                      width):
+                      width, row_scale=None):
     """wsl._C.moi_pool_backward (MOIPool.h:85-95)."""
-    return roi_pool_backward(grad, rois, argmax, (batch_size, channels, height, width), (pooled_height, pooled_width))
+    return roi_pool_backward(grad, rois, argmax, (batch_size, channels, height, width), (pooled_height, pooled_width),
+                             row_scale=row_scale)

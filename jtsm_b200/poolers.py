@@ -4,8 +4,9 @@ detectron2/modeling/poolers.py:147-249) built on the sm_100a ops.
 
 Same constructor arguments, same `forward(x, box_lists, level_ids=None, oh_labels_list=None, superpixels=None)`,
 same level-assignment rule and output layout (ROILoopPool: `[3M, C, P, P]`).  Boxes may be detectron2 `Boxes`
-(anything with a `.tensor` attribute) or plain `[R_i, 4]` tensors.  Extension: `row_scale=` (per-RoI factor,
-`objectness_logits + 1` in the WSL heads, roi_heads_oicr.py:393-394) is fused into the RoIPool kernels.
+(anything with a `.tensor` attribute) or plain `[R_i, 4]` tensors.  Extensions: `row_scale=` (per-RoI factor,
+`objectness_logits + 1` in the WSL heads, roi_heads_oicr.py:393-394) is fused into the RoIPool / MOIPool kernels,
+`mask_scale=True` adds MOIPool's P*P / (#valid bins + 1) factor of the JTSM heads (roi_heads_jtsm.py:615-630).
 """
 import math
 
@@ -77,7 +78,8 @@ class ROIPooler(nn.Module):
         self.canonical_box_size = canonical_box_size
         self.valid_range = VALID_RANGE if use_range else None
 
-    def forward(self, x, box_lists, level_ids=None, oh_labels_list=None, superpixels=None, row_scale=None):
+    def forward(self, x, box_lists, level_ids=None, oh_labels_list=None, superpixels=None, row_scale=None,
+                mask_scale=False):
         n_levels = len(self.level_poolers)
         assert isinstance(x, list) and isinstance(box_lists, list), "Arguments to pooler must be lists"
         assert len(x) == n_levels, "num_level_assignments={}, but x is list of {} Tensors".format(n_levels, len(x))
@@ -93,9 +95,9 @@ class ROIPooler(nn.Module):
         def call(level, boxes, lab=None, scale=None):
             pooler = self.level_poolers[level]
             if lab is not None:
-                return pooler(x[level], boxes, lab, sp)
+                return pooler(x[level], boxes, lab, sp, row_scale=scale, mask_scale=mask_scale)
             if scale is not None:
-                assert isinstance(pooler, RoIPool), "row_scale is fused for ROIPool only"
+                assert isinstance(pooler, RoIPool), "row_scale is fused for ROIPool and MOIPool only"
                 return pooler(x[level], boxes, row_scale=scale)
             return pooler(x[level], boxes)
 

@@ -70,3 +70,29 @@ def test_wsl_pools_empty(cuda):
                                     torch.zeros(0, 4, dtype=torch.int32, device=cuda),
                                     torch.zeros(1, 16, 16, dtype=torch.int32, device=cuda))
     assert out.shape == (0, 3, 7, 7)
+
+
+def test_moi_pool_fused_jtsm_scales(cuda, oracle):
+    """Fused mask_scale * (objectness + 1) epilogue == the JTSM heads' eager arithmetic on the oracle's output
+    (roi_heads_jtsm.py:615-633), bit for bit; backward carries the same factors."""
+    from jtsm_b200.layers import MOIPool
+
+    g, x, rois = _case(81, 2, 5, 75, 100, 70)
+    sp, s = synth.superpixels(g, 2, 600, 800, 40)
+    oh = synth.oh_labels(g, rois.shape[0], s, p=0.2)
+    obj = torch.rand(rois.shape[0], generator=g) + 1.0
+    ref, rarg = oracle.moi_pool_forward(x.numpy(), rois.numpy(), oh.numpy(), sp.numpy(), 1 / 8.0, (7, 7))
+    ref, rarg = torch.from_numpy(ref), torch.from_numpy(rarg)
+    mask_scale = rarg.size(2) * rarg.size(3) * ((rarg[:, 0, :, :] != -1).view(rarg.size(0), -1).sum(dim=1)
+                                                .to(dtype=torch.float32) + 1).reciprocal()
+    want = (ref * mask_scale.view(-1, 1, 1, 1)) * obj.view(-1, 1, 1, 1)
+    assert mask_scale.min() < mask_scale.max()
+    xg = x.to(cuda).requires_grad_()
+    out, arg = MOIPool((7, 7), 1 / 8.0)(xg, rois.to(cuda), oh.to(cuda), sp.to(cuda), row_scale=obj.to(cuda),
+                                        mask_scale=True)
+    assert torch.equal(out.detach().cpu(), want) and torch.equal(arg.cpu(), rarg)
+    go = torch.randn(out.shape, generator=synth.generator(82))
+    out.backward(go.to(cuda))
+    gi_ref = oracle.max_pool_backward((go * (mask_scale * obj).view(-1, 1, 1, 1)).numpy(), rarg.numpy(), rois.numpy(),
+                                      tuple(x.shape))
+    np.testing.assert_allclose(xg.grad.cpu().numpy(), gi_ref, rtol=1e-5, atol=1e-5 * float(np.abs(gi_ref).max()))
