@@ -320,8 +320,12 @@ bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, 
   const long long hw = (long long)height * width;
   const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
   return (algo == 0 || algo == 3) && !tuning("roi_pool_force_gmem", 0) && hw < 65535 &&
-         rmq_smem_bytes((int)hw) <= 227 * 1024 && (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL;
+         rmq_smem_bytes((int)hw) <= 227 * 1024 && (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL &&
+         (long long)num_rois * PH * PW * PH * PW < 0xFFFFFFFFLL;  // exact magic division of a bin id by PH*PW
 }
+
+template <typename T> constexpr bool dtype_is_f32() { return false; }
+template <> constexpr bool dtype_is_f32<float>() { return true; }
 
 int pick_splits(int planes, int num_rois, int ctas_per_sm) {
   // enough CTAs for ~4 waves, but keep >= 64 RoIs per CTA so the plane load amortises
@@ -345,7 +349,10 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
   const size_t rmq_smem = rmq_smem_bytes(hw);
   const int algo = tuning("roi_pool_fwd_algo", 0);
   if (rmq_eligible(batch, channels, height, width, num_rois, PH, PW)) {
-    const size_t smem = rmq_smem;
+    // a second plane buffer (fp32 inputs) lets the next plane stream in behind the queries of the current one
+    const int two_planes = dtype_is_f32<T>() && rmq_smem + (size_t)hw * 4 <= 227 * 1024 &&
+                           tuning("roi_pool_fwd_async", 1);
+    const size_t smem = rmq_smem + (two_planes ? (size_t)hw * 4 : 0);
     static bool rmq_attr = false;
     if (!rmq_attr) {
       cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
@@ -362,7 +369,7 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
     const int items = planes * chunks;
     const int grid = items < max_grid ? items : max_grid;
     roi_pool_fwd_rmq_kernel<T, A><<<grid, kRmqThreads, smem, st>>>(
-        (const T*)input, channels, height, width, PH, PW, chunks, items, ws, (T*)output, (A*)argmax);
+        (const T*)input, channels, height, width, PH, PW, chunks, items, two_planes, ws, (T*)output, (A*)argmax);
     count_launch();
     return cuda_status();
   }

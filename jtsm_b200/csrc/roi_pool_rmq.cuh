@@ -71,16 +71,10 @@ __device__ __forceinline__ void rmq_build_level(const float* plane, const unsign
   }
 }
 
-// plane (fp32) + the 10 tables of one (image, channel) plane; all threads of the CTA call it.
-template <typename T>
-__device__ __forceinline__ void rmq_build_plane(const T* __restrict__ src, float* plane, unsigned short* tabs,
-                                                int hw, int W) {
+// The 9 non-identity tables of the plane in `plane` (slot 0, the identity level, is written once per kernel);
+// all threads of the CTA call it, after a barrier that makes the plane visible.
+__device__ __forceinline__ void rmq_build_tables(const float* plane, unsigned short* tabs, int hw, int W) {
 #define TAB(s) (tabs + (size_t)(s) * hw)
-  for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
-    plane[p] = Elem<T>::to_f(src[p]);
-    TAB(0)[p] = (unsigned short)p;  // identity level (0,0)
-  }
-  __syncthreads();
   rmq_build_level(plane, TAB(0), TAB(2), hw, 1);      // (0,1)
   rmq_build_level(plane, TAB(0), TAB(1), hw, W);      // (1,0)
   __syncthreads();
@@ -98,6 +92,19 @@ __device__ __forceinline__ void rmq_build_plane(const T* __restrict__ src, float
   __syncthreads();
 #undef TAB
 }
+
+// fp32 planes can be fetched asynchronously (4-byte cp.async per cell) into the spare plane buffer while the
+// queries of the current plane run.
+template <typename T> struct PlaneAsync { static constexpr bool ok = false; };
+template <> struct PlaneAsync<float> { static constexpr bool ok = true; };
+__device__ __forceinline__ void plane_prefetch_async(const float* __restrict__ src, float* dst, int hw) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+  for (int p = threadIdx.x; p < hw; p += kRmqThreads)
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u * p), "l"(src + p) : "memory");
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <typename T>
+__device__ __forceinline__ void plane_prefetch_async(const T*, float*, int) {}
 
 // Slow path of one bin (empty, elongated or > 16-cell ranges) from the packed [start, end) ranges:
 // nearest stored level, as many windows as needed.  Empty bin -> value 0, index 0xFFFFFFFF.
@@ -125,16 +132,26 @@ __device__ __noinline__ RmqCand rmq_query_slow(const float* plane, const unsigne
   return best;
 }
 
-// 2 x 2 windows of a stored level: byte offsets base, +db, +dh, +dh+db into the table block.
-__device__ __forceinline__ RmqCand rmq_query_fast(const float* plane, const unsigned short* tabs, unsigned base,
-                                                  unsigned dh, unsigned db) {
-  const char* tb = (const char*)tabs + base;
-  const unsigned ia = *(const unsigned short*)(tb);
-  const unsigned ib = *(const unsigned short*)(tb + db);
-  const unsigned ic = *(const unsigned short*)(tb + dh);
-  const unsigned id = *(const unsigned short*)(tb + dh + db);
-  return rmq_best(rmq_best(rmq_load(plane, ia), rmq_load(plane, ib)),
-                  rmq_best(rmq_load(plane, ic), rmq_load(plane, id)));
+// Shared-memory loads by 32-bit shared-window address: the address arithmetic of the hot loop stays one add
+// per look-up (the compiler otherwise re-derives the window base from the CTA rank every round).
+__device__ __forceinline__ unsigned lds_u16(unsigned addr) {
+  unsigned short v;
+  asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float lds_f32(unsigned addr) {
+  float v;
+  asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
+// 2 x 2 windows of a stored level: table look-ups at base, +db, +dh, +dh+db (shared-window byte addresses),
+// then the 4 candidate values from the plane at plane_s.
+__device__ __forceinline__ RmqCand rmq_query_fast(unsigned plane_s, unsigned base, unsigned dh, unsigned db) {
+  const unsigned ia = lds_u16(base), ib = lds_u16(base + db), ic = lds_u16(base + dh), id = lds_u16(base + dh + db);
+  const RmqCand a{lds_f32(plane_s + 4u * ia), ia}, b{lds_f32(plane_s + 4u * ib), ib};
+  const RmqCand c{lds_f32(plane_s + 4u * ic), ic}, d{lds_f32(plane_s + 4u * id), id};
+  return rmq_best(rmq_best(a, b), rmq_best(c, d));
 }
 
 struct RmqItem {
@@ -159,86 +176,151 @@ __device__ __forceinline__ RmqItem rmq_item(int item, int chunks, int channels, 
   return it;
 }
 
+// Main loop of one (plane, RoI-chunk) item: one fast bin per thread and round.  Everything is indexed with
+// 32-bit offsets from the kernel's own pointer arguments (the launcher checks the sizes): bin id i ->
+// RoI r = i / PP (magic multiply) -> output element i + r * (C - 1) * PP + c * PP.  Descriptor and row scale
+// are loaded one round ahead (they come from L2: little L1 is left next to 180+ KB of shared memory; deeper
+// rings of 2 and 4 rounds measured the same).  x = 0 marks a slow bin (left to the list)
+// or an inactive thread: the branch-free look-ups then run on offset 0, which is harmless.
+template <typename T, typename A, bool kUngrouped>
+__device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
+                                              const RmqItem& it, int PP, int cpp, unsigned w2, unsigned magic_pp,
+                                              T* __restrict__ output, A* __restrict__ argmax) {
+  const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
+  const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
+  const unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
+  const unsigned tabs_s = (unsigned)__cvta_generic_to_shared(tabs);
+  unsigned i = (unsigned)(it.r0 * PP) + threadIdx.x;
+  unsigned xn = 0u;
+  float scn = 0.f;
+  if (i < i_end) {
+    xn = __ldg(ws.bdesc + i);
+    scn = __ldg(ws.rscale + __umulhi(i, magic_pp));
+  }
+  while (i < i_end) {
+    const unsigned x = xn;
+    const float sc = scn;
+    const unsigned r = __umulhi(i, magic_pp);
+    const unsigned o = i + r * o_r + o_c;
+    i += kRmqThreads;
+    if (i < i_end) {  // next round's descriptor and scale in flight during this round's look-ups
+      xn = __ldg(ws.bdesc + i);
+      scn = __ldg(ws.rscale + __umulhi(i, magic_pp));
+    }
+    const RmqCand best = rmq_query_fast(plane_s, tabs_s + (x & 0x3FFFFu), ((x >> 18) & 15u) * w2, (x >> 22) & 31u);
+    bool act = (int)x < 0;  // x >= 0: slow bin, left to the list
+    if (kUngrouped && act) act = __ldg(ws.batch_idx + r) == it.n;
+    if (act) {
+      output[o] = Elem<T>::from_f(__fmul_rn(best.v, sc));
+      argmax[o] = (A)best.i;  // a fast bin always has a cell
+    }
+  }
+}
+
+// The few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%) of RoIs [r_lo, r_hi) for the plane
+// whose tables are resident.  The prep kernel lists them, so no warp of the main loop diverges into the long
+// path; the list is short and every CTA filters it for the RoI range it has just served.
+template <typename T, typename A>
+__device__ __forceinline__ void rmq_slow_pass(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
+                                              int n, int c, int r_lo, int r_hi, bool ungrouped, int channels, int hw,
+                                              int W, int PH, int PW, T* __restrict__ output, A* __restrict__ argmax) {
+  const int PP = PH * PW;
+  const int ns = __ldg(ws.slow_count);
+  for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
+    const int id = __ldg(ws.slow_list + j);
+    const int rr = id / PP, b = id - rr * PP;
+    if (rr < r_lo || rr >= r_hi) continue;
+    if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+    const int ph = b / PW, pw = b - ph * PW;
+    const RmqCand best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)rr * PH + ph),
+                                        __ldg(ws.wbins + (size_t)rr * PW + pw));
+    const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
+    output[so] = Elem<T>::from_f(__fmul_rn(best.v, __ldg(ws.rscale + rr)));
+    argmax[so] = Arg<A>::enc((int)best.i);
+  }
+}
+
+// dynamic smem: plane A (hw fp32) | 10 tables (hw uint16 each) | plane B (hw fp32, only when two_planes)
 template <typename T, typename A>
 __global__ void __launch_bounds__(kRmqThreads, 1)
 roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW,
-                        int chunks, int num_items, PoolWorkspace ws, T* __restrict__ output,
+                        int chunks, int num_items, int two_planes, PoolWorkspace ws, T* __restrict__ output,
                         A* __restrict__ argmax) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int hw = H * W;
   float* plane = (float*)smem_raw;
   unsigned short* tabs = (unsigned short*)(plane + hw);
+  float* spare = (float*)(tabs + (size_t)kRmqTables * hw);  // valid only when two_planes
   const int PP = PH * PW, cpp = channels * PP;
   const unsigned w2 = 2u * (unsigned)W;
   const bool ungrouped = *ws.ungrouped != 0;
-  // (RoI, bin) of this thread's output and the step of one round (kRmqThreads outputs); the output
-  // offset rl * cpp + bin is stepped along with them
-  const int step_r = kRmqThreads / PP, step_b = kRmqThreads - step_r * PP;
-  const int step_o = step_r * cpp + step_b, wrap_o = cpp - PP;
-  const int rl_init = threadIdx.x / PP, bin_init = threadIdx.x - rl_init * PP;
+  const unsigned magic_pp = (unsigned)((0x100000000ull + PP - 1) / PP);
+  const bool async = PlaneAsync<T>::ok && two_planes;
 
-  // contiguous item range of this CTA
-  const int per = num_items / gridDim.x, rem = num_items % gridDim.x;
-  const int i0 = blockIdx.x * per + min((int)blockIdx.x, rem);
-  const int i1 = i0 + per + ((int)blockIdx.x < rem ? 1 : 0);
-  int cur_plane = -1;
+  // Item schedule of this CTA.  Planes are dealt round-robin -- CTA k serves planes k, k + G, k + 2G, ... with all
+  // their RoI chunks -- so that at any moment neighbouring CTAs write neighbouring channels of the same RoIs: the
+  // 196-byte runs of channel c and c + 1 share a 32-byte sector, and its two halves now reach L2 within
+  // microseconds of each other instead of a plane's whole processing time apart (a half-written sector that is
+  // evicted costs a DRAM read-modify-write).  The planes left over after the full rounds are cut into chunks and
+  // spread over all CTAs as one contiguous range each.
+  const int G = gridDim.x, planes = num_items / chunks;
+  const int full = (planes / G) * chunks;               // items of the full rounds, per CTA
+  const int tail_items = (planes % G) * chunks;         // items of the last, partial round (all CTAs together)
+  const int tail_base = (planes / G) * G * chunks;      // id of its first item
+  const int t_per = tail_items / G, t_rem = tail_items % G;
+  const int t0 = blockIdx.x * t_per + min((int)blockIdx.x, t_rem);
+  const int my_items = full + t_per + ((int)blockIdx.x < t_rem ? 1 : 0);
+  auto item_id = [&](int idx) {  // idx-th item of this CTA -> global item id = plane * chunks + chunk
+    if (idx < full) return ((idx / chunks) * G + (int)blockIdx.x) * chunks + idx % chunks;
+    return tail_base + t0 + (idx - full);
+  };
+  int cur_plane = -1, in_flight = -1;  // plane whose tables are resident / plane being fetched into `spare`
+  int r_lo = 0, r_hi = 0;              // RoIs served with the resident tables
 
-  for (int item = i0; item < i1; ++item) {
+  for (int p = threadIdx.x; p < hw; p += kRmqThreads) tabs[p] = (unsigned short)p;  // identity level (0,0), slot 0
+
+  for (int idx = 0; idx < my_items; ++idx) {
     int nc;
-    const RmqItem it = rmq_item(item, chunks, channels, ws, nc);
+    const RmqItem it = rmq_item(item_id(idx), chunks, channels, ws, nc);
     if (nc != cur_plane) {
-      __syncthreads();  // previous item's queries are done with the old tables
+      if (cur_plane >= 0)
+        rmq_slow_pass<T, A>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
+                            channels, hw, W, PH, PW, output, argmax);
+      if (async && in_flight == nc) {
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();  // everyone is done with the old plane and tables; the fetched plane is complete
+        float* t = plane;
+        plane = spare;
+        spare = t;
+      } else {
+        __syncthreads();
+        const T* src = input + (size_t)nc * hw;
+        for (int p = threadIdx.x; p < hw; p += kRmqThreads) plane[p] = Elem<T>::to_f(src[p]);
+        __syncthreads();
+      }
       cur_plane = nc;
-      rmq_build_plane(input + (size_t)nc * hw, plane, tabs, hw, W);
-    }
-    // All indices are 32-bit offsets from the kernel's own pointer arguments (the launcher checks the
-    // sizes), so the loop carries five integers and no 64-bit pointers.
-    unsigned i = (unsigned)(it.r0 * PP) + threadIdx.x;           // bin id
-    const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
-    unsigned r = (unsigned)(it.r0 + rl_init);                    // RoI of bin i
-    int bin = bin_init;                                          // i - r * PP
-    unsigned o = (r * (unsigned)channels + (unsigned)it.c) * (unsigned)PP + (unsigned)bin;  // output element
-    // descriptor and row scale are loaded one round ahead (they come from L2: little L1 is left next to
-    // 180+ KB of shared memory), so their latency hides behind the look-ups of the current round
-    unsigned xn = 0u;
-    float scn = 0.f;
-    if (i < i_end) xn = __ldg(ws.bdesc + i), scn = __ldg(ws.rscale + r);
-    while (i < i_end) {
-      const unsigned x = xn;  // x = 0: slow bin, left to the list below (the look-ups then run on offset 0)
-      const float sc = scn;
-      bool act = (int)x < 0;
-      if (ungrouped && act) act = __ldg(ws.batch_idx + r) == it.n;
-      const unsigned o_cur = o;
-      i += kRmqThreads;
-      bin += step_b;
-      r += step_r;
-      o += step_o;
-      if (bin >= PP) bin -= PP, ++r, o += wrap_o;
-      if (i < i_end) xn = __ldg(ws.bdesc + i), scn = __ldg(ws.rscale + r);
-      const RmqCand best = rmq_query_fast(plane, tabs, x & 0x3FFFFu, ((x >> 18) & 15u) * w2, (x >> 22) & 31u);
-      const float v = __fmul_rn(best.v, sc);
-      if (act) {
-        output[o_cur] = Elem<T>::from_f(v);
-        argmax[o_cur] = Arg<A>::enc((int)best.i);
+      r_lo = it.r0, r_hi = it.r0;
+      rmq_build_tables(plane, tabs, hw, W);
+      // the next plane this CTA will serve, if any: fetch it behind the queries of this one
+      if (async) {
+        int j = idx + 1;
+        while (j < my_items && item_id(j) / chunks == nc) ++j;
+        if (j < my_items) {
+          in_flight = item_id(j) / chunks;
+          plane_prefetch_async(input + (size_t)in_flight * hw, spare, hw);
+        }
       }
     }
-    // the few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%), listed by the prep
-    // kernel so that no warp of the main loop diverges into the long path; the list is short, every
-    // item filters it for its own RoI range
-    const int ns = __ldg(ws.slow_count);
-    for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
-      const int id = __ldg(ws.slow_list + j);
-      const int rr = id / PP, b = id - rr * PP;
-      if (rr < it.r0 || rr >= it.r0 + it.nr) continue;
-      if (ungrouped && __ldg(ws.batch_idx + rr) != it.n) continue;
-      const int ph = b / PW, pw = b - ph * PW;
-      const RmqCand best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)rr * PH + ph),
-                                          __ldg(ws.wbins + (size_t)rr * PW + pw));
-      const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)it.c) * (unsigned)PP + (unsigned)b;
-      output[so] = Elem<T>::from_f(__fmul_rn(best.v, __ldg(ws.rscale + rr)));
-      argmax[so] = Arg<A>::enc((int)best.i);
-    }
+    if (it.nr > 0) r_hi = it.r0 + it.nr;  // chunks of a plane are consecutive RoI ranges
+    if (ungrouped)
+      rmq_main_loop<T, A, true>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, output, argmax);
+    else
+      rmq_main_loop<T, A, false>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, output, argmax);
   }
+  if (cur_plane >= 0)
+    rmq_slow_pass<T, A>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped, channels,
+                        hw, W, PH, PW, output, argmax);
+  asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 }  // namespace jtsm
