@@ -31,6 +31,7 @@
 namespace jtsm {
 
 constexpr int kRmqThreads = 1024;
+constexpr int kRmqBinsPerThread = 2;  // independent look-up chains per thread and round
 constexpr int kRmqTables = 10;   // slot = kh + 2*kw for |kh-kw| <= 1, kh,kw in 0..3; slot 0 = identity
 constexpr int kRmqMaxLevel = 3;  // windows of 1,2,4,8 cells per axis
 
@@ -190,29 +191,45 @@ __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned
   const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
   const unsigned tabs_s = (unsigned)__cvta_generic_to_shared(tabs);
+  constexpr int K = kRmqBinsPerThread;
   unsigned i = (unsigned)(it.r0 * PP) + threadIdx.x;
-  unsigned xn = 0u;
-  float scn = 0.f;
-  if (i < i_end) {
-    xn = __ldg(ws.bdesc + i);
-    scn = __ldg(ws.rscale + __umulhi(i, magic_pp));
-  }
-  while (i < i_end) {
-    const unsigned x = xn;
-    const float sc = scn;
-    const unsigned r = __umulhi(i, magic_pp);
-    const unsigned o = i + r * o_r + o_c;
-    i += kRmqThreads;
-    if (i < i_end) {  // next round's descriptor and scale in flight during this round's look-ups
-      xn = __ldg(ws.bdesc + i);
-      scn = __ldg(ws.rscale + __umulhi(i, magic_pp));
+  unsigned xn[K];
+  float scn[K];
+  auto fetch = [&](unsigned i0) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const unsigned ik = i0 + k * kRmqThreads;
+      xn[k] = 0u, scn[k] = 0.f;
+      if (ik < i_end) {
+        xn[k] = __ldg(ws.bdesc + ik);
+        scn[k] = __ldg(ws.rscale + __umulhi(ik, magic_pp));
+      }
     }
-    const RmqCand best = rmq_query_fast(plane_s, tabs_s + (x & 0x3FFFFu), ((x >> 18) & 15u) * w2, (x >> 22) & 31u);
-    bool act = (int)x < 0;  // x >= 0: slow bin, left to the list
-    if (kUngrouped && act) act = __ldg(ws.batch_idx + r) == it.n;
-    if (act) {
-      output[o] = Elem<T>::from_f(__fmul_rn(best.v, sc));
-      argmax[o] = (A)best.i;  // a fast bin always has a cell
+  };
+  fetch(i);
+  while (i < i_end) {
+    unsigned x[K], o[K];
+    float sc[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const unsigned ik = i + k * kRmqThreads;
+      x[k] = xn[k], sc[k] = scn[k];
+      o[k] = ik + __umulhi(ik, magic_pp) * o_r + o_c;
+    }
+    i += K * kRmqThreads;
+    fetch(i);  // next round's descriptors and scales in flight during this round's look-ups
+    RmqCand best[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      best[k] = rmq_query_fast(plane_s, tabs_s + (x[k] & 0x3FFFFu), ((x[k] >> 18) & 15u) * w2, (x[k] >> 22) & 31u);
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      bool act = (int)x[k] < 0;  // x >= 0: slow bin (left to the list) or past the end
+      if (kUngrouped && act) act = __ldg(ws.batch_idx + (o[k] - o_c) / (unsigned)cpp) == it.n;
+      if (act) {
+        output[o[k]] = Elem<T>::from_f(__fmul_rn(best[k].v, sc[k]));
+        argmax[o[k]] = (A)best[k].i;  // a fast bin always has a cell
+      }
     }
   }
 }
