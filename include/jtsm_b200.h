@@ -224,7 +224,7 @@ JTSM_API int jtsm_refine_assign(
  * jtsm_refine_assign for seed sets it does not build itself: get_pgt_mist (roi_heads_oicr.py:549-591: top 15% per
  * class + class-agnostic NMS), thresholded / top-k > 1 get_pgt_top_k, or annotated boxes.
  * pgt_* [total seeds] DEVICE, seeds of image n at [seed_offsets[n], seed_offsets[n+1]) (int32 DEVICE);
- * max_seeds_per_image bounds the shared-memory staging (<= 6400).  Outputs as jtsm_refine_assign. */
+ * max_seeds_per_image bounds the shared-memory staging (<= 5000).  Outputs as jtsm_refine_assign. */
 JTSM_API int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_classes, const float* pgt_scores,
                                const float* pgt_weights, const int* seed_offsets, int max_seeds_per_image,
                                const float* proposals, const int* seg_offsets, int num_images, int num_rois,

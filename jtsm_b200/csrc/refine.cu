@@ -14,11 +14,16 @@
 // Bit-exactness notes: IoU uses the reference's operation order with explicit round-to-nearest
 // intrinsics (no FMA contraction, IEEE division); argmax ties resolve to the lowest index
 // (what torch.max(dim=0) / CPU topk do).
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace jtsm {
 
-constexpr int kAssignThreads = 1024;
+constexpr int kAssignThreads = 256;
+constexpr int kAssignCluster = 8;  // CTAs per image
 
 struct MatcherParams {  // detectron2/modeling/matcher.py:36-59
   float t0, t1;         // thresholds (t1 unused when n == 1)
@@ -41,10 +46,16 @@ __device__ __forceinline__ float iou_ref(const float4 g, float area_g, const flo
   return __fdiv_rn(inter, __fsub_rn(__fadd_rn(area_g, area_p), inter));
 }
 
-// One CTA per image.
-//  phase 1: for every image-level class g, argmax over the image's proposals of
-//           prev_scores[:, cls_g] (lowest index on ties) -> seed box / class / score / weight;
+// One thread-block CLUSTER of kAssignCluster CTAs per image (a single CTA was latency bound at ~14 us for 2000
+// proposals); proposals are strided over all threads of the cluster.
+//  phase 1: for every image-level class g, argmax over the image's proposals of prev_scores[:, cls_g] (lowest
+//           index on ties): per-CTA candidates, exchanged through distributed shared memory, every CTA then holds
+//           the seed boxes / classes / scores / weights;   (skipped when the caller supplies the seeds)
 //  phase 2: every proposal: IoU against the G seeds, first max, Matcher thresholds -> labels.
+__device__ __forceinline__ bool seed_better(float ov, int oi, float bv, int bi) {
+  return oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi));
+}
+
 __global__ void __launch_bounds__(kAssignThreads)
 refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
                      const float* __restrict__ prev_boxes, int boxes_per_row,
@@ -57,20 +68,25 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
                      float* __restrict__ matched_iou, long long* __restrict__ gt_classes,
                      float* __restrict__ gt_weights, float* __restrict__ gt_scores,
                      float* __restrict__ gt_boxes, float* __restrict__ loss_weights,
-                     int* __restrict__ counters /* [N*3] fg,bg,ignore ; then [1] valid */,
+                     int* __restrict__ counters /* [N*3] fg,bg,ignore ; then [1] valid; zeroed by the caller */,
                      int num_images) {
-  extern __shared__ float4 seeds[];  // [G] boxes, then float area[G], weight[G], score[G], int cls[G]
-  const int n = blockIdx.x;
+  extern __shared__ float4 seeds[];  // [G] boxes, then float area[G], weight[G], score[G], int cls[G], cand_v[G], cand_i[G]
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank(), nrank = (int)cluster.num_blocks();
+  const int n = blockIdx.x / nrank;
   const int r0 = seg[n], r1 = seg[n + 1];
   const int g0 = cls_off[n], G = cls_off[n + 1] - g0;
   float* s_area = (float*)(seeds + G);
   float* s_weight = s_area + G;
   float* s_score = s_weight + G;
   int* s_cls = (int*)(s_score + G);
-  __shared__ float red_v[32];
-  __shared__ int red_i[32];
+  float* cand_v = (float*)(s_cls + G);
+  int* cand_i = (int*)(cand_v + G);
+  __shared__ float red_v[kAssignThreads / 32];
+  __shared__ int red_i[kAssignThreads / 32];
   __shared__ int s_cnt[4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tid = rank * kAssignThreads + threadIdx.x, nthr = nrank * kAssignThreads;
   if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
   const bool has_gt = (G > 0) && (r1 > r0);  // top_k = min(num_pred, 1)
   const bool given = prev_scores == nullptr;  // seeds supplied by the caller (jtsm_refine_match)
@@ -83,46 +99,51 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
       s_score[g] = pgt_scores[g0 + g];
       s_cls[g] = (int)pgt_classes[g0 + g];
     }
-  }
-
-  for (int g = 0; g < G && has_gt && !given; ++g) {
-    const int cls = (int)cls_ids[g0 + g];
-    float bv = -INFINITY;
-    int bi = 0x7fffffff;
-    for (int r = r0 + threadIdx.x; r < r1; r += kAssignThreads) {
-      const float v = prev_scores[(size_t)r * score_stride + cls];
-      if (v > bv || bi == 0x7fffffff) {
-        bv = v;
-        bi = r;
+  } else {
+    // per-CTA candidate of every class
+    for (int g = 0; g < G && has_gt; ++g) {
+      const int cls = (int)cls_ids[g0 + g];
+      float bv = -INFINITY;
+      int bi = 0x7fffffff;
+      for (int r = r0 + tid; r < r1; r += nthr) {
+        const float v = prev_scores[(size_t)r * score_stride + cls];
+        if (v > bv || bi == 0x7fffffff) {
+          bv = v;
+          bi = r;
+        }
       }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi))) {
-        bv = ov;
-        bi = oi;
-      }
-    }
-    if (lane == 0) {
-      red_v[warp] = bv;
-      red_i[warp] = bi;
-    }
-    __syncthreads();
-    if (warp == 0) {
-      bv = red_v[lane];
-      bi = red_i[lane];
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
         const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (oi != 0x7fffffff && (bi == 0x7fffffff || ov > bv || (ov == bv && oi < bi))) {
-          bv = ov;
-          bi = oi;
-        }
+        if (seed_better(ov, oi, bv, bi)) bv = ov, bi = oi;
       }
-      if (lane == 0) {
+      if (lane == 0) red_v[warp] = bv, red_i[warp] = bi;
+      __syncthreads();
+      if (warp == 0) {
+        bv = lane < kAssignThreads / 32 ? red_v[lane] : -INFINITY;
+        bi = lane < kAssignThreads / 32 ? red_i[lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+          const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+          if (seed_better(ov, oi, bv, bi)) bv = ov, bi = oi;
+        }
+        if (lane == 0) cand_v[g] = bv, cand_i[g] = bi;
+      }
+      __syncthreads();
+    }
+    cluster.sync();  // every CTA's candidates are visible cluster-wide
+    for (int g = threadIdx.x; g < G; g += kAssignThreads) {
+      if (has_gt) {
+        float bv = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int j = 0; j < nrank; ++j) {  // fixed order: deterministic
+          const float ov = cluster.map_shared_rank(cand_v, j)[g];
+          const int oi = cluster.map_shared_rank(cand_i, j)[g];
+          if (seed_better(ov, oi, bv, bi)) bv = ov, bi = oi;
+        }
+        const int cls = (int)cls_ids[g0 + g];
         const int col = boxes_per_row > 1 ? cls : 0;
         const float4 b = *(const float4*)(prev_boxes + ((size_t)bi * boxes_per_row + col) * 4);
         const float wgt = img_scores[(size_t)n * num_classes + cls];
@@ -131,18 +152,24 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
         s_weight[g] = wgt;
         s_score[g] = bv;
         s_cls[g] = cls;
-        *(float4*)(pgt_boxes + (size_t)(g0 + g) * 4) = b;
-        pgt_classes[g0 + g] = cls;
-        pgt_scores[g0 + g] = bv;
-        pgt_weights[g0 + g] = wgt;
+        if (rank == 0) {
+          *(float4*)(pgt_boxes + (size_t)(g0 + g) * 4) = b;
+          pgt_classes[g0 + g] = cls;
+          pgt_scores[g0 + g] = bv;
+          pgt_weights[g0 + g] = wgt;
+        }
+      } else if (rank == 0) {  // image without proposals: its seed slots hold zeros
+        *(float4*)(pgt_boxes + (size_t)(g0 + g) * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        pgt_classes[g0 + g] = 0;
+        pgt_scores[g0 + g] = 0.f;
+        pgt_weights[g0 + g] = 0.f;
       }
     }
-    __syncthreads();
   }
-  __syncthreads();
+  cluster.sync();  // seeds complete in every CTA; nobody reads remote candidates after this point
 
   int c_fg = 0, c_bg = 0, c_ig = 0, c_valid = 0;
-  for (int r = r0 + threadIdx.x; r < r1; r += kAssignThreads) {
+  for (int r = r0 + tid; r < r1; r += nthr) {
     const float4 p = *(const float4*)(proposals + (size_t)r * 4);
     long long cls_out;
     float w_out = 0.f, sc_out = 0.f, best = 0.f;
@@ -197,8 +224,9 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
     atomicAdd(&s_cnt[3], c_valid);
   }
   __syncthreads();
-  if (threadIdx.x < 3) counters[n * 3 + threadIdx.x] = s_cnt[threadIdx.x];
-  if (threadIdx.x == 3) atomicAdd(counters + num_images * 3, s_cnt[3]);  // integer: order independent
+  // integer sums: order independent
+  if (threadIdx.x < 3) atomicAdd(counters + n * 3 + threadIdx.x, s_cnt[threadIdx.x]);
+  if (threadIdx.x == 3) atomicAdd(counters + num_images * 3, s_cnt[3]);
 }
 
 // Deterministic grid-wide float sum: per-CTA partial -> the last CTA to arrive adds the partials
@@ -483,6 +511,25 @@ SumWs carve_sum_ws(void* workspace) {
 }
 }  // namespace
 
+namespace {
+template <typename... Args>
+cudaError_t launch_assign(int num_images, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(num_images * kAssignCluster));
+  cfg.blockDim = dim3(kAssignThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kAssignCluster;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, refine_assign_kernel, args...);
+}
+}  // namespace
+
 extern "C" size_t jtsm_refine_workspace_bytes(void) { return 16 + kMaxSumCtas * 4 + 512; }
 
 extern "C" int jtsm_refine_assign(
@@ -505,16 +552,15 @@ extern "C" int jtsm_refine_assign(
   if (!seg_offsets || !img_cls_offsets || !matched_idx || !gt_classes || !gt_weights ||
       !gt_scores || !gt_boxes || !loss_weights)
     return JTSM_ERR_INVALID_ARGUMENT;
-  const size_t smem = (size_t)max_classes_per_image * (16 + 4 * 4) + 16;
+  const size_t smem = (size_t)max_classes_per_image * (16 + 6 * 4) + 16;
   if (smem > 200 * 1024) return JTSM_ERR_UNSUPPORTED;
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(refine_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   MatcherParams mp{iou_t0, iou_t1, label0, label1, label2, num_thresholds};
-  refine_assign_kernel<<<num_images, kAssignThreads, smem, st>>>(
-      prev_scores, score_stride, prev_boxes, boxes_per_row, proposals, seg_offsets, num_classes,
-      img_cls_offsets, img_cls_ids, img_scores, mp, pgt_boxes, pgt_classes, pgt_scores, pgt_weights,
-      matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes, loss_weights, counters,
-      num_images);
+  launch_assign(num_images, smem, st, prev_scores, score_stride, prev_boxes, boxes_per_row, proposals, seg_offsets,
+                num_classes, img_cls_offsets, img_cls_ids, img_scores, mp, pgt_boxes, pgt_classes, pgt_scores,
+                pgt_weights, matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes, loss_weights,
+                counters, num_images);
   count_launch();
   return cuda_status();
 }
@@ -538,16 +584,16 @@ extern "C" int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_cl
     return JTSM_ERR_INVALID_ARGUMENT;
   if (max_seeds_per_image > 0 && (!pgt_boxes || !pgt_classes || !pgt_scores || !pgt_weights))
     return JTSM_ERR_INVALID_ARGUMENT;
-  const size_t smem = (size_t)max_seeds_per_image * (16 + 4 * 4) + 16;
+  const size_t smem = (size_t)max_seeds_per_image * (16 + 6 * 4) + 16;
   if (smem > 200 * 1024) return JTSM_ERR_UNSUPPORTED;
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(refine_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   MatcherParams mp{iou_t0, iou_t1, label0, label1, label2, num_thresholds};
-  refine_assign_kernel<<<num_images, kAssignThreads, smem, st>>>(
-      nullptr, 0, nullptr, 1, proposals, seg_offsets, num_classes, seed_offsets, nullptr, nullptr, mp,
-      const_cast<float*>(pgt_boxes), const_cast<long long*>(pgt_classes), const_cast<float*>(pgt_scores),
-      const_cast<float*>(pgt_weights), matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes,
-      loss_weights, counters, num_images);
+  launch_assign(num_images, smem, st, (const float*)nullptr, 0, (const float*)nullptr, 1, proposals, seg_offsets,
+                num_classes, seed_offsets, (const long long*)nullptr, (const float*)nullptr, mp,
+                const_cast<float*>(pgt_boxes), const_cast<long long*>(pgt_classes), const_cast<float*>(pgt_scores),
+                const_cast<float*>(pgt_weights), matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes,
+                loss_weights, counters, num_images);
   count_launch();
   return cuda_status();
 }

@@ -225,9 +225,9 @@ def refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_cl
     thr = list(iou_thresholds)
     lab = list(iou_labels)
     assert len(thr) in (1, 2) and len(lab) == len(thr) + 1
-    # one zero-filled arena per dtype instead of 13 small fills
-    fl = torch.zeros(ctot * 6 + r * 8 + (r if want_iou else 0), dtype=torch.float32, device=dev)
-    il = torch.zeros(ctot + 2 * r, dtype=torch.int64, device=dev)
+    # one arena per dtype instead of 13 small tensors; the kernel writes every element, so no fill
+    fl = torch.empty(ctot * 6 + r * 8 + (r if want_iou else 0), dtype=torch.float32, device=dev)
+    il = torch.empty(ctot + 2 * r, dtype=torch.int64, device=dev)
     fo, io = [0], [0]
 
     def f(*shape):
@@ -277,8 +277,8 @@ def refine_match(pgt_boxes, pgt_classes, pgt_scores, pgt_weights, seeds_per_imag
     soff = segment_offsets(seeds_per_image, dev)
     thr, lab = list(iou_thresholds), list(iou_labels)
     assert len(thr) in (1, 2) and len(lab) == len(thr) + 1
-    fl = torch.zeros(r * 8 + (r if want_iou else 0), dtype=torch.float32, device=dev)
-    il = torch.zeros(2 * r, dtype=torch.int64, device=dev)
+    fl = torch.empty(r * 8 + (r if want_iou else 0), dtype=torch.float32, device=dev)
+    il = torch.empty(2 * r, dtype=torch.int64, device=dev)
     out = dict(gt_boxes=fl[:4 * r].view(r, 4), gt_weights=fl[4 * r:5 * r], gt_scores=fl[5 * r:6 * r],
                loss_weights=fl[6 * r:7 * r], matched_iou=fl[8 * r:9 * r] if want_iou else None,
                matched_idx=il[:r], gt_classes=il[r:], counters=torch.empty(n * 3 + 1, dtype=torch.int32, device=dev))
