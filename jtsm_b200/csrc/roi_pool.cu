@@ -321,7 +321,8 @@ bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, 
   const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
   return (algo == 0 || algo == 3) && !tuning("roi_pool_force_gmem", 0) && hw < 65535 &&
          rmq_smem_bytes((int)hw) <= 227 * 1024 && (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL &&
-         (long long)num_rois * PH * PW * PH * PW < 0xFFFFFFFFLL;  // exact magic division of a bin id by PH*PW
+         (long long)num_rois * PH * PW * PH * PW < 0xFFFFFFFFLL &&  // exact magic division of a bin id by PH*PW
+         (long long)num_rois * 64 < 0x7FFFFFFFLL;                  // chunk bounds in 32 bits (chunks <= 64)
 }
 
 template <typename T> constexpr bool dtype_is_f32() { return false; }
@@ -366,6 +367,7 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
       const int cap = num_rois / 64 > 1 ? num_rois / 64 : 1;
       chunks = chunks > cap ? cap : (chunks < 1 ? 1 : chunks);
     }
+    if (chunks > 64) chunks = 64;
     const int items = planes * chunks;
     const int grid = items < max_grid ? items : max_grid;
     roi_pool_fwd_rmq_kernel<T, A><<<grid, kRmqThreads, smem, st>>>(

@@ -55,41 +55,39 @@ __device__ __forceinline__ RmqCand rmq_best(const RmqCand a, const RmqCand b) {
   return take_b ? b : a;
 }
 
-// One doubling step: dst[p] = better of src[p] and src[p + off].  No bounds logic: a partner past
-// the end of the plane is clamped to the last cell, and an entry whose window would leave its row
-// or the plane is simply never queried -- every query window lies inside its bin (and every valid
-// entry is built from two valid halves), so only entries of in-plane windows have to be right.
-__device__ __forceinline__ void rmq_build_level(const float* plane, const unsigned short* src,
-                                                unsigned short* dst, int hw, int off) {
+// One build phase: from level (k, k) in `src` (window 2^k x 2^k, s = 2^k) to the three levels (k, k+1), (k+1, k)
+// and (k+1, k+1): the four (k, k) windows at p, p + s, p + s*W, p + s*W + s give all three with 4 index loads,
+// 4 value loads and 3 comparisons.  kIdentity: level (0, 0) is the cell itself, no index loads.
+// No bounds logic: a partner past the end of the plane is clamped to the last cell, and an entry whose window
+// would leave its row or the plane is simply never queried -- every query window lies inside its bin (and every
+// valid entry is built from valid ones), so only entries of in-plane windows have to be right.
+template <bool kIdentity>
+__device__ __forceinline__ void rmq_build_phase(const float* plane, const unsigned short* src, unsigned short* d_w,
+                                                unsigned short* d_h, unsigned short* d_hw, int hw, int W, int s) {
   const int last = hw - 1;
-#pragma unroll 4
+#pragma unroll 2
   for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
-    const unsigned a = src[p];
-    const unsigned b = src[min(p + off, last)];
-    const float va = plane[a], vb = plane[b];
-    const bool take_b = (vb > va) || (vb == va && b < a);
-    dst[p] = (unsigned short)(take_b ? b : a);
+    const int pb = min(p + s, last), pc = min(p + s * W, last), pd = min(p + s * W + s, last);
+    const RmqCand a = rmq_load(plane, kIdentity ? (unsigned)p : (unsigned)src[p]);
+    const RmqCand b = rmq_load(plane, kIdentity ? (unsigned)pb : (unsigned)src[pb]);
+    const RmqCand c = rmq_load(plane, kIdentity ? (unsigned)pc : (unsigned)src[pc]);
+    const RmqCand d = rmq_load(plane, kIdentity ? (unsigned)pd : (unsigned)src[pd]);
+    const RmqCand ab = rmq_best(a, b), cd = rmq_best(c, d);
+    d_w[p] = (unsigned short)ab.i;                 // (k, k+1): wider
+    d_h[p] = (unsigned short)rmq_best(a, c).i;     // (k+1, k): taller
+    d_hw[p] = (unsigned short)rmq_best(ab, cd).i;  // (k+1, k+1)
   }
 }
 
 // The 9 non-identity tables of the plane in `plane` (slot 0, the identity level, is written once per kernel);
-// all threads of the CTA call it, after a barrier that makes the plane visible.
+// all threads of the CTA call it, after a barrier that makes the plane visible.  Slot of level (kh, kw) = kh + 2*kw.
 __device__ __forceinline__ void rmq_build_tables(const float* plane, unsigned short* tabs, int hw, int W) {
 #define TAB(s) (tabs + (size_t)(s) * hw)
-  rmq_build_level(plane, TAB(0), TAB(2), hw, 1);      // (0,1)
-  rmq_build_level(plane, TAB(0), TAB(1), hw, W);      // (1,0)
+  rmq_build_phase<true>(plane, TAB(0), TAB(2), TAB(1), TAB(3), hw, W, 1);   // (0,1) (1,0) (1,1)
   __syncthreads();
-  rmq_build_level(plane, TAB(2), TAB(3), hw, W);      // (1,1)
+  rmq_build_phase<false>(plane, TAB(3), TAB(5), TAB(4), TAB(6), hw, W, 2);  // (1,2) (2,1) (2,2)
   __syncthreads();
-  rmq_build_level(plane, TAB(3), TAB(5), hw, 2);      // (1,2)
-  rmq_build_level(plane, TAB(3), TAB(4), hw, 2 * W);  // (2,1)
-  __syncthreads();
-  rmq_build_level(plane, TAB(5), TAB(6), hw, 2 * W);  // (2,2)
-  __syncthreads();
-  rmq_build_level(plane, TAB(6), TAB(8), hw, 4);      // (2,3)
-  rmq_build_level(plane, TAB(6), TAB(7), hw, 4 * W);  // (3,2)
-  __syncthreads();
-  rmq_build_level(plane, TAB(8), TAB(9), hw, 4 * W);  // (3,3)
+  rmq_build_phase<false>(plane, TAB(6), TAB(8), TAB(7), TAB(9), hw, W, 4);  // (2,3) (3,2) (3,3)
   __syncthreads();
 #undef TAB
 }
@@ -158,11 +156,10 @@ __device__ __forceinline__ RmqCand rmq_query_fast(unsigned plane_s, unsigned bas
 struct RmqItem {
   int n, c, r0, nr;
 };
-// (plane, chunk) item -> image, channel and RoI range; nr = 0 when the image has no RoIs
-__device__ __forceinline__ RmqItem rmq_item(int item, int chunks, int channels, const PoolWorkspace& ws, int& nc) {
+// (plane, chunk) -> image, channel and RoI range; nr = 0 when the image has no RoIs.  32-bit arithmetic only
+// (the launcher bounds num_rois * chunks).
+__device__ __forceinline__ RmqItem rmq_item(int nc, int chunk, int chunks, int channels, const PoolWorkspace& ws) {
   RmqItem it;
-  nc = item / chunks;
-  const int chunk = item - nc * chunks;
   it.n = nc / channels;
   it.c = nc - it.n * channels;
   const int first = ws.first[it.n];
@@ -170,9 +167,9 @@ __device__ __forceinline__ RmqItem rmq_item(int item, int chunks, int channels, 
   it.r0 = 0;
   it.nr = 0;
   if (first <= last) {
-    const int len = last - first + 1;
-    it.r0 = first + (int)(((long long)len * chunk) / chunks);
-    it.nr = first + (int)(((long long)len * (chunk + 1)) / chunks) - it.r0;
+    const unsigned len = (unsigned)(last - first + 1);
+    it.r0 = first + (int)(len * (unsigned)chunk / (unsigned)chunks);
+    it.nr = first + (int)(len * (unsigned)(chunk + 1) / (unsigned)chunks) - it.r0;
   }
   return it;
 }
@@ -287,9 +284,17 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
   const int t_per = tail_items / G, t_rem = tail_items % G;
   const int t0 = blockIdx.x * t_per + min((int)blockIdx.x, t_rem);
   const int my_items = full + t_per + ((int)blockIdx.x < t_rem ? 1 : 0);
-  auto item_id = [&](int idx) {  // idx-th item of this CTA -> global item id = plane * chunks + chunk
-    if (idx < full) return ((idx / chunks) * G + (int)blockIdx.x) * chunks + idx % chunks;
-    return tail_base + t0 + (idx - full);
+  // (plane, chunk) of this CTA's idx-th item, stepped without divisions
+  int nc = full > 0 ? (int)blockIdx.x : (tail_base + t0) / chunks;
+  int chunk = full > 0 ? 0 : (tail_base + t0) % chunks;
+  auto advance = [&](int idx_next, int& pl, int& ch) {  // (pl, ch) of item idx_next - 1 -> item idx_next
+    if (idx_next == full) {  // first item of the tail range
+      pl = (tail_base + t0) / chunks;
+      ch = (tail_base + t0) % chunks;
+    } else if (++ch == chunks) {
+      ch = 0;
+      pl += idx_next < full ? G : 1;
+    }
   };
   int cur_plane = -1, in_flight = -1;  // plane whose tables are resident / plane being fetched into `spare`
   int r_lo = 0, r_hi = 0;              // RoIs served with the resident tables
@@ -297,8 +302,8 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
   for (int p = threadIdx.x; p < hw; p += kRmqThreads) tabs[p] = (unsigned short)p;  // identity level (0,0), slot 0
 
   for (int idx = 0; idx < my_items; ++idx) {
-    int nc;
-    const RmqItem it = rmq_item(item_id(idx), chunks, channels, ws, nc);
+    if (idx > 0) advance(idx, nc, chunk);
+    const RmqItem it = rmq_item(nc, chunk, chunks, channels, ws);
     if (nc != cur_plane) {
       if (cur_plane >= 0)
         rmq_slow_pass<T, A>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
@@ -320,10 +325,14 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
       rmq_build_tables(plane, tabs, hw, W);
       // the next plane this CTA will serve, if any: fetch it behind the queries of this one
       if (async) {
-        int j = idx + 1;
-        while (j < my_items && item_id(j) / chunks == nc) ++j;
+        int j = idx + 1, pl = nc, ch = chunk;
+        while (j < my_items) {
+          advance(j, pl, ch);
+          if (pl != nc) break;
+          ++j;
+        }
         if (j < my_items) {
-          in_flight = item_id(j) / chunks;
+          in_flight = pl;
           plane_prefetch_async(input + (size_t)in_flight * hw, spare, hw);
         }
       }
