@@ -361,11 +361,19 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
     }
     const int per_sm = (int)((227 * 1024) / (smem + 1024)) >= 2 ? 2 : 1;  // 1024-thread CTAs
     const int max_grid = num_sms() * per_sm;
+    // RoI chunks per plane: the planes of the last, partial round (planes % grid) are cut into chunks and dealt to
+    // all CTAs, so the round costs ceil(tail_planes * chunks / grid) / chunks plane-times; every extra chunk adds
+    // a little per-item overhead (and a table build when a CTA's range crosses planes).  Pick the cheapest.
     int chunks = tuning("roi_pool_splits", 0);
     if (chunks <= 0) {
-      chunks = (16 * max_grid + planes - 1) / planes;
-      const int cap = num_rois / 64 > 1 ? num_rois / 64 : 1;
-      chunks = chunks > cap ? cap : (chunks < 1 ? 1 : chunks);
+      const int cap = num_rois / 64 > 1 ? (num_rois / 64 < 64 ? num_rois / 64 : 64) : 1;
+      const int tail = planes % max_grid;
+      double best = 1e30;
+      chunks = 1;
+      for (int c = 1; c <= cap && tail > 0; ++c) {
+        const double cost = (double)((tail * c + max_grid - 1) / max_grid) / c + 0.01 * c;
+        if (cost < best - 1e-9) best = cost, chunks = c;
+      }
     }
     if (chunks > 64) chunks = 64;
     const int items = planes * chunks;
