@@ -201,28 +201,46 @@ def run_b200(a):
     t_wall = time.perf_counter() - t_wall0
     launches = step.launches_per_step * a.steps if use_graph else _lib.launch_count() - lc0
     dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
-    # dominant kernel: CUDA events around its launch, same inputs, L2 flushed, eager (events cannot be
-    # recorded inside a captured graph)
+    # dominant op (RoIPool forward = 2 memsets + prep kernel + pooling kernel): its own CUDA graph, CUDA events
+    # around each replay, same inputs, L2 flushed (events cannot be recorded inside the step's captured graph)
+    step.capture_dominant(resident)
     kev = []
     for i in range(a.steps):
         flush.zero_()
-        kev.append(step.run(resident, time_dominant=True))
+        kev.append(step.time_dominant())
     barrier()
     dom_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / len(kev)
 
     # ---------------- end-to-end from host buffers (e2e) ----------------
-    from_host = step.replay_from_host if use_graph else step.run_from_host
-    for _ in range(3):
-        from_host(host)
-    barrier()
-    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
-    for i in range(a.steps):
-        flush.zero_()
-        ev2[i][0].record()
-        from_host(host)  # ends with a blocking D2H of the results
-        ev2[i][1].record()
-    barrier()
-    e2e_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev2)
+    # Every step uploads its inputs from pinned host memory and downloads its results; with the CUDA-graph step
+    # the public streaming call (HotPathStep.run_stream) double-buffers, so step i + 1's H2D and step i - 1's D2H
+    # overlap step i's kernels.  The L2 flush stays between steps (on the compute stream, inside the timed region).
+    if use_graph:
+        step.prepare_stream(host)
+        seen = []
+        step.run_stream([host] * 3, before_step=flush.zero_)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step.run_stream([host] * a.steps, consume=lambda i, out: seen.append(float(out[0][0])), before_step=flush.zero_)
+        e1.record()
+        barrier()
+        assert len(seen) == a.steps
+        e2e_ms = e0.elapsed_time(e1)
+        e2e_mode = "pipelined: H2D(i+1) | step(i) | D2H(i-1) on three streams, two buffer sets"
+    else:
+        for _ in range(3):
+            step.run_from_host(host)
+        barrier()
+        ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+        for i in range(a.steps):
+            flush.zero_()
+            ev2[i][0].record()
+            step.run_from_host(host)  # ends with a blocking D2H of the results
+            ev2[i][1].record()
+        barrier()
+        e2e_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev2)
+        e2e_mode = "sequential: H2D, step, blocking D2H"
 
     clocks = sampler.stop() if rank == 0 else None
     tm = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
@@ -245,7 +263,8 @@ def run_b200(a):
                        "l2": "flushed (256 MiB write) between timed steps", "stages": step.stages(),
                        "launch": "cuda_graph_replay" if use_graph else "eager"},
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes()},
+                    "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes(),
+                    "mode": e2e_mode},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": step.dominant_kernel(), "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "peak_source": peak_src, "traffic": step.ncu_traffic(wl["name"] if a.dtype == "fp32" else None),

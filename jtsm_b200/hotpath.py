@@ -80,24 +80,39 @@ class HotPathStep:
         return rec["dram_bytes_per_launch"] if rec else None
 
     # ------------------------------------------------------------------ the step
-    def run(self, d, time_dominant=False):
-        x, rois = d["feat"], d["rois"]
+    def pool_forward(self, d):
+        x = d["feat"]
         adt = torch.int16 if x.shape[2] * x.shape[3] < 65535 else torch.int32
-        if time_dominant:
-            # keep the GPU busy while the host enqueues the op, so the events bracket back-to-back device
-            # work (memsets, prep kernel, pooling kernel) and not the host's launch latency
-            torch.cuda._sleep(2_000_000)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-        pooled, argmax = ops.roi_pool_forward(x, rois, self.scale, self.P, row_scale=d["row_scale"], argmax_dtype=adt)
-        if time_dominant:
-            e1.record()
+        return ops.roi_pool_forward(x, d["rois"], self.scale, self.P, row_scale=d["row_scale"], argmax_dtype=adt)
+
+    def capture_dominant(self, d):
+        """The dominant op (RoIPool forward: two memsets, prep kernel, pooling kernel) alone in a CUDA graph, so it
+        can be timed with events without host launch gaps, exactly as it runs inside the step's graph."""
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self.pool_forward(d)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.dom_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.dom_graph):
+            self._dom_out = self.pool_forward(d)
+
+    def time_dominant(self):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        self.dom_graph.replay()
+        e1.record()
+        return e0, e1
+
+    def run(self, d):
+        x, rois = d["feat"], d["rois"]
+        pooled, argmax = self.pool_forward(d)
         cfg = self.cfg
         h = heads.head_step(d["mil_cls"], d["mil_det"], d["ref_logits"], d["ref_deltas"], d["proposals"], self.counts,
                             self.labels, cfg["K"], d["labels_onehot"], reg=cfg["reg"])
         grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=d["row_scale"])
         self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
-        return (e0, e1) if time_dominant else None
 
     # ------------------------------------------------------------------ CUDA graph of the step
     def capture(self, d):
@@ -148,6 +163,70 @@ class HotPathStep:
         out = [t.to("cpu") for t in self.results(self.graph_last)]
         self._d2h = sum(t.numel() * t.element_size() for t in out)
         return out
+
+    # ------------------------------------------------------------------ pipelined stream of steps from host memory
+    def prepare_stream(self, host):
+        """Two captured copies of the step (two sets of static device buffers) + pinned result buffers, so that
+        step i + 1's inputs upload and step i - 1's results download while step i computes."""
+        self.slots = []
+        for _ in range(2):
+            d = self.upload(host)
+            torch.cuda.synchronize()
+            graph = self.capture(d)
+            res = self.results(self.graph_last)
+            self.slots.append(dict(graph=graph, inputs=d, last=self.graph_last,
+                                   out=[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res],
+                                   ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event()))
+        self.copy_stream, self.d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
+        self._d2h = sum(t.numel() * t.element_size() for t in self.slots[0]["out"])
+
+    def run_stream(self, host_batches, consume=None, before_step=None):
+        """Run one step per element of `host_batches` (dicts of pinned host tensors as from pin_host_inputs).
+        Per step: H2D of its inputs on a copy stream, graph replay on the current stream, D2H of its results
+        (losses, pseudo-labels, counters) into pinned buffers on a third stream; `consume(i, results)` is called on
+        the host once step i's results have landed (one step behind the submission)."""
+        comp = torch.cuda.current_stream()
+        self.copy_stream.wait_stream(comp)
+        n = 0
+        for i, host in enumerate(host_batches):
+            sl = self.slots[i % 2]
+            with torch.cuda.stream(self.copy_stream):
+                if i >= 2:
+                    self.copy_stream.wait_event(sl["ev_done"])  # the slot's previous step no longer reads its inputs
+                for k, v in host.items():
+                    if not k.startswith("_"):
+                        sl["inputs"][k].copy_(v, non_blocking=True)
+                sl["ev_in"].record(self.copy_stream)
+            comp.wait_event(sl["ev_in"])
+            if i >= 2:
+                comp.wait_event(sl["ev_out"])  # the slot's previous results have left the device
+            if before_step is not None:
+                before_step()
+            d = sl["inputs"]
+            d["row_scale"].copy_(d["objectness"] + 1.0)
+            d["proposals"].copy_(d["rois"][:, 1:])
+            sl["graph"].replay()
+            res = self.results(sl["last"])
+            sl["ev_done"].record(comp)
+            with torch.cuda.stream(self.d2h_stream):
+                self.d2h_stream.wait_event(sl["ev_done"])
+                for dst, src in zip(sl["out"], res):
+                    dst.copy_(src, non_blocking=True)
+                    src.record_stream(self.d2h_stream)
+                sl["ev_out"].record(self.d2h_stream)
+            if i >= 1:
+                prev = self.slots[(i - 1) % 2]
+                prev["ev_out"].synchronize()
+                if consume is not None:
+                    consume(i - 1, prev["out"])
+            n = i + 1
+        if n:
+            lastslot = self.slots[(n - 1) % 2]
+            lastslot["ev_out"].synchronize()
+            if consume is not None:
+                consume(n - 1, lastslot["out"])
+            comp.wait_event(lastslot["ev_out"])  # so that an event recorded on `comp` now covers the last D2H
+        return n
 
     def run_from_host(self, host):
         d = self.upload(host)
