@@ -22,30 +22,42 @@ class HotPathStep:
 
     # ------------------------------------------------------------------ inputs
     def pin_host_inputs(self, wl):
-        host = dict(
-            feat=wl["feat"].to(self.dtype).contiguous().pin_memory(),
-            rois=wl["rois"].contiguous().pin_memory(),
-            objectness=wl["objectness"].contiguous().pin_memory(),
-            mil_cls=wl["mil_cls"].contiguous().pin_memory(),
-            mil_det=wl["mil_det"].contiguous().pin_memory(),
-        )
-        for k, t in enumerate(wl["ref_logits"]):
-            host["ref_logits%d" % k] = t.contiguous().pin_memory()
-        for k, t in enumerate(wl["ref_deltas"]):
-            host["ref_deltas%d" % k] = t.contiguous().pin_memory()
+        """Host-side inputs of one step as views of ONE pinned arena (host["__arena"]), so a step's upload is a
+        single copy instead of ten small ones."""
         cfg = self.cfg
         self.counts = [int(b.shape[0]) for b in wl["boxes"]]
         self.labels = wl["labels"]
         oh = torch.zeros(len(self.counts), cfg["K"])
         for i, l in enumerate(self.labels):
             oh[i, l] = 1.0
-        host["labels_onehot"] = oh.pin_memory()
+        src = dict(feat=wl["feat"].to(self.dtype), rois=wl["rois"], objectness=wl["objectness"], mil_cls=wl["mil_cls"],
+                   mil_det=wl["mil_det"], labels_onehot=oh)
+        for k, t in enumerate(wl["ref_logits"]):
+            src["ref_logits%d" % k] = t
+        for k, t in enumerate(wl["ref_deltas"]):
+            src["ref_deltas%d" % k] = t
+        self._layout, off = [], 0
+        for k, t in src.items():
+            nbytes = t.numel() * t.element_size()
+            self._layout.append((k, off, nbytes, t.dtype, tuple(t.shape)))
+            off = (off + nbytes + 255) & ~255
+        arena = torch.empty(off, dtype=torch.uint8).pin_memory()
+        host = self._views(arena)
+        for k, t in src.items():
+            host[k].copy_(t)
+        host["__arena"] = arena
         # gradient handed over by fc6's backward lives on the device in the real system
         host["_grad_pooled"] = synth.expand_grad_tile(wl["grad_tile"].to(self.dev), wl["rois"].shape[0]).to(self.dtype)
         return host
 
+    def _views(self, arena):
+        return {k: arena[off:off + nbytes].view(dt).view(shape) for k, off, nbytes, dt, shape in self._layout}
+
     def upload(self, host):
-        res = {k: (v.to(self.dev, non_blocking=True) if not k.startswith("_") else v) for k, v in host.items()}
+        arena = host["__arena"].to(self.dev, non_blocking=True)
+        res = self._views(arena)
+        res["__arena"] = arena
+        res["_grad_pooled"] = host["_grad_pooled"]
         res["row_scale"] = res["objectness"] + 1.0
         res["proposals"] = res["rois"][:, 1:].contiguous()
         res["ref_logits"] = [res["ref_logits%d" % k] for k in range(self.cfg["Kr"])]
@@ -53,7 +65,7 @@ class HotPathStep:
         return res
 
     def h2d_bytes(self, host):
-        return sum(v.numel() * v.element_size() for k, v in host.items() if not k.startswith("_"))
+        return sum(nbytes for _, _, nbytes, _, _ in self._layout)
 
     def d2h_bytes(self):
         return self._d2h
@@ -154,9 +166,7 @@ class HotPathStep:
     def replay_from_host(self, host):
         """H2D of the step's inputs into the graph's static buffers, replay, blocking D2H of the results."""
         d = self.static_inputs
-        for k, v in host.items():
-            if not k.startswith("_"):
-                d[k].copy_(v, non_blocking=True)
+        d["__arena"].copy_(host["__arena"], non_blocking=True)
         d["row_scale"].copy_(d["objectness"] + 1.0)
         d["proposals"].copy_(d["rois"][:, 1:])
         self.graph.replay()
@@ -193,9 +203,7 @@ class HotPathStep:
             with torch.cuda.stream(self.copy_stream):
                 if i >= 2:
                     self.copy_stream.wait_event(sl["ev_done"])  # the slot's previous step no longer reads its inputs
-                for k, v in host.items():
-                    if not k.startswith("_"):
-                        sl["inputs"][k].copy_(v, non_blocking=True)
+                sl["inputs"]["__arena"].copy_(host["__arena"], non_blocking=True)  # one copy: all inputs of the step
                 sl["ev_in"].record(self.copy_stream)
             comp.wait_event(sl["ev_in"])
             if i >= 2:
