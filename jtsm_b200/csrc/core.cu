@@ -20,7 +20,8 @@ std::map<std::string, int>& tuning_map() {
       {"roi_pool_bwd_algo", 0},    // 0 = auto
       {"roi_pool_fwd_algo", 0},    // 0 = auto, 1 = direct smem scan, 2 = gmem scan, 3 = range-max tables
       {"roi_pool_fwd_async", 1},   // 1 = fetch the next plane with cp.async when a second plane buffer fits
-      {"roi_align_bwd_algo", 0},   // 0 = auto
+      {"roi_align_bwd_algo", 0},   // 0 = auto (separable: column kernel for PH <= 16, else cell kernel), 1 = one RED per tap, 2 = cell kernel
+      {"roi_align_fwd_algo", 0},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
       {"roi_align_force_gmem", 0},
   };
   return m;

@@ -21,11 +21,24 @@ struct AlignGeom {  // ROIAlign_cpu.cpp:139-166
 };
 
 struct AlignWorkspace {
-  AlignGeom* geom;  // [R]
+  AlignGeom* geom;  // [R]   (geom.pad = 1 when the RoI has tap tables)
   int* first;       // [batch]
   int* neg_last;    // [batch]
   int* ungrouped;   // [1]
+  float* taps;      // [R][tap_stride]: PH * grid_h row sample coordinates, then PW * grid_w column ones (forward)
 };
+
+// Largest sampling grid per axis that gets a table, and the table entries of one RoI.  A RoI that lies inside the
+// map has grid <= ceil(L / P) with the adaptive grid; bigger grids (boxes far outside the map, large fixed
+// sampling ratios on tiny maps) take the direct path.  P * cap <= L + 2 * P, which bounds the workspace without
+// knowing P (jtsm_roi_align_workspace_bytes has no pooled-size arguments; P <= 64).
+__host__ __device__ inline int align_grid_cap(int L, int P) { return L / P + 2; }
+__host__ __device__ inline int align_tap_stride(int H, int W, int PH, int PW) {
+  return PH * align_grid_cap(H, PH) + PW * align_grid_cap(W, PW);
+}
+inline size_t align_tap_bytes(int H, int W, int num_rois) {
+  return align_up((size_t)num_rois * ((size_t)H + W + 4 * 64) * sizeof(float), 256);
+}
 
 inline size_t align_workspace_bytes(int batch, int num_rois) {
   return align_up((size_t)num_rois * sizeof(AlignGeom), 256) + align_up((size_t)batch * 8 + 16, 256) + 256;
@@ -38,6 +51,8 @@ inline AlignWorkspace carve_align_workspace(void* ws, int batch, int num_rois) {
   w.first = (int*)p;
   w.neg_last = w.first + batch;
   w.ungrouped = w.neg_last + batch;
+  p += align_up((size_t)batch * 8 + 16, 256);
+  w.taps = (float*)p;  // only valid when the caller sized the workspace for the forward pass
   return w;
 }
 
@@ -120,6 +135,50 @@ __device__ __forceinline__ float sample_coord(float start, int p, float bin, int
                    __fdiv_rn(__fmul_rn(__fadd_rn((float)i, 0.5f), bin), (float)grid));
 }
 
+// Sample coordinate tables.  Everything about a sample that needs a division -- start + p * bin + (i + .5) * bin /
+// grid -- is channel independent, so the forward kernel reads it from a per-RoI table instead of recomputing it for
+// each of the C planes: one float per sample position and axis, already clamped at 0, kTapOutside when the sample is
+// off the map.  (A 16-byte entry with the two cell offsets and both weights was tried first: the LDG.128 per sample
+// costs 4 LSU wavefronts and the kernel is LSU bound -- profiles/r1q_roi_align.md; 4-byte entries cost one.)
+constexpr float kTapOutside = -2.f;
+__device__ __forceinline__ float align_tap_coord(float c, int L) {
+  if (c < -1.f || c > (float)L) return kTapOutside;
+  return c <= 0.f ? 0.f : c;
+}
+// cells and weights of a table coordinate: the tail of bilinear_taps for one axis
+__device__ __forceinline__ void align_tap_cells(float c, int L, int& lo, int& hi, float& h, float& l) {
+  lo = (int)c;
+  if (lo >= L - 1) {
+    hi = lo = L - 1;
+    c = (float)lo;
+  } else {
+    hi = lo + 1;
+  }
+  l = __fsub_rn(c, (float)lo);
+  h = __fsub_rn(1.f, l);
+}
+
+// Tables of every RoI whose grids fit (one CTA per RoI); marks the RoI in geom.pad.
+__global__ void roi_align_taps_kernel(int num_rois, int H, int W, int PH, int PW, AlignWorkspace ws) {
+  const int r = blockIdx.x;
+  const AlignGeom g = ws.geom[r];
+  if (g.batch < 0 || g.grid_h <= 0 || g.grid_w <= 0 || g.grid_h > align_grid_cap(H, PH) ||
+      g.grid_w > align_grid_cap(W, PW))
+    return;
+  float* t = ws.taps + (size_t)r * align_tap_stride(H, W, PH, PW);
+  const int ny = PH * g.grid_h, nx = PW * g.grid_w;
+  for (int e = threadIdx.x; e < ny + nx; e += blockDim.x) {
+    if (e < ny) {
+      const int p = e / g.grid_h, i = e - p * g.grid_h;
+      t[e] = align_tap_coord(sample_coord(g.start_h, p, g.bin_h, i, g.grid_h), H);
+    } else {
+      const int p = (e - ny) / g.grid_w, i = (e - ny) - p * g.grid_w;
+      t[e] = align_tap_coord(sample_coord(g.start_w, p, g.bin_w, i, g.grid_w), W);
+    }
+  }
+  if (threadIdx.x == 0) ws.geom[r].pad = 1;
+}
+
 constexpr int kAlignThreads = 512;
 
 // grid: persistent CTAs over (plane, chunk) items.  kSmem: plane staged in shared memory.
@@ -134,6 +193,7 @@ roi_align_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, in
   const int step_r = kAlignThreads / PP, step_b = kAlignThreads - step_r * PP;
   const int rl_init = threadIdx.x / PP, bin_init = threadIdx.x - rl_init * PP;
   const bool ungrouped = *ws.ungrouped != 0;
+  const int tap_stride = align_tap_stride(H, W, PH, PW);
   const int per = num_items / gridDim.x, rem = num_items % gridDim.x;
   const int i0 = blockIdx.x * per + min((int)blockIdx.x, rem);
   const int i1 = i0 + per + ((int)blockIdx.x < rem ? 1 : 0);
@@ -173,6 +233,38 @@ roi_align_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, in
       if (ungrouped && g.batch != n) continue;
       const float count = (float)max(g.grid_h * g.grid_w, 1);
       float v = 0.f;
+      if (g.pad) {  // coordinate tables: no divisions left; products and sums in the reference's order
+        const float* ty = ws.taps + (size_t)r * tap_stride + ph * g.grid_h;
+        const float* tx = ws.taps + (size_t)r * tap_stride + PH * g.grid_h + pw * g.grid_w;
+        for (int iy = 0; iy < g.grid_h; ++iy) {
+          const float y = __ldg(ty + iy);
+          if (y < 0.f) continue;  // adding the 0 of an outside sample changes nothing (v is never -0)
+          int yl, yh;
+          float hy, ly;
+          align_tap_cells(y, H, yl, yh, hy, ly);
+          yl *= W, yh *= W;
+          for (int ix = 0; ix < g.grid_w; ++ix) {
+            const float x = __ldg(tx + ix);
+            if (x < 0.f) continue;
+            int xl, xh;
+            float hx, lx;
+            align_tap_cells(x, W, xl, xh, hx, lx);
+            float v1, v2, v3, v4;
+            if (kSmem) {
+              v1 = plane_s[yl + xl]; v2 = plane_s[yl + xh]; v3 = plane_s[yh + xl]; v4 = plane_s[yh + xh];
+            } else {
+              v1 = Elem<T>::to_f(__ldg(src + yl + xl)); v2 = Elem<T>::to_f(__ldg(src + yl + xh));
+              v3 = Elem<T>::to_f(__ldg(src + yh + xl)); v4 = Elem<T>::to_f(__ldg(src + yh + xh));
+            }
+            const float w1 = __fmul_rn(hy, hx), w2 = __fmul_rn(hy, lx);
+            const float w3 = __fmul_rn(ly, hx), w4 = __fmul_rn(ly, lx);
+            v = __fadd_rn(v, __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(w1, v1), __fmul_rn(w2, v2)), __fmul_rn(w3, v3)),
+                                       __fmul_rn(w4, v4)));
+          }
+        }
+        output[o] = Elem<T>::from_f(__fdiv_rn(v, count));
+        continue;
+      }
       for (int iy = 0; iy < g.grid_h; ++iy) {
         const float y = sample_coord(g.start_h, ph, g.bin_h, iy, g.grid_h);
         for (int ix = 0; ix < g.grid_w; ++ix) {
@@ -236,6 +328,200 @@ roi_align_bwd_kernel(const T* __restrict__ grad_output, long long sn, long long 
   }
 }
 
+// backward, separable form: the bilinear weight of a sample is (row weight) x (column weight), and both depend on
+// one axis only, so   grad_in[y][x] += 1/count * sum_ph sum_pw  Wy[y][ph] * g[ph][pw] * Wx[x][pw]
+// with Wy[y][ph] = sum of the row weights the samples of bin row ph put on map row y (ROIAlign_cuda.cu:203-306
+// distributes g * w_i / count per sample; same sum, different association -> tolerance like any atomic backward).
+// One CTA per (RoI, channel slice): the two weight matrices are built once (channel independent), the touched
+// rows / columns are compacted, and every touched cell of every channel gets ONE RED instead of one per tap
+// (16 per bin at sampling_ratio 2, 4 * grid^2 per bin with the adaptive grid).
+// dynamic smem: Wy [H][PH] | Wx [W][PW] | row list [H] | column list [W]   (list entry: y | p_lo << 16 | p_hi << 24)
+constexpr int kAlignBwdThreads = 256;
+
+__device__ __forceinline__ void align_axis_weights(float start, float bin, int grid, int P, int L, float* w,
+                                                   int stride, int* list, int* count_out) {
+  // called by one full warp; lane p owns column p of w, so its sequential adds need no atomics
+  const int lane = threadIdx.x & 31;
+  int lo_min = L, hi_max = -1;
+  for (int p = lane; p < P; p += 32) {
+    for (int i = 0; i < grid; ++i) {
+      float c = sample_coord(start, p, bin, i, grid);
+      if (c < -1.f || c > (float)L) continue;
+      if (c <= 0.f) c = 0.f;
+      int lo = (int)c, hi;
+      if (lo >= L - 1) {
+        hi = lo = L - 1;
+        c = (float)lo;
+      } else {
+        hi = lo + 1;
+      }
+      const float l = __fsub_rn(c, (float)lo), h = __fsub_rn(1.f, l);
+      w[lo * stride + p] += h;
+      w[hi * stride + p] += l;
+      lo_min = min(lo_min, lo);
+      hi_max = max(hi_max, hi);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo_min = min(lo_min, __shfl_xor_sync(0xffffffffu, lo_min, o));
+    hi_max = max(hi_max, __shfl_xor_sync(0xffffffffu, hi_max, o));
+  }
+  __syncwarp();
+  int n = 0;
+  for (int base = lo_min; base <= hi_max; base += 32) {
+    const int y = base + lane;
+    int p_lo = P, p_hi = -1;
+    if (y <= hi_max)
+      for (int p = 0; p < P; ++p)
+        if (w[y * stride + p] != 0.f) {
+          p_lo = min(p_lo, p);
+          p_hi = p;
+        }
+    const unsigned m = __ballot_sync(0xffffffffu, p_hi >= 0);
+    if (p_hi >= 0) list[n + __popc(m & ((1u << lane) - 1u))] = y | (p_lo << 16) | (p_hi << 24);
+    n += __popc(m);
+  }
+  if (lane == 0) *count_out = n;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kAlignBwdThreads)
+roi_align_bwd_patch_kernel(const T* __restrict__ grad_output, long long sn, long long sc, long long sh, long long sw,
+                           int channels, int H, int W, int PH, int PW, AlignWorkspace ws,
+                           float* __restrict__ grad_acc) {
+  extern __shared__ float align_bwd_s[];
+  float* wy = align_bwd_s;
+  float* wx = wy + H * PH;
+  int* rows = (int*)(wx + W * PW);
+  int* cols = rows + H;
+  __shared__ int s_n[2];
+  const int r = blockIdx.x;
+  const AlignGeom g = ws.geom[r];
+  if (g.batch < 0 || g.grid_h <= 0 || g.grid_w <= 0) return;
+  for (int i = threadIdx.x; i < H * PH + W * PW; i += kAlignBwdThreads) wy[i] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) align_axis_weights(g.start_h, g.bin_h, g.grid_h, PH, H, wy, PH, rows, &s_n[0]);
+  if (warp == 1) align_axis_weights(g.start_w, g.bin_w, g.grid_w, PW, W, wx, PW, cols, &s_n[1]);
+  __syncthreads();
+  const int nr = s_n[0], nc = s_n[1], cells = nr * nc;
+  if (cells == 0) return;
+  // channel slice of this CTA
+  const int c0 = (int)(((long long)channels * blockIdx.y) / gridDim.y);
+  const int c1 = (int)(((long long)channels * (blockIdx.y + 1)) / gridDim.y);
+  const float inv = __fdiv_rn(1.f, (float)(g.grid_h * g.grid_w));  // unclamped count (ROIAlign_cuda.cu:258)
+  // item = (channel, row entry, column entry), column fastest; stepped by the CTA size without divisions
+  int cc = c0 + threadIdx.x / cells;
+  int rem = threadIdx.x % cells;
+  int jj = rem / nc, kk = rem - jj * nc;
+  const int step_c = kAlignBwdThreads / cells, srem = kAlignBwdThreads % cells;
+  const int step_j = srem / nc, step_k = srem - step_j * nc;
+  const T* gr = grad_output + r * sn;
+  float* acc_b = grad_acc + (size_t)g.batch * channels * H * W;
+  while (cc < c1) {
+    const int ri = rows[jj], ci = cols[kk];
+    const int y = ri & 0xFFFF, p_lo = (ri >> 16) & 0xFF, p_hi = (ri >> 24) & 0xFF;
+    const int x = ci & 0xFFFF, q_lo = (ci >> 16) & 0xFF, q_hi = (ci >> 24) & 0xFF;
+    const T* gp = gr + cc * sc;
+    const float* wyr = wy + y * PH;
+    const float* wxr = wx + x * PW;
+    float sum = 0.f;
+    for (int ph = p_lo; ph <= p_hi; ++ph) {
+      const T* gq = gp + ph * sh;
+      float inner = 0.f;
+      for (int pw = q_lo; pw <= q_hi; ++pw) inner = fmaf(Elem<T>::to_f(gq[pw * sw]), wxr[pw], inner);
+      sum = fmaf(wyr[ph], inner, sum);
+    }
+    if (sum != 0.f) atomicAdd(acc_b + ((size_t)cc * H + y) * W + x, sum * inv);
+    kk += step_k;
+    if (kk >= nc) {
+      kk -= nc;
+      ++jj;
+    }
+    jj += step_j;
+    if (jj >= nr) {
+      jj -= nr;
+      ++cc;
+    }
+    cc += step_c;
+  }
+}
+
+// Same, for PH <= PMAX (8 or 16): a thread owns one touched column x of one channel, folds the column weights into
+// PH partial sums   t[ph] = sum_pw g[ph][pw] * Wx[x][pw]   once (registers), then walks the touched rows with one
+// broadcast read of the row's weights, PMAX FMAs and one RED per cell; neighbouring threads own neighbouring
+// columns, so the REDs of a warp fall into a few sectors.  (Weights outside a row's bins are exact zeros; a
+// non-finite gradient therefore spreads over the RoI's column instead of its own bins only.)
+// dynamic smem: Wy [H][PMAX] | Wx [W][PW] | row list [H] | column list [W]
+template <typename T, int PMAX>
+__global__ void __launch_bounds__(kAlignBwdThreads)
+roi_align_bwd_cols_kernel(const T* __restrict__ grad_output, long long sn, long long sc, long long sh, long long sw,
+                          int channels, int H, int W, int PH, int PW, AlignWorkspace ws,
+                          float* __restrict__ grad_acc) {
+  extern __shared__ __align__(16) float align_bwd_s[];
+  float* wy = align_bwd_s;
+  float* wx = wy + H * PMAX;
+  int* rows = (int*)(wx + W * PW);
+  int* cols = rows + H;
+  __shared__ int s_n[2];
+  const int r = blockIdx.x;
+  const AlignGeom g = ws.geom[r];
+  if (g.batch < 0 || g.grid_h <= 0 || g.grid_w <= 0) return;
+  for (int i = threadIdx.x; i < H * PMAX + W * PW; i += kAlignBwdThreads) wy[i] = 0.f;
+  __syncthreads();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) align_axis_weights(g.start_h, g.bin_h, g.grid_h, PH, H, wy, PMAX, rows, &s_n[0]);
+  if (warp == 1) align_axis_weights(g.start_w, g.bin_w, g.grid_w, PW, W, wx, PW, cols, &s_n[1]);
+  __syncthreads();
+  const int nr = s_n[0], nc = s_n[1];
+  if (nr == 0 || nc == 0) return;
+  const int c0 = (int)(((long long)channels * blockIdx.y) / gridDim.y);
+  const int c1 = (int)(((long long)channels * (blockIdx.y + 1)) / gridDim.y);
+  const float inv = __fdiv_rn(1.f, (float)(g.grid_h * g.grid_w));  // unclamped count (ROIAlign_cuda.cu:258)
+  int cc = c0 + threadIdx.x / nc, kk = threadIdx.x % nc;
+  const int step_c = kAlignBwdThreads / nc, step_k = kAlignBwdThreads % nc;
+  const T* gr = grad_output + r * sn;
+  float* acc_b = grad_acc + (size_t)g.batch * channels * H * W;
+  while (cc < c1) {
+    const int ci = cols[kk];
+    const int x = ci & 0xFFFF, q_lo = (ci >> 16) & 0xFF, q_hi = (ci >> 24) & 0xFF;
+    const T* gp = gr + cc * sc;
+    const float* wxr = wx + x * PW;
+    float t[PMAX];
+#pragma unroll
+    for (int ph = 0; ph < PMAX; ++ph) t[ph] = 0.f;
+    for (int pw = q_lo; pw <= q_hi; ++pw) {
+      const float wv = wxr[pw];
+      const T* gq = gp + pw * sw;
+#pragma unroll
+      for (int ph = 0; ph < PMAX; ++ph)
+        if (ph < PH) t[ph] = fmaf(Elem<T>::to_f(gq[ph * sh]), wv, t[ph]);
+    }
+    float* acc = acc_b + (size_t)cc * H * W + x;
+    for (int jj = 0; jj < nr; ++jj) {
+      const int y = rows[jj] & 0xFFFF;
+      const float4* wr = reinterpret_cast<const float4*>(wy + y * PMAX);
+      float sum = 0.f;
+#pragma unroll
+      for (int q = 0; q < PMAX / 4; ++q) {
+        const float4 w4 = wr[q];
+        sum = fmaf(w4.x, t[4 * q], sum);
+        sum = fmaf(w4.y, t[4 * q + 1], sum);
+        sum = fmaf(w4.z, t[4 * q + 2], sum);
+        sum = fmaf(w4.w, t[4 * q + 3], sum);
+      }
+      if (sum != 0.f) atomicAdd(acc + y * W, sum * inv);
+    }
+    kk += step_k;
+    if (kk >= nc) {
+      kk -= nc;
+      ++cc;
+    }
+    cc += step_c;
+  }
+}
+
 template <typename T>
 __global__ void align_convert_from_f32_kernel(const float* __restrict__ src, T* __restrict__ dst, size_t n) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
@@ -248,12 +534,16 @@ using namespace jtsm;
 
 namespace {
 int align_prep(const float* rois, int num_rois, int batch, float scale, int PH, int PW, int sampling_ratio,
-               int aligned, const AlignWorkspace& ws, cudaStream_t st) {
+               int aligned, const AlignWorkspace& ws, cudaStream_t st, int H = 0, int W = 0, bool taps = false) {
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
   cudaMemsetAsync(ws.ungrouped, 0, sizeof(int), st);
   roi_align_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, scale, PH, PW,
                                                                 sampling_ratio, aligned, ws);
   count_launch();
+  if (taps) {
+    roi_align_taps_kernel<<<num_rois, 64, 0, st>>>(num_rois, H, W, PH, PW, ws);
+    count_launch();
+  }
   return cuda_status();
 }
 
@@ -288,6 +578,7 @@ extern "C" size_t jtsm_roi_align_workspace_bytes(int dtype, int batch, int chann
                                                  int num_rois, int backward) {
   if (batch < 0 || num_rois < 0) return 0;
   size_t b = align_workspace_bytes(batch, num_rois);
+  if (!backward) b += align_tap_bytes(height, width, num_rois);
   if (backward && dtype != JTSM_F32) b += (size_t)batch * channels * height * width * sizeof(float) + 256;
   return b;
 }
@@ -307,7 +598,8 @@ extern "C" int jtsm_roi_align_forward(const void* input, const float* rois, int 
     return JTSM_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   AlignWorkspace ws = carve_align_workspace(workspace, batch, num_rois);
-  int rc = align_prep(rois, num_rois, batch, spatial_scale, pooled_h, pooled_w, sampling_ratio, aligned, ws, st);
+  int rc = align_prep(rois, num_rois, batch, spatial_scale, pooled_h, pooled_w, sampling_ratio, aligned, ws, st,
+                      height, width, tuning("roi_align_fwd_algo", 0) != 1);
   if (rc != JTSM_OK) return rc;
   JTSM_DISPATCH_DTYPE(dtype, T, {
     rc = launch_align_fwd<T>(input, batch, channels, height, width, num_rois, pooled_h, pooled_w, ws, output, st);
@@ -339,15 +631,35 @@ extern "C" int jtsm_roi_align_backward(const void* grad_output, long long stride
     if (!grad_output || !rois) return JTSM_ERR_INVALID_ARGUMENT;
     rc = align_prep(rois, num_rois, batch, spatial_scale, pooled_h, pooled_w, sampling_ratio, aligned, ws, st);
     if (rc != JTSM_OK) return rc;
-    const int cpp = channels * pooled_h * pooled_w;
-    int ysplit = (cpp + 255) / 256;
-    const int want = (4 * num_sms() * 8 + num_rois - 1) / num_rois;
-    if (ysplit > want) ysplit = want < 1 ? 1 : want;
-    dim3 grid(num_rois, ysplit);
-    JTSM_DISPATCH_DTYPE(dtype, T, {
-      roi_align_bwd_kernel<T><<<grid, 256, 0, st>>>((const T*)grad_output, stride_n, stride_c, stride_h, stride_w,
-                                                    channels, height, width, pooled_h, pooled_w, num_rois, ws, acc);
-    });
+    const int algo = tuning("roi_align_bwd_algo", 0);
+    const int pmax = pooled_h <= 8 ? 8 : 16;
+    const bool cols = algo != 2 && pooled_h <= 16;
+    const size_t smem = ((size_t)height * (cols ? pmax : pooled_h) + (size_t)width * pooled_w + height + width) * 4;
+    const bool patch = algo != 1 && smem <= 96 * 1024 && height < 65536 && width < 65536 && pooled_h < 256 &&
+                       pooled_w < 256;
+    if (patch) {
+      // every CTA rebuilds the RoI's weight matrices, so only as many channel slices as it takes to fill the GPU
+      int ysplit = (16 * num_sms() + num_rois - 1) / num_rois;
+      ysplit = ysplit < 1 ? 1 : (ysplit > channels ? channels : ysplit);
+      dim3 grid(num_rois, ysplit);
+      JTSM_DISPATCH_DTYPE(dtype, T, {
+        auto k = !cols ? roi_align_bwd_patch_kernel<T>
+                       : (pmax == 8 ? roi_align_bwd_cols_kernel<T, 8> : roi_align_bwd_cols_kernel<T, 16>);
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k<<<grid, kAlignBwdThreads, smem, st>>>((const T*)grad_output, stride_n, stride_c, stride_h, stride_w,
+                                                channels, height, width, pooled_h, pooled_w, ws, acc);
+      });
+    } else {
+      const int cpp = channels * pooled_h * pooled_w;
+      int ysplit = (cpp + 255) / 256;
+      const int want = (4 * num_sms() * 8 + num_rois - 1) / num_rois;
+      if (ysplit > want) ysplit = want < 1 ? 1 : want;
+      dim3 grid(num_rois, ysplit);
+      JTSM_DISPATCH_DTYPE(dtype, T, {
+        roi_align_bwd_kernel<T><<<grid, 256, 0, st>>>((const T*)grad_output, stride_n, stride_c, stride_h, stride_w,
+                                                      channels, height, width, pooled_h, pooled_w, num_rois, ws, acc);
+      });
+    }
     count_launch();
     rc = cuda_status();
     if (rc != JTSM_OK) return rc;
