@@ -214,19 +214,40 @@ def run_b200(a):
     # ---------------- end-to-end from host buffers (e2e) ----------------
     # Every step uploads its inputs from pinned host memory and downloads its results; with the CUDA-graph step
     # the public streaming call (HotPathStep.run_stream) double-buffers, so step i + 1's H2D and step i - 1's D2H
-    # overlap step i's kernels.  The L2 flush stays between steps (on the compute stream, inside the timed region).
+    # overlap step i's kernels.  Cache state: every step's inputs arrive fresh over PCIe and the two buffer sets
+    # alternate, each step streaming > 500 MB (pooled tensor, argmax, upstream gradient) through the 126 MB L2
+    # before a buffer is touched again, so nothing a step reads can be warm from the previous one; the same loop
+    # with an explicit 256 MiB flush before every step is timed as well and reported next to it.
+    e2e_flush_ms = None
+    h2d_gbps = None
     if use_graph:
         step.prepare_stream(host)
-        seen = []
-        step.run_stream([host] * 3, before_step=flush.zero_)
+        # the link alone: the step's pinned arena copied 10 times back to back
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dst = step.slots[0]["inputs"]["__arena"]
+        dst.copy_(host["__arena"], non_blocking=True)
+        c0.record()
+        for _ in range(10):
+            dst.copy_(host["__arena"], non_blocking=True)
+        c1.record()
+        torch.cuda.synchronize()
+        h2d_gbps = 10 * step.h2d_bytes(host) / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        step.run_stream([host] * 3)
         barrier()
+        seen = []
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        step.run_stream([host] * a.steps, consume=lambda i, out: seen.append(float(out[0][0])), before_step=flush.zero_)
+        step.run_stream([host] * a.steps, consume=lambda i, out: seen.append(float(out[0][0])))
         e1.record()
         barrier()
         assert len(seen) == a.steps
         e2e_ms = e0.elapsed_time(e1)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        step.run_stream([host] * a.steps, before_step=flush.zero_)
+        f1.record()
+        barrier()
+        e2e_flush_ms = f0.elapsed_time(f1)
         e2e_mode = "pipelined: H2D(i+1) | step(i) | D2H(i-1) on three streams, two buffer sets"
     else:
         for _ in range(3):
@@ -243,10 +264,10 @@ def run_b200(a):
         e2e_mode = "sequential: H2D, step, blocking D2H"
 
     clocks = sampler.stop() if rank == 0 else None
-    tm = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    tm = torch.tensor([dev_ms, e2e_ms, e2e_flush_ms or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_ms = (float(v) for v in tm.tolist())
+    dev_ms, e2e_ms, e2e_flush_ms = (float(v) for v in tm.tolist())
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -260,11 +281,16 @@ def run_b200(a):
             "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
                        "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
                        "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool",
-                       "l2": "flushed (256 MiB write) between timed steps", "stages": step.stages(),
+                       "l2": "flushed (256 MiB write) between timed steps (value, roofline); e2e: see e2e.l2", "stages": step.stages(),
                        "launch": "cuda_graph_replay" if use_graph else "eager"},
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes(),
-                    "mode": e2e_mode},
+                    "mode": e2e_mode,
+                    "l2": "fresh H2D inputs every step; two alternating buffer sets, > 500 MB streamed per step "
+                          "(126 MB L2) before a buffer is reused; no explicit flush" if use_graph else
+                          "flushed (256 MiB write) before every step",
+                    "h2d_link_gbps": h2d_gbps,
+                    "value_with_l2_flush": (world * R * a.steps / (e2e_flush_ms * 1e-3)) if e2e_flush_ms else None},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": step.dominant_kernel(), "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "peak_source": peak_src, "traffic": step.ncu_traffic(wl["name"] if a.dtype == "fp32" else None),

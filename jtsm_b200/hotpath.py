@@ -127,24 +127,38 @@ class HotPathStep:
         self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
 
     # ------------------------------------------------------------------ CUDA graph of the step
-    def capture(self, d):
+    def derive_inputs(self, d):
+        """Inputs the step derives from the uploaded ones (row scale = objectness + 1, boxes = RoI columns 1..4)."""
+        d["row_scale"].copy_(d["objectness"] + 1.0)
+        d["proposals"].copy_(d["rois"][:, 1:])
+
+    def capture(self, d, with_io=False):
         """Capture one step over the device-resident inputs `d` into a CUDA graph (all launches go
         through the C ABI on the capturing stream; allocations come from the graph's private pool).
-        Afterwards `replay()` re-runs it; the outputs in `self.last` are the graph's static buffers."""
+        Afterwards `replay()` re-runs it; the outputs in `self.last` are the graph's static buffers.
+        with_io: the graph also derives the dependent inputs first and packs the host-bound results last
+        (`self.graph_results`), so a streamed step is one copy in, one replay, a few copies out."""
         from . import _lib
 
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             for _ in range(2):  # warm caches (segment tables, function attributes) outside the capture
+                if with_io:
+                    self.derive_inputs(d)
                 self.run(d)
+                if with_io:
+                    self.results()
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         before = _lib.launch_count()
         with torch.cuda.graph(self.graph):
+            if with_io:
+                self.derive_inputs(d)
             self.run(d)
-        self.launches_per_step = _lib.launch_count() - before
+            self.launches_per_step = _lib.launch_count() - before
+            self.graph_results = self.results() if with_io else None
         self.static_inputs = d
         self.graph_last = self.last  # the graph's static output buffers
         return self.graph
@@ -167,8 +181,7 @@ class HotPathStep:
         """H2D of the step's inputs into the graph's static buffers, replay, blocking D2H of the results."""
         d = self.static_inputs
         d["__arena"].copy_(host["__arena"], non_blocking=True)
-        d["row_scale"].copy_(d["objectness"] + 1.0)
-        d["proposals"].copy_(d["rois"][:, 1:])
+        self.derive_inputs(d)
         self.graph.replay()
         out = [t.to("cpu") for t in self.results(self.graph_last)]
         self._d2h = sum(t.numel() * t.element_size() for t in out)
@@ -182,9 +195,9 @@ class HotPathStep:
         for _ in range(2):
             d = self.upload(host)
             torch.cuda.synchronize()
-            graph = self.capture(d)
-            res = self.results(self.graph_last)
-            self.slots.append(dict(graph=graph, inputs=d, last=self.graph_last,
+            graph = self.capture(d, with_io=True)
+            res = self.graph_results
+            self.slots.append(dict(graph=graph, inputs=d, last=self.graph_last, res=res,
                                    out=[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res],
                                    ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event()))
         self.copy_stream, self.d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
@@ -210,17 +223,12 @@ class HotPathStep:
                 comp.wait_event(sl["ev_out"])  # the slot's previous results have left the device
             if before_step is not None:
                 before_step()
-            d = sl["inputs"]
-            d["row_scale"].copy_(d["objectness"] + 1.0)
-            d["proposals"].copy_(d["rois"][:, 1:])
-            sl["graph"].replay()
-            res = self.results(sl["last"])
+            sl["graph"].replay()  # derive inputs, the step, pack the results: all inside the slot's graph
             sl["ev_done"].record(comp)
             with torch.cuda.stream(self.d2h_stream):
                 self.d2h_stream.wait_event(sl["ev_done"])
-                for dst, src in zip(sl["out"], res):
+                for dst, src in zip(sl["out"], sl["res"]):
                     dst.copy_(src, non_blocking=True)
-                    src.record_stream(self.d2h_stream)
                 sl["ev_out"].record(self.d2h_stream)
             if i >= 1:
                 prev = self.slots[(i - 1) % 2]
