@@ -281,7 +281,7 @@ def run_b200(a):
             "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
                        "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
                        "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool",
-                       "l2": "flushed (256 MiB write) between timed steps (value, roofline); e2e: see e2e.l2", "stages": step.stages(),
+                       "l2": "flushed (256 MiB write) between timed steps (value, roofline); e2e: see e2e.l2", "stages": step.stages(), "schedule": step.schedule(),
                        "launch": "cuda_graph_replay" if use_graph else "eager"},
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes(),

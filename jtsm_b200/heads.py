@@ -13,14 +13,22 @@ from . import ops
 def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposals, num_preds_per_image, gt_classes_img_int,
               num_classes, labels_onehot, mean_loss=True, reg=False, reg_weighted=True, iou_thresholds=(0.5,),
               iou_labels=(0, 1), need_grad=True, term_weights=None, smooth_l1_beta=0.0,
-              bbox_reg_weights=(10.0, 10.0, 5.0, 5.0), refine_mist=False, mist_top_pro=0.15):
+              bbox_reg_weights=(10.0, 10.0, 5.0, 5.0), refine_mist=False, mist_top_pro=0.15, streams=None):
     """proposals: [R,4] (all images concatenated).  Returns dict(losses, scores, img_scores, branches[...],
     grad_cls, grad_det, grad_ref_logits, grad_ref_deltas).  Launches: 1 (MIL fwd+loss) + 1 (MIL bwd)
     + per branch 2 (assign, CE fwd/bwd/softmax) [+ 2 with box regression].
     refine_mist: WSL.REFINE_MIST targets (roi_heads_oicr.py:418-424) -- seeds from get_pgt_mist, branch 0 weighted x3
-    unless term_weights is given; that path reads the per-image seed counts on the host (not graph-capturable)."""
+    unless term_weights is given; that path reads the per-image seed counts on the host (not graph-capturable).
+    streams: optional list of >= len(ref_logits) + 1 side streams.  The branches only meet through the previous
+    branch's softmax scores and decoded boxes, and neither depends on the labels, so with side streams every branch
+    (its own softmax of the previous logits, assign, CE, box regression) and the MIL backward run concurrently
+    after the MIL forward instead of as one chain of small latency-bound launches; same kernels, same results."""
     fwd = ops.wsddn_forward(mil_cls, mil_det, num_preds_per_image, labels_onehot, mean_loss)
     out = dict(losses={"loss_cls": fwd["loss"]}, scores=fwd["scores"], img_scores=fwd["img_scores"], branches=[])
+    if streams is not None and not refine_mist and len(ref_logits) > 0 and len(streams) > len(ref_logits):
+        return _head_step_concurrent(fwd, out, ref_logits, ref_deltas, proposals, num_preds_per_image,
+                                     gt_classes_img_int, num_classes, reg, reg_weighted, iou_thresholds, iou_labels,
+                                     need_grad, term_weights, smooth_l1_beta, bbox_reg_weights, streams)
     prev_scores, prev_boxes = fwd["scores"], proposals
     grads_l, grads_d = [], []
     boxes_noreg = None
@@ -55,6 +63,72 @@ def head_step(mil_cls, mil_det, ref_logits, ref_deltas, proposals, num_preds_per
     if need_grad:
         out["grad_cls"], out["grad_det"] = ops.wsddn_backward(fwd)
         out["grad_ref_logits"], out["grad_ref_deltas"] = grads_l, grads_d
+    return out
+
+
+def _head_step_concurrent(fwd, out, ref_logits, ref_deltas, proposals, num_preds_per_image, gt_classes_img_int,
+                          num_classes, reg, reg_weighted, iou_thresholds, iou_labels, need_grad, term_weights,
+                          smooth_l1_beta, bbox_reg_weights, streams):
+    main = torch.cuda.current_stream()
+    kr = len(ref_logits)
+    boxes_noreg = None
+    if not reg:  # zero deltas: predict_boxes still round-trips through (ctr, size) (fast_rcnn_oicr.py:684-709)
+        boxes_noreg = ops.apply_deltas(torch.zeros(proposals.shape[0], 4, device=proposals.device), proposals,
+                                       bbox_reg_weights)
+    start = torch.cuda.Event()
+    start.record(main)
+    boxes, box_ready = [None] * kr, [None] * kr
+    branches, losses, grads_l, grads_d = [None] * kr, [dict() for _ in range(kr)], [None] * kr, [None] * kr
+    for k, logits in enumerate(ref_logits):
+        st = streams[k]
+        st.wait_event(start)
+        tw = 1.0 if term_weights is None else float(term_weights[k])
+        with torch.cuda.stream(st):
+            if reg:
+                boxes[k] = ops.apply_deltas(ref_deltas[k], proposals, bbox_reg_weights)
+                box_ready[k] = torch.cuda.Event()
+                box_ready[k].record(st)
+            else:
+                boxes[k] = boxes_noreg
+            if k == 0:
+                prev_scores, prev_boxes = fwd["scores"], proposals
+            else:
+                prev_scores = ops.softmax_rows(ref_logits[k - 1])  # = the previous branch's probs, bit for bit
+                prev_boxes = boxes[k - 1]
+                if reg:
+                    st.wait_event(box_ready[k - 1])
+            a = ops.refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_classes_img_int,
+                                  fwd["img_scores"], num_classes, iou_thresholds, iou_labels, want_iou=True)
+            ce = ops.refine_ce(logits, a["gt_classes"], a["loss_weights"], a["valid_count"], loss_scale=tw,
+                               want_grad=need_grad)
+            losses[k]["loss_cls_r%d" % k] = ce["loss"]
+            grads_l[k] = ce["grad_logits"]
+            if reg:
+                br = ops.refine_box_reg(ref_deltas[k], proposals, a["gt_boxes"], a["gt_classes"],
+                                        a["loss_weights"] if reg_weighted else None, num_classes, bbox_reg_weights,
+                                        smooth_l1_beta, loss_scale=tw, want_grad=need_grad)
+                losses[k]["loss_box_reg_r%d" % k] = br["loss"]
+                grads_d[k] = br["grad_deltas"]
+            a.update(probs=ce["probs"], boxes=boxes[k], acc=ce["acc"])
+            branches[k] = a
+            for t in list(a.values()) + [ce["loss"], ce["grad_logits"], prev_scores] + \
+                    ([br["loss"], br["grad_deltas"]] if reg else []):
+                if torch.is_tensor(t):
+                    t.record_stream(main)
+    if need_grad:
+        st = streams[kr]
+        st.wait_event(start)
+        with torch.cuda.stream(st):
+            out["grad_cls"], out["grad_det"] = ops.wsddn_backward(fwd)
+            out["grad_cls"].record_stream(main)
+            out["grad_det"].record_stream(main)
+    for st in streams[:kr + 1]:
+        main.wait_stream(st)
+    for k in range(kr):
+        out["losses"].update(losses[k])
+    out["branches"] = branches
+    if need_grad:
+        out["grad_ref_logits"], out["grad_ref_deltas"] = grads_l, [g for g in grads_d if g is not None]
     return out
 
 

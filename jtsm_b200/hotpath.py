@@ -6,6 +6,8 @@ Mirrors what `OICRROIHeads._forward_box` + autograd execute per step in the refe
    label assignment, weighted CE, softmax) -> backward to the head logits and to the feature map.
 Used by bench.py and by the parity tests; stages are enabled as their kernels exist.
 """
+import os
+
 import torch
 
 from . import heads, ops, synth
@@ -19,6 +21,9 @@ class HotPathStep:
         self.P = (cfg["P"], cfg["P"])
         self.scale = cfg["scale"]
         self._d2h = 0
+        # side streams of the head: one per refinement branch + one for the MIL backward (heads.head_step)
+        self.side_streams = [torch.cuda.Stream(device=device) for _ in range(cfg["Kr"] + 1)] \
+            if os.environ.get("JTSM_SERIAL_HEADS", "0") != "1" else None
 
     # ------------------------------------------------------------------ inputs
     def pin_host_inputs(self, wl):
@@ -77,6 +82,13 @@ class HotPathStep:
             st += ["refine_box_reg"] * self.cfg["Kr"]
         return st + ["roi_pool_bwd"]
 
+    def schedule(self):
+        """How the stages are ordered on the device."""
+        if self.side_streams is None:
+            return "one stream, stages in order"
+        return ("pool fwd -> MIL fwd -> {branch k: softmax(prev logits), assign, CE[, box reg]} x Kr and MIL bwd "
+                "concurrently on side streams -> pool bwd")
+
     def dominant_kernel(self):
         return "roi_pool_fwd_rmq_kernel"
 
@@ -122,7 +134,7 @@ class HotPathStep:
         pooled, argmax = self.pool_forward(d)
         cfg = self.cfg
         h = heads.head_step(d["mil_cls"], d["mil_det"], d["ref_logits"], d["ref_deltas"], d["proposals"], self.counts,
-                            self.labels, cfg["K"], d["labels_onehot"], reg=cfg["reg"])
+                            self.labels, cfg["K"], d["labels_onehot"], reg=cfg["reg"], streams=self.side_streams)
         grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=d["row_scale"])
         self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
 

@@ -33,7 +33,7 @@ def run_cuda(inputs, kw, dev):
                            [d(x) for x in inputs["ref_deltas"]], d(torch.cat(inputs["proposal_boxes"])), counts,
                            inputs["labels"], k, d(oh), mean_loss=kw.get("mean_loss", True), reg=kw.get("reg", False),
                            iou_thresholds=kw.get("thresholds", (0.5,)), iou_labels=kw.get("iou_labels", (0, 1)),
-                           refine_mist=kw.get("refine_mist", False))
+                           refine_mist=kw.get("refine_mist", False), streams=kw.get("streams"))
 
 
 def close(a, b, what, rtol=RTOL, atol=ATOL):
@@ -215,6 +215,31 @@ def test_head_step_config2_vs_oracle(cuda):
     close(out["grad_cls"], ref["grad_cls"], "grad_cls", atol=1e-8)
     for a, b in zip(out["grad_ref_logits"], ref["grad_ref_logits"]):
         close(a, b, "grad_ref_logits", atol=1e-9)
+
+
+@pytest.mark.parametrize("name,reg", [("c2", False), ("c3", True)])
+def test_head_step_concurrent_branches_equal_serial(cuda, name, reg):
+    """Branches + MIL backward on side streams (heads.head_step(streams=...)) == the serial chain, bit for bit."""
+    wl = synth.step_case(name)
+    cfg = wl["cfg"]
+    inputs = dict(mil_cls=wl["mil_cls"], mil_det=wl["mil_det"], ref_logits=wl["ref_logits"], ref_deltas=wl["ref_deltas"],
+                  proposal_boxes=wl["boxes"], labels=wl["labels"], num_classes=cfg["K"])
+    serial = run_cuda(inputs, dict(reg=reg), cuda)
+    side = [torch.cuda.Stream() for _ in range(cfg["Kr"] + 1)]
+    par = run_cuda(inputs, dict(reg=reg, streams=side), cuda)
+    torch.cuda.synchronize()
+    assert sorted(serial["losses"]) == sorted(par["losses"])
+    for k in serial["losses"]:
+        assert torch.equal(serial["losses"][k], par["losses"][k]), k
+    for a, b in zip(serial["branches"], par["branches"]):
+        for key in ("gt_classes", "gt_weights", "gt_boxes", "loss_weights", "probs", "boxes", "counters", "acc"):
+            assert torch.equal(a[key], b[key]), key
+    for key in ("grad_cls", "grad_det"):
+        assert torch.equal(serial[key], par[key]), key
+    for key in ("grad_ref_logits", "grad_ref_deltas"):
+        assert len(serial[key]) == len(par[key])
+        for a, b in zip(serial[key], par[key]):
+            assert torch.equal(a, b), key
 
 
 @pytest.mark.parametrize("counts,k,top_pro", [((2000,), 20, 0.15), ((700, 1, 1300), 12, 0.10), ((3,), 5, 0.15)])
