@@ -1,0 +1,155 @@
+"""oracle/_ref: the reference's OWN native code for the path, built in place from /root/reference and run on the CPU.
+
+TEST INFRASTRUCTURE ONLY (tests/, __graft_entry__.build()): never imported by jtsm_b200/.
+
+ * libref_wslpool.so -- the device kernels of projects/WSL/wsl/layers/csrc/{ROILoopPool,MOIPool}/*_cuda.cu compiled
+   as serial host C++ (oracle/Makefile.ref, oracle/ref_shim/, oracle/ref_wslpool_driver.cpp).  The reference has no
+   runnable CPU path for these two ops (ROILoopPool.h:62, MOIPool.h:74 raise), so this is the only way to execute
+   the reference's arithmetic for them without a GPU; it pins oracle/jtsm_oracle.c's restatement bit for bit.
+
+ * libref_roialign.so -- detectron2/layers/csrc/ROIAlign/ROIAlign_cpu.cpp compiled where it lies against this image's
+   ATen (oracle/ref_roialign_driver.cpp): the reference's CPU RoIAlign forward / backward behind plain pointers.
+
+The .so files are built when /root/reference is present (this container) and travels to the GPU box prebuilt.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("JTSM_REFERENCE", "/root/reference")
+OUT = os.path.join(HERE, "_ref")
+WSLPOOL = os.path.join(OUT, "libref_wslpool.so")
+ROIALIGN = os.path.join(OUT, "libref_roialign.so")
+
+_wsl = None
+_align = None
+
+
+def build():
+    """Build oracle/_ref from the reference sources where they lie; returns the .so path or None when absent."""
+    if os.path.isdir(os.path.join(REF, "projects", "WSL")):
+        subprocess.run(["make", "-s", "-f", "Makefile.ref", f"REF={REF}"], cwd=HERE, check=True)
+    return WSLPOOL if os.path.exists(WSLPOOL) else None
+
+
+def build_roi_align():
+    if os.path.isfile(os.path.join(REF, "detectron2", "layers", "csrc", "ROIAlign", "ROIAlign_cpu.cpp")):
+        import torch
+        from torch.utils import cpp_extension as ce
+
+        inc = " ".join(ce.include_paths())
+        libdir = os.path.join(os.path.dirname(torch.__file__), "lib")
+        subprocess.run(["make", "-s", "-f", "Makefile.ref", f"REF={REF}", f"TORCH_INC={inc}", f"TORCH_LIB={libdir}",
+                        "_ref/libref_roialign.so"], cwd=HERE, check=True)
+    return ROIALIGN if os.path.exists(ROIALIGN) else None
+
+
+def available():
+    return build() is not None
+
+
+def roi_align_available():
+    return build_roi_align() is not None
+
+
+def align():
+    global _align
+    if _align is None:
+        path = build_roi_align()
+        if path is None:
+            raise RuntimeError("oracle/_ref/libref_roialign.so missing and /root/reference not present")
+        import torch  # noqa: F401  (libtorch_cpu / libc10 must be loaded first)
+
+        _align = ctypes.CDLL(path)
+    return _align
+
+
+def wsl():
+    global _wsl
+    if _wsl is None:
+        path = build()
+        if path is None:
+            raise RuntimeError("oracle/_ref/libref_wslpool.so missing and /root/reference not present")
+        _wsl = ctypes.CDLL(path)
+    return _wsl
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def roi_loop_pool_forward(inp, rois, spatial_scale, pooled):
+    inp, rois = _f32(inp), _f32(rois)
+    n, c, h, w = inp.shape
+    r = rois.shape[0]
+    ph, pw = pooled
+    out = np.empty((3 * r, c, ph, pw), np.float32)
+    arg = np.empty((3 * r, c, ph, pw), np.int32)
+    wsl().ref_roi_loop_pool_forward(_p(inp), _p(rois), r, c, h, w, ph, pw, ctypes.c_float(spatial_scale),
+                                    _p(out), _p(arg))
+    return out, arg
+
+
+def roi_loop_pool_backward(grad_out, argmax, rois, input_shape, spatial_scale=1.0):
+    grad_out, argmax, rois = _f32(grad_out), _i32(argmax), _f32(rois)
+    n, c, h, w = input_shape
+    ph, pw = grad_out.shape[2:]
+    gi = np.empty(input_shape, np.float32)
+    wsl().ref_roi_loop_pool_backward(_p(grad_out), _p(argmax), _p(rois), rois.shape[0], n, c, h, w, ph, pw,
+                                     ctypes.c_float(spatial_scale), _p(gi))
+    return gi
+
+
+def moi_pool_forward(inp, rois, oh_labels, superpixels, spatial_scale, pooled, return_mask=False):
+    inp, rois, oh, sp = _f32(inp), _f32(rois), _i32(oh_labels), _i32(superpixels)
+    n, c, h, w = inp.shape
+    r = rois.shape[0]
+    ph, pw = pooled
+    out = np.empty((r, c, ph, pw), np.float32)
+    arg = np.empty((r, c, ph, pw), np.int32)
+    mois = np.empty((r, h, w), np.int32)
+    wsl().ref_moi_pool_forward(_p(inp), _p(rois), r, _p(oh), oh.shape[1], _p(sp), sp.shape[1], sp.shape[2],
+                               c, h, w, ph, pw, ctypes.c_float(spatial_scale), _p(out), _p(arg), _p(mois))
+    return (out, arg, mois) if return_mask else (out, arg)
+
+
+def moi_pool_backward(grad_out, argmax, rois, input_shape, spatial_scale=1.0):
+    grad_out, argmax, rois = _f32(grad_out), _i32(argmax), _f32(rois)
+    n, c, h, w = input_shape
+    ph, pw = grad_out.shape[2:]
+    gi = np.empty(input_shape, np.float32)
+    wsl().ref_moi_pool_backward(_p(grad_out), _p(argmax), _p(rois), rois.shape[0], n, c, h, w, ph, pw,
+                                ctypes.c_float(spatial_scale), _p(gi))
+    return gi
+
+
+def roi_align_forward(inp, rois, spatial_scale, pooled, sampling_ratio, aligned):
+    inp, rois = _f32(inp), _f32(rois)
+    n, c, h, w = inp.shape
+    r = rois.shape[0]
+    ph, pw = pooled
+    out = np.empty((r, c, ph, pw), np.float32)
+    align().ref_roi_align_forward(_p(inp), n, c, h, w, _p(rois), r, ctypes.c_float(spatial_scale), ph, pw,
+                                  int(sampling_ratio), int(bool(aligned)), _p(out))
+    return out
+
+
+def roi_align_backward(grad_out, rois, spatial_scale, input_shape, sampling_ratio, aligned):
+    grad_out, rois = _f32(grad_out), _f32(rois)
+    n, c, h, w = input_shape
+    r, _, ph, pw = grad_out.shape
+    gi = np.empty(input_shape, np.float32)
+    align().ref_roi_align_backward(_p(grad_out), _p(rois), r, ctypes.c_float(spatial_scale), ph, pw, n, c, h, w,
+                                   int(sampling_ratio), int(bool(aligned)), _p(gi))
+    return gi
