@@ -279,6 +279,47 @@ JTSM_API int jtsm_batched_nms(const float* boxes, const float* scores, const lon
                               long long* num_keep, void* workspace, size_t workspace_bytes,
                               void* stream);
 
+/* ------------------------------------------------------------------------
+ * Test-time-augmentation average.
+ * GeneralizedRCNNWithTTAAVG._get_augmented_boxes
+ * (projects/WSL/wsl/modeling/test_time_augmentation_avg.py:364-390): the boxes of every augmented
+ * pass are mapped back to the original image with `tfm.inverse().apply_box` (a host numpy round trip
+ * per augmentation in the reference), then boxes and scores are averaged over the augmentations.
+ *
+ * A transform list is a sequence of at most JTSM_TTA_MAX_OPS stages, applied in order; every stage
+ * follows fvcore's Transform.apply_box: the four corners go through apply_coords, the result is the
+ * (min, max) box of the mapped corners.  Stage kinds:
+ *   JTSM_TTA_NOOP   NoOpTransform                 (coords unchanged; still takes min / max)
+ *   JTSM_TTA_HFLIP  HFlipTransform(width = a)     x -> a - x
+ *   JTSM_TTA_SCALE  ResizeTransform               x -> x * a, y -> y * b  (a = float(new_w / w), b = float(new_h / h);
+ *                                                  detectron2/data/transforms/transform.py:149-152)
+ *   JTSM_TTA_END    terminates the list early
+ * op_type / op_a / op_b are HOST arrays [num_aug * JTSM_TTA_MAX_OPS] (copied into the launch parameters).
+ * ------------------------------------------------------------------------ */
+#define JTSM_TTA_MAX_OPS 4
+#define JTSM_TTA_MAX_AUG 32
+#define JTSM_TTA_END 0
+#define JTSM_TTA_NOOP 1
+#define JTSM_TTA_HFLIP 2
+#define JTSM_TTA_SCALE 3
+/* boxes / scores: HOST arrays of num_aug DEVICE pointers, each [num_rois, boxes_per_row, 4] /
+ * [num_rois, score_cols] fp32 contiguous (the per-augmentation outputs stay where inference left them).
+ * mean_boxes [num_rois, boxes_per_row, 4], mean_scores [num_rois, score_cols]: sum over the augmentations in
+ * list order, divided by num_aug (what torch.mean(dim=0) computes on the CPU).  scores / mean_scores may be
+ * NULL (boxes only) and so may boxes / mean_boxes (scores only).  One launch. */
+JTSM_API int jtsm_tta_merge(const void* const* boxes, const void* const* scores, int num_aug,
+                            int num_rois, int boxes_per_row, int score_cols, const int* op_type,
+                            const float* op_a, const float* op_b, float* mean_boxes,
+                            float* mean_scores, void* stream);
+/* transform_proposals (test_time_augmentation_avg.py:27-70): boxes [n, 4] -> transform list (forward) ->
+ * Boxes.clip to (image_h, image_w) (detectron2/structures/boxes.py:195-211) -> out_boxes [n, 4] and
+ * keep [n] uint8 = Boxes.nonempty(threshold = min_box_size) (boxes.py:213-225: width > t and height > t).
+ * One transform list (op arrays of JTSM_TTA_MAX_OPS entries, HOST). */
+JTSM_API int jtsm_tta_transform_boxes(const float* boxes, int num_boxes, const int* op_type,
+                                      const float* op_a, const float* op_b, float image_h,
+                                      float image_w, float min_box_size, float* out_boxes,
+                                      unsigned char* keep, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -526,3 +526,74 @@ def moi_pool_backward(grad, rois, argmax, spatial_scale, pooled_height, pooled_w
     """wsl._C.moi_pool_backward (MOIPool.h:85-95)."""
     return roi_pool_backward(grad, rois, argmax, (batch_size, channels, height, width), (pooled_height, pooled_width),
                              row_scale=row_scale)
+
+
+# --------------------------------------------------------------------------- TTA-AVG merge (SURVEY 8f-1)
+TTA_MAX_OPS, TTA_MAX_AUG = 4, 32
+TTA_END, TTA_NOOP, TTA_HFLIP, TTA_SCALE = 0, 1, 2, 3
+
+
+def _tta_op_arrays(op_lists):
+    """[[(type, a, b), ...] per augmentation] -> flat ctypes arrays [len * TTA_MAX_OPS] (type, a, b)."""
+    import ctypes
+
+    n = len(op_lists) * TTA_MAX_OPS
+    ty, aa, bb = (ctypes.c_int * n)(), (ctypes.c_float * n)(), (ctypes.c_float * n)()
+    for i, ops_ in enumerate(op_lists):
+        if len(ops_) > TTA_MAX_OPS:
+            raise RuntimeError("jtsm_b200: a transform list has more than %d stages" % TTA_MAX_OPS)
+        for s, (t, a, b) in enumerate(ops_):
+            ty[i * TTA_MAX_OPS + s], aa[i * TTA_MAX_OPS + s], bb[i * TTA_MAX_OPS + s] = int(t), float(a), float(b)
+    return ty, aa, bb
+
+
+def tta_merge(all_boxes, all_scores, op_lists):
+    """Mean over augmentations of inverse-transformed boxes and of scores
+    (GeneralizedRCNNWithTTAAVG._get_augmented_boxes, test_time_augmentation_avg.py:364-390).
+    all_boxes: list of A tensors [R, 4k] (or [1, R, 4k]); all_scores: list of A tensors [R, S] (or [1, R, S]) or None;
+    op_lists: per augmentation the INVERSE stage list [(type, a, b), ...].  -> (mean_boxes [R, 4k], mean_scores [R, S])."""
+    import ctypes
+
+    A = len(all_boxes)
+    if A == 0 or A > TTA_MAX_AUG:
+        raise RuntimeError("jtsm_b200.tta_merge: 1..%d augmentations, got %d" % (TTA_MAX_AUG, A))
+    _require_cuda(*all_boxes)
+    B = [_f32c(b.reshape(b.shape[-2], b.shape[-1])) for b in all_boxes]
+    r, cols = B[0].shape
+    if cols % 4 or any(b.shape != B[0].shape for b in B):
+        raise RuntimeError("jtsm_b200.tta_merge: boxes must all be [R, 4k]")
+    S = None
+    sc = 0
+    if all_scores is not None:
+        _require_cuda(*all_scores)
+        S = [_f32c(s.reshape(s.shape[-2], s.shape[-1])) for s in all_scores]
+        if len(S) != A or any(s.shape != S[0].shape for s in S) or S[0].shape[0] != r:
+            raise RuntimeError("jtsm_b200.tta_merge: scores must all be [R, S], one per augmentation")
+        sc = S[0].shape[1]
+    if len(op_lists) != A:
+        raise RuntimeError("jtsm_b200.tta_merge: one transform list per augmentation")
+    ty, aa, bb = _tta_op_arrays(op_lists)
+    dev = B[0].device
+    mb = torch.empty((r, cols), dtype=torch.float32, device=dev)
+    ms = torch.empty((r, sc), dtype=torch.float32, device=dev) if S is not None else None
+    bp = (ctypes.c_void_p * A)(*[b.data_ptr() for b in B])
+    sp = (ctypes.c_void_p * A)(*[s.data_ptr() for s in S]) if S is not None else None
+    with torch.cuda.device(dev):
+        check(lib().jtsm_tta_merge(bp, sp, A, r, cols // 4, sc, ty, aa, bb, _ptr(mb), _ptr(ms), _stream()), "tta_merge")
+    return mb, ms
+
+
+def tta_transform_boxes(boxes, ops_, image_shape, min_box_size=0.0):
+    """transform_proposals (test_time_augmentation_avg.py:27-70): stage list forward, Boxes.clip, Boxes.nonempty.
+    boxes [n, 4] -> (boxes [n, 4] clipped, keep bool [n])."""
+    _require_cuda(boxes)
+    B = _f32c(boxes)
+    n = B.shape[0]
+    out = torch.empty_like(B)
+    keep = torch.empty(n, dtype=torch.uint8, device=B.device)
+    ty, aa, bb = _tta_op_arrays([ops_])
+    h, w = image_shape
+    with torch.cuda.device(B.device):
+        check(lib().jtsm_tta_transform_boxes(_ptr(B), n, ty, aa, bb, float(h), float(w), float(min_box_size),
+                                             _ptr(out), _ptr(keep), _stream()), "tta_transform_boxes")
+    return out, keep.bool()

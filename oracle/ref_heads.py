@@ -311,3 +311,32 @@ def batched_nms(boxes, scores, idxs, thr):
     keep = np.concatenate(keep) if keep else np.zeros(0, np.int64)
     order = np.lexsort((keep, -s[keep]))
     return torch.from_numpy(keep[order].astype(np.int64))
+
+
+def fast_rcnn_inference_single_image(boxes, scores, image_shape, score_thresh, nms_thresh, topk_per_image):
+    """fast_rcnn_oicr.py:95-163 on CPU tensors -> dict(pred_boxes, scores, pred_classes, pred_inds, kept_rois).
+    NMS = `batched_nms` above (per class on the original coordinates)."""
+    pred_inds = torch.arange(scores.size(0), dtype=torch.long).unsqueeze(1).repeat(1, scores.size(1))
+    valid = torch.isfinite(boxes).all(dim=1) & torch.isfinite(scores).all(dim=1)
+    if not valid.all():
+        boxes, scores, pred_inds = boxes[valid], scores[valid], pred_inds[valid]
+    scores = scores[:, :-1]
+    nb = boxes.shape[1] // 4
+    h, w = image_shape
+    b = boxes.reshape(-1, 4).clone()
+    b[:, 0].clamp_(min=0, max=w)
+    b[:, 1].clamp_(min=0, max=h)
+    b[:, 2].clamp_(min=0, max=w)
+    b[:, 3].clamp_(min=0, max=h)
+    b = b.view(-1, nb, 4)
+    pred_inds = pred_inds[:, :-1]
+    mask = scores > score_thresh
+    fi = mask.nonzero()
+    b = b[fi[:, 0], 0] if nb == 1 else b[mask]
+    s = scores[mask]
+    pred_inds = pred_inds[mask]
+    keep = batched_nms(b, s, fi[:, 1], nms_thresh)
+    if topk_per_image >= 0:
+        keep = keep[:topk_per_image]
+    return dict(pred_boxes=b[keep], scores=s[keep], pred_classes=fi[keep][:, 1], pred_inds=pred_inds[keep],
+                kept_rois=fi[keep][:, 0])

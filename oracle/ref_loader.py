@@ -176,3 +176,54 @@ def make_self(num_classes, gt_classes_img_int, pred_class_img_logits, iou_thresh
     s._sample_proposals = lambda *a: f["_sample_proposals"](s, *a)
     s.get_pgt_top_k = lambda *a, **k: f["get_pgt_top_k"](s, *a, **k)
     return s, f
+
+
+def extract_function(path, name, namespace):
+    """Compile one module-level function of the reference file `path` (in place) into a callable."""
+    with open(path) as fh:
+        tree = ast.parse(fh.read(), filename=path)
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name == name:
+            code = compile(ast.Module(body=[node], type_ignores=[]), path, "exec")
+            ns = dict(namespace)
+            exec(code, ns)
+            return ns[name]
+    raise KeyError("%s not found in %s" % (name, path))
+
+
+_tta = {}
+
+
+def tta_reference():
+    """The reference's own TTA-AVG code, executed in place on top of the restated fvcore base classes
+    (oracle/fvcore_transforms.py):
+      ResizeTransform              detectron2/data/transforms/transform.py:94-159 (whole module loaded)
+      ResizeShortestEdge.get_transform   detectron2/data/transforms/augmentation_impl.py:152-172
+      GeneralizedRCNNWithTTAAVG._get_augmented_boxes   projects/WSL/wsl/modeling/test_time_augmentation_avg.py:364-390
+      transform_proposals          test_time_augmentation_avg.py:27-70
+    -> dict(ResizeTransform, get_transform, get_augmented_boxes, transform_proposals, Boxes, Instances)."""
+    if _tta:
+        return _tta
+    m = install()
+    import numpy as np
+
+    from . import fvcore_transforms as fv
+
+    _stub("fvcore.transforms", HFlipTransform=fv.HFlipTransform, NoOpTransform=fv.NoOpTransform)
+    _stub("fvcore.transforms.transform", CropTransform=fv.CropTransform, HFlipTransform=fv.HFlipTransform,
+          NoOpTransform=fv.NoOpTransform, Transform=fv.Transform, TransformList=fv.TransformList)
+    from PIL import Image
+
+    if not hasattr(Image, "LINEAR"):  # removed from Pillow >= 10; the reference names it in a default argument only
+        Image.LINEAR = Image.BILINEAR
+    tr = _load_file("detectron2.data.transforms.transform", os.path.join(D2, "data", "transforms", "transform.py"))
+    ns = dict(np=np, torch=torch, ResizeTransform=tr.ResizeTransform, NoOpTransform=fv.NoOpTransform,
+              Boxes=m["boxes"].Boxes, Instances=m["instances"].Instances)
+    gt = extract_methods(os.path.join(D2, "data", "transforms", "augmentation_impl.py"), "ResizeShortestEdge",
+                         ["get_transform"], ns)["get_transform"]
+    tta_path = os.path.join(WSL, "modeling", "test_time_augmentation_avg.py")
+    gab = extract_methods(tta_path, "GeneralizedRCNNWithTTAAVG", ["_get_augmented_boxes"], ns)["_get_augmented_boxes"]
+    tp = extract_function(tta_path, "transform_proposals", ns)
+    _tta.update(ResizeTransform=tr.ResizeTransform, get_transform=gt, get_augmented_boxes=gab,
+                transform_proposals=tp, Boxes=m["boxes"].Boxes, Instances=m["instances"].Instances)
+    return _tta

@@ -58,6 +58,41 @@ def main():
         out = ref_drive.reference_head_step(**inputs, **kw)
         np.savez_compressed(os.path.join(HERE, "heads_%s.npz" % name), **flatten(out))
         print("wrote heads_%s.npz" % name)
+    make_tta()
+
+
+TTA_CASE = dict(seed=301, image_hw=(375, 500), orig_hw=(375, 500), min_sizes=(480, 688, 1200), max_size=4000, flip=True,
+                r=120, k=6)
+
+
+def make_tta():
+    """tests/golden/tta_case0.npz: the reference's own GeneralizedRCNNWithTTAAVG._get_augmented_boxes (run in place;
+    ResizeShortestEdge.get_transform and ResizeTransform are the reference's too) on synthetic augmented passes."""
+    import types
+
+    from oracle import ref_loader, ref_tta
+    from oracle.fvcore_transforms import HFlipTransform, TransformList
+
+    c = TTA_CASE
+    ref = ref_loader.tta_reference()
+    g = synth.generator(c["seed"])
+    img = np.zeros(c["image_hw"] + (3,), np.uint8)
+    tf_ref = []
+    for size in c["min_sizes"]:
+        aug = types.SimpleNamespace(is_range=False, short_edge_length=(size, size), max_size=c["max_size"], interp=None)
+        resize = ref["get_transform"](aug, img)
+        tf_ref.append(TransformList([resize]))
+        tf_ref.append(TransformList([resize, HFlipTransform(resize.new_w)]))
+    pb = synth.proposals(g, c["r"], *c["orig_hw"])
+    boxes, scores = ref_tta.synth_augmented_outputs(g, pb, tf_ref, c["k"])
+    self_ = types.SimpleNamespace(_batch_inference=lambda inputs: (None, [s.clone() for s in scores],
+                                                                   [b.clone() for b in boxes]))
+    mb, ms, _ = ref["get_augmented_boxes"](self_, [None] * len(tf_ref), tf_ref)
+    np.savez_compressed(os.path.join(HERE, "tta_case0.npz"), image_hw=np.array(c["image_hw"]),
+                        orig_hw=np.array(c["orig_hw"]), min_sizes=np.array(c["min_sizes"]), max_size=c["max_size"],
+                        flip=c["flip"], boxes=torch.cat(boxes).numpy(), scores=torch.cat(scores).numpy(),
+                        mean_boxes=mb.numpy(), mean_scores=ms.numpy())
+    print("wrote tta_case0.npz")
 
 
 if __name__ == "__main__":

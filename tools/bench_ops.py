@@ -35,7 +35,7 @@ def main():
     ap.add_argument("--tv", action="store_true")
     ap.add_argument("--tune", nargs="*", default=[])
     ap.add_argument("--dtype", default="fp32")
-    ap.add_argument("--ops", default="pool", help="pool | all")
+    ap.add_argument("--ops", default="pool", help="pool | all | tta")
     a = ap.parse_args()
     for kv in a.tune:
         k, v = kv.split("=")
@@ -91,7 +91,45 @@ def main():
         sp_d, oh_d = sp.to(dev), oh.to(dev)
         med, _ = timeit(lambda: ops.moi_pool_forward(x, rois_d, cfg["scale"], ph, pw, oh_d, sp_d), a.iters, flush)
         res["moi_pool_fwd_us"] = med
+    if a.ops in ("all", "tta"):
+        res.update(bench_tta(dev, a.iters, flush))
     print(json.dumps(res))
+
+
+def bench_tta(dev, iters, flush):
+    """c4: R = 4000, K = 20, 10 augmentations: device merge vs the reference's composition on the same GPU
+    (per augmentation D2H -> numpy apply_box -> H2D, then torch.cat + torch.mean; test_time_augmentation_avg.py:364-390)."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    from jtsm_b200 import tta
+    from oracle import ref_tta  # timed beside it as the reference's own composition, not part of the product path
+
+    g = synth.generator(synth.seed_for(4))
+    hw = (600, 800)
+    sizes = (480, 576, 688, 864, 1200)
+    tf_o = ref_tta.tta_transforms(hw, hw, sizes, 4000, True)
+    tf = tta.tta_transforms(hw, hw, sizes, 4000, True)
+    pb = synth.proposals(g, 4000, *hw)
+    boxes, scores = ref_tta.synth_augmented_outputs(g, pb, tf_o, 20)
+    bd, sd = [b.to(dev) for b in boxes], [s.to(dev) for s in scores]
+    out = {}
+    med, _ = timeit(lambda: tta.get_augmented_boxes(bd, sd, tf), iters, flush)
+    out["tta_merge_us"] = med
+    nbytes = (len(bd) + 1) * (bd[0].numel() + sd[0].numel()) * 4
+    out["tta_merge_algorithmic_GBps"] = nbytes / med / 1e3
+
+    def ref_path():
+        ab = list(bd)
+        for i, t in enumerate(tf_o):
+            pbx = ab[i]
+            o = t.inverse().apply_box(pbx.reshape(-1, 4).cpu().numpy())
+            ab[i] = torch.from_numpy(o).to(dev).reshape(pbx.shape)
+        return torch.mean(torch.cat(ab, 0), 0), torch.mean(torch.cat(sd, 0), 0)
+
+    med, _ = timeit(ref_path, max(3, iters // 4), flush)
+    out["tta_merge_reference_composition_us"] = med
+    med, _ = timeit(lambda: tta.inference_one_image_boxes(bd, sd, tf, hw, 1e-5, 0.3, 100), iters, flush)
+    out["tta_one_image_boxes_us"] = med
+    return out
 
 
 if __name__ == "__main__":
