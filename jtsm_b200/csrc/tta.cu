@@ -58,12 +58,21 @@ __global__ void __launch_bounds__(256) tta_merge_kernel(const __grid_constant__ 
     const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
     if (i >= num_boxes) return;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int a = 0; a < num_aug; ++a) {
-      float4 b = tta_apply_ops(__ldg(p.boxes[a] + i), p.ops[a]);
-      acc.x = __fadd_rn(acc.x, b.x);
-      acc.y = __fadd_rn(acc.y, b.y);
-      acc.z = __fadd_rn(acc.z, b.z);
-      acc.w = __fadd_rn(acc.w, b.w);
+    // four independent 16-byte loads in flight per thread; the sum itself stays in list order
+    for (int a0 = 0; a0 < num_aug; a0 += 4) {
+      float4 v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (a0 + j < num_aug) v[j] = __ldg(p.boxes[a0 + j] + i);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (a0 + j >= num_aug) break;
+        float4 b = tta_apply_ops(v[j], p.ops[a0 + j]);
+        acc.x = __fadd_rn(acc.x, b.x);
+        acc.y = __fadd_rn(acc.y, b.y);
+        acc.z = __fadd_rn(acc.z, b.z);
+        acc.w = __fadd_rn(acc.w, b.w);
+      }
     }
     mean_boxes[i] = make_float4(__fdiv_rn(acc.x, fa), __fdiv_rn(acc.y, fa), __fdiv_rn(acc.z, fa),
                                 __fdiv_rn(acc.w, fa));
@@ -71,7 +80,15 @@ __global__ void __launch_bounds__(256) tta_merge_kernel(const __grid_constant__ 
     const long long i = (long long)(blockIdx.x - box_ctas) * 256 + threadIdx.x;
     if (i >= num_scores) return;
     float acc = 0.f;
-    for (int a = 0; a < num_aug; ++a) acc = __fadd_rn(acc, __ldg(p.scores[a] + i));
+    for (int a0 = 0; a0 < num_aug; a0 += 4) {
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (a0 + j < num_aug) v[j] = __ldg(p.scores[a0 + j] + i);
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (a0 + j < num_aug) acc = __fadd_rn(acc, v[j]);
+    }
     mean_scores[i] = __fdiv_rn(acc, fa);
   }
 }

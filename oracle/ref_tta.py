@@ -55,8 +55,21 @@ def tta_transforms(image_hw, orig_hw, min_sizes, max_size, flip, resize_cls=Resi
     return out
 
 
-def get_augmented_boxes(all_boxes, all_scores, tfms):
-    """all_boxes: list of [1, R, 4K] tensors, all_scores: list of [1, R, K+1] -> (mean boxes, mean scores)."""
+def mean_sequential(x):
+    """Mean over dim 0 as ONE sequential fp32 sum in list order followed by a true division -- the arithmetic the
+    device kernel is specified to do.  torch.mean(dim=0) on the CPU computes exactly this for every element of the
+    vectorised body; in the scalar tail of the inner dimension (numel % (4 x SIMD width)) ATen sums the rows in four
+    interleaved accumulators instead, so those few elements can differ by one ulp -- and which elements they are
+    depends on the host's SIMD width.  (On CUDA torch.mean multiplies by 1/A instead of dividing.)"""
+    acc = torch.zeros_like(x[0])
+    for a in range(x.shape[0]):
+        acc = acc + x[a]
+    return acc / x.shape[0]
+
+
+def get_augmented_boxes(all_boxes, all_scores, tfms, mean=None):
+    """all_boxes: list of [1, R, 4K] tensors, all_scores: list of [1, R, K+1] -> (mean boxes, mean scores).
+    mean: None = torch.mean as the reference calls it; `mean_sequential` = the machine-independent definition."""
     all_boxes = list(all_boxes)
     for idx, tfm in enumerate(tfms):
         pred_boxes = all_boxes[idx]
@@ -64,6 +77,8 @@ def get_augmented_boxes(all_boxes, all_scores, tfms):
         assert num_img == 1
         orig = tfm.inverse().apply_box(pred_boxes.reshape(num_pred * num_col // 4, 4).cpu().numpy())
         all_boxes[idx] = torch.from_numpy(orig).reshape(1, num_pred, num_col)
+    if mean is not None:
+        return mean(torch.cat(all_boxes, dim=0)), mean(torch.cat(list(all_scores), dim=0))
     boxes = torch.mean(torch.cat(all_boxes, dim=0), dim=0, keepdim=False)
     scores = torch.mean(torch.cat(list(all_scores), dim=0), dim=0, keepdim=False)
     return boxes, scores

@@ -97,6 +97,19 @@ def test_golden_tta_fixture():
     assert np.array_equal(mb.numpy(), z["mean_boxes"]) and np.array_equal(ms.numpy(), z["mean_scores"])
 
 
+def test_sequential_mean_vs_torch_mean():
+    """The device kernel's definition (ref_tta.mean_sequential) against torch.mean as the reference calls it: at most
+    one ulp apart, and only in the scalar tail of ATen's vectorised outer sum."""
+    g = synth.generator(5)
+    for a, n in ((10, 4000 * 84), (16, 6300), (3, 37)):
+        x = torch.randn(a, n, generator=g) * 50
+        m, t = ref_tta.mean_sequential(x), torch.mean(x, dim=0)
+        bound = 4 * 2.0 ** -24 * x.abs().sum(0)  # a different association of the same a-term sum
+        assert bool(((m - t).abs() <= bound).all())
+        body = n - n % 64
+        assert torch.equal(m[:body], t[:body])
+
+
 def test_host_mirror_transform_lists_match_restatement():
     """jtsm_b200.tta builds the same augmentations (shapes, order) and the inverse stage lists carry the factors the
     numpy code multiplies by."""
