@@ -320,6 +320,23 @@ JTSM_API int jtsm_tta_transform_boxes(const float* boxes, int num_boxes, const i
                                       float image_w, float min_box_size, float* out_boxes,
                                       unsigned char* keep, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Superpixel-set IoU + Matcher: pairwise_iou_sp
+ * (projects/WSL/wsl/modeling/roi_heads/roi_heads_jtsm.py:49-73) as called by
+ * label_and_sample_proposals_wsl (:1627-1634), followed by Matcher.__call__
+ * (detectron2/modeling/matcher.py:61-103, no low-quality matches).
+ * oh1 [n1, S] int32 (targets' superpixel flags), oh2 [n2, S] int32 (proposals'), cnt_sp [S] int64
+ * (pixels per superpixel) -> iou [n1, n2] fp32 = float(inter) / float(area1 + area2 - inter) with exact
+ * integer sums (0 / 0 = NaN as in the reference).  Optional (both or none): matched_idx [n2] int64 =
+ * first arg-max over the targets, matched_label [n2] int8 by the thresholds (as jtsm_refine_match).
+ * n1 == 0: matched_idx = 0, matched_label = label0.  S <= 2844 (shared-memory staging).
+ * ------------------------------------------------------------------------ */
+JTSM_API int jtsm_pairwise_iou_sp(const int* oh1, int n1, const int* oh2, int n2,
+                                  const long long* cnt_sp, int S, float* iou, float iou_t0,
+                                  float iou_t1, int label0, int label1, int label2,
+                                  int num_thresholds, long long* matched_idx,
+                                  signed char* matched_label, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,7 +25,7 @@ _sz = ctypes.c_size_t
 _CTYPE = {
     "void*": _vp, "float*": _vp, "int*": _vp, "char*": ctypes.c_char_p, "int": _i, "float": _f,
     "long long": _ll, "size_t": _sz, "unsigned long long": ctypes.c_ulonglong,
-    "int64_t*": _vp, "int32_t*": _vp, "uint8_t*": _vp, "unsigned char*": _vp,
+    "int64_t*": _vp, "int32_t*": _vp, "uint8_t*": _vp, "unsigned char*": _vp, "signed char*": _vp,
 }
 
 

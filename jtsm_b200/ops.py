@@ -597,3 +597,35 @@ def tta_transform_boxes(boxes, ops_, image_shape, min_box_size=0.0):
         check(lib().jtsm_tta_transform_boxes(_ptr(B), n, ty, aa, bb, float(h), float(w), float(min_box_size),
                                              _ptr(out), _ptr(keep), _stream()), "tta_transform_boxes")
     return out, keep.bool()
+
+
+# --------------------------------------------------------------------------- superpixel IoU
+def pairwise_iou_sp(oh_labels1, oh_labels2, cnt_sp, thresholds=None, labels=None):
+    """pairwise_iou_sp (roi_heads_jtsm.py:49-73) on raw tensors: oh_labels1 [n1, S], oh_labels2 [n2, S] (int32 flags),
+    cnt_sp [S] (pixels per superpixel) -> iou [n1, n2] fp32.  With thresholds / labels (Matcher's constructor
+    arguments) -> (iou, matched_idxs int64 [n2], matched_labels int8 [n2])."""
+    _require_cuda(oh_labels1, oh_labels2, cnt_sp)
+    A = oh_labels1.to(torch.int32).contiguous()
+    B = oh_labels2.to(torch.int32).contiguous()
+    C = cnt_sp.reshape(-1).to(torch.int64).contiguous()
+    n1, n2, s = A.shape[0], B.shape[0], B.shape[1]
+    if A.shape[1] != s or C.numel() != s:
+        raise RuntimeError("jtsm_b200.pairwise_iou_sp: oh_labels1 [n1,S], oh_labels2 [n2,S], cnt_sp [S] expected")
+    dev = B.device
+    iou = torch.empty((n1, n2), dtype=torch.float32, device=dev)
+    mi = ml = None
+    t = [0.0, 0.0]
+    lb = [0, 0, 0]
+    nt = 1
+    if thresholds is not None:
+        nt = len(thresholds)
+        if nt not in (1, 2) or len(labels) != nt + 1:
+            raise RuntimeError("jtsm_b200.pairwise_iou_sp: one or two thresholds, len(labels) = len(thresholds) + 1")
+        t[:nt] = [float(v) for v in thresholds]
+        lb[:nt + 1] = [int(v) for v in labels]
+        mi = torch.empty(n2, dtype=torch.int64, device=dev)
+        ml = torch.empty(n2, dtype=torch.int8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().jtsm_pairwise_iou_sp(_ptr(A), n1, _ptr(B), n2, _ptr(C), s, _ptr(iou), t[0], t[1], lb[0], lb[1], lb[2],
+                                         nt, _ptr(mi), _ptr(ml), _stream()), "pairwise_iou_sp")
+    return iou if thresholds is None else (iou, mi, ml)

@@ -340,3 +340,14 @@ def fast_rcnn_inference_single_image(boxes, scores, image_shape, score_thresh, n
         keep = keep[:topk_per_image]
     return dict(pred_boxes=b[keep], scores=s[keep], pred_classes=fi[keep][:, 1], pred_inds=pred_inds[keep],
                 kept_rois=fi[keep][:, 0])
+
+
+def pairwise_iou_sp(oh_labels1, oh_labels2, cnt_sp):
+    """pairwise_iou_sp, roi_heads_jtsm.py:49-73, without the [n1, n2, S] temporaries: the three sums are exact
+    integer sums, so any order gives the reference's values; the division is the same fp32 division."""
+    c = cnt_sp.reshape(1, -1).to(torch.int64)
+    a, b = oh_labels1.to(torch.int64), oh_labels2.to(torch.int64)
+    inter = (a * c) @ b.t()
+    area1 = (a * c).sum(1, keepdim=True)
+    area2 = (b * c).sum(1).unsqueeze(0)
+    return torch.div(inter.to(torch.float32), (area1 + area2 - inter).to(torch.float32))

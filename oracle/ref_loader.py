@@ -227,3 +227,11 @@ def tta_reference():
     _tta.update(ResizeTransform=tr.ResizeTransform, get_transform=gt, get_augmented_boxes=gab,
                 transform_proposals=tp, Boxes=m["boxes"].Boxes, Instances=m["instances"].Instances)
     return _tta
+
+
+def pairwise_iou_sp_reference():
+    """The reference's own pairwise_iou_sp (roi_heads_jtsm.py:49-73), compiled in place; takes objects with
+    an `.oh_labels` attribute like the reference's Instances."""
+    install()
+    path = os.path.join(WSL, "modeling", "roi_heads", "roi_heads_jtsm.py")
+    return extract_function(path, "pairwise_iou_sp", dict(torch=torch))
