@@ -337,6 +337,28 @@ JTSM_API int jtsm_pairwise_iou_sp(const int* oh1, int n1, const int* oh2, int n2
                                   int num_thresholds, long long* matched_idx,
                                   signed char* matched_label, void* stream);
 
+/* ------------------------------------------------------------------------
+ * PCL loss: wsl/layers/pcl_loss.py:8-88 over
+ * projects/WSL/wsl/layers/csrc/pcl_loss/pcl_loss_cpu.cpp:8-115 (the reference copies the probabilities to
+ * the host and runs this CPU code on every forward and backward).  All arrays fp32 as in the reference:
+ * probs [R, C] (column 0 = background), labels / cls_loss_weights / gt_assignment [R],
+ * pc_labels / pc_probs / pc_count / img_cls_loss_weights [P], im_labels [C].
+ * forward: output [C] per-class sums, loss [1] = sum(output) / R (may be NULL).
+ * backward: grad_probs [R, C], already divided by R; the upstream gradient is not applied (the reference
+ * ignores it, pcl_loss_cpu.cpp:59-115).
+ * ------------------------------------------------------------------------ */
+JTSM_API int jtsm_pcl_loss_forward(const float* probs, const float* labels,
+                                   const float* cls_loss_weights, const float* pc_labels,
+                                   const float* pc_probs, const float* img_cls_loss_weights,
+                                   const float* im_labels, int num_rois, int channels,
+                                   int num_positive, float* output, float* loss, void* stream);
+JTSM_API int jtsm_pcl_loss_backward(const float* probs, const float* labels,
+                                    const float* cls_loss_weights, const float* gt_assignment,
+                                    const float* pc_labels, const float* pc_probs,
+                                    const float* pc_count, const float* img_cls_loss_weights,
+                                    const float* im_labels, int num_rois, int channels,
+                                    int num_positive, float* grad_probs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

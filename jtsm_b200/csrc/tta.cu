@@ -130,11 +130,11 @@ extern "C" int jtsm_tta_merge(const void* const* boxes, const void* const* score
                               const float* op_b, float* mean_boxes, float* mean_scores, void* stream) {
   if (num_aug <= 0 || num_aug > JTSM_TTA_MAX_AUG || num_rois < 0 || boxes_per_row < 0 || score_cols < 0)
     return JTSM_ERR_INVALID_ARGUMENT;
+  if (num_rois == 0) return JTSM_OK;
   const bool do_boxes = boxes && mean_boxes && boxes_per_row > 0;
   const bool do_scores = scores && mean_scores && score_cols > 0;
   if (!do_boxes && !do_scores) return JTSM_ERR_INVALID_ARGUMENT;
   if (do_boxes && (!op_type || !op_a || !op_b)) return JTSM_ERR_INVALID_ARGUMENT;
-  if (num_rois == 0) return JTSM_OK;
   TtaMergeParams p;
   for (int a = 0; a < JTSM_TTA_MAX_AUG; ++a) {
     p.boxes[a] = nullptr;

@@ -629,3 +629,44 @@ def pairwise_iou_sp(oh_labels1, oh_labels2, cnt_sp, thresholds=None, labels=None
         check(lib().jtsm_pairwise_iou_sp(_ptr(A), n1, _ptr(B), n2, _ptr(C), s, _ptr(iou), t[0], t[1], lb[0], lb[1], lb[2],
                                          nt, _ptr(mi), _ptr(ml), _stream()), "pairwise_iou_sp")
     return iou if thresholds is None else (iou, mi, ml)
+
+
+# --------------------------------------------------------------------------- PCL loss
+def _pcl_vec(t, dev):
+    return t.reshape(-1).to(device=dev, dtype=torch.float32).contiguous()
+
+
+def pcl_loss_forward(pcl_probs, labels, cls_loss_weights, pc_labels, pc_probs, img_cls_loss_weights, im_labels):
+    """wsl._C.pcl_loss_forward (pcl_loss_cpu.cpp:8-57) + the `output.sum() / R` of pcl_loss.py:52, on the device.
+    pcl_probs [R, C] CUDA; the small per-proposal / per-cluster vectors may arrive as CPU tensors (the reference builds
+    them with numpy, fast_rcnn_oicr.py:925-935) and are moved once.  -> (loss [1], output [C])."""
+    _require_cuda(pcl_probs)
+    P = _f32c(pcl_probs)
+    dev = P.device
+    r, c = P.shape
+    v = [_pcl_vec(t, dev) for t in (labels, cls_loss_weights, pc_labels, pc_probs, img_cls_loss_weights, im_labels)]
+    if v[0].numel() != r or v[1].numel() != r or v[5].numel() != c or v[3].numel() != v[2].numel() \
+            or v[4].numel() != v[2].numel():
+        raise RuntimeError("jtsm_b200.pcl_loss_forward: inconsistent shapes")
+    out = torch.empty(c, dtype=torch.float32, device=dev)
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().jtsm_pcl_loss_forward(_ptr(P), _ptr(v[0]), _ptr(v[1]), _ptr(v[2]), _ptr(v[3]), _ptr(v[4]), _ptr(v[5]),
+                                          r, c, v[2].numel(), _ptr(out), _ptr(loss), _stream()), "pcl_loss_forward")
+    return loss, out
+
+
+def pcl_loss_backward(pcl_probs, labels, cls_loss_weights, gt_assignment, pc_labels, pc_probs, pc_count,
+                      img_cls_loss_weights, im_labels):
+    """wsl._C.pcl_loss_backward (pcl_loss_cpu.cpp:59-115) followed by `/ R` (pcl_loss.py:84) -> grad [R, C]."""
+    _require_cuda(pcl_probs)
+    P = _f32c(pcl_probs)
+    dev = P.device
+    r, c = P.shape
+    v = [_pcl_vec(t, dev) for t in (labels, cls_loss_weights, gt_assignment, pc_labels, pc_probs, pc_count,
+                                    img_cls_loss_weights, im_labels)]
+    grad = torch.empty_like(P)
+    with torch.cuda.device(dev):
+        check(lib().jtsm_pcl_loss_backward(_ptr(P), *[_ptr(x) for x in v], r, c, v[3].numel(), _ptr(grad), _stream()),
+              "pcl_loss_backward")
+    return grad

@@ -138,3 +138,26 @@ def superpixels(g, n, hs, ws, block=24):
 def oh_labels(g, num_rois, s, p=0.35):
     """oh_labels [R, S] int32: which superpixels are switched on for each RoI."""
     return (torch.rand(num_rois, s, generator=g) < p).to(torch.int32)
+
+
+def pcl_case(g, r, k, p):
+    """Synthetic PCL-loss inputs with the shapes / dtypes wsl/layers/pcl_loss.py passes (all fp32): probs [R, K+1]
+    (column 0 = background), labels / cls_loss_weights / gt_assignment [1, R], pc_* / img_cls_loss_weights [1, P],
+    im_labels [1, K+1].  Proposal clusters: P clusters with distinct-ish classes; labels[i] = class of its cluster or 0."""
+    probs = torch.softmax(torch.randn(r, k + 1, generator=g) * 2, dim=1)
+    probs[::17, 0] = 1e-8  # exercises the eps clamps
+    pc_labels = torch.randint(1, k + 1, (1, p), generator=g).float()
+    gt_assignment = torch.randint(0, p, (1, r), generator=g).float()
+    is_bg = torch.rand(1, r, generator=g) < 0.6
+    labels = torch.where(is_bg, torch.zeros(1, r), pc_labels[0, gt_assignment[0].long()][None])
+    cls_loss_weights = torch.rand(1, r, generator=g)
+    pc_probs = torch.rand(1, p, generator=g) * 0.9 + 1e-7
+    pc_probs[0, ::5] = 1e-9
+    pc_count = torch.randint(1, 40, (1, p), generator=g).float()
+    img_cls_loss_weights = torch.rand(1, p, generator=g)
+    im_labels = torch.zeros(1, k + 1)
+    im_labels[0, 0] = 1.0
+    im_labels[0, pc_labels[0, : max(1, p - 1)].long()] = 1.0  # the last cluster's class may be switched off
+    return dict(probs=probs, labels=labels, cls_loss_weights=cls_loss_weights, gt_assignment=gt_assignment,
+                pc_labels=pc_labels, pc_probs=pc_probs, pc_count=pc_count, img_cls_loss_weights=img_cls_loss_weights,
+                im_labels=im_labels)

@@ -140,3 +140,26 @@ def nms(boxes, scores, thr):
     keep = np.zeros(b.shape[0], np.int64)
     nk = lib().oracle_nms(_p(b), _p(s), b.shape[0], ctypes.c_float(thr), _p(keep))
     return keep[:nk].copy()
+
+
+def pcl_loss_forward(probs, labels, cls_loss_weights, pc_labels, pc_probs, img_cls_loss_weights, im_labels):
+    """-> (output [C], loss = output.sum() / R)  (pcl_loss_cpu.cpp:8-57, pcl_loss.py:52)."""
+    a = [_f32(x).reshape(-1) for x in (labels, cls_loss_weights, pc_labels, pc_probs, img_cls_loss_weights, im_labels)]
+    probs = _f32(probs)
+    r, c = probs.shape
+    out = np.zeros(c, np.float32)
+    lib().oracle_pcl_loss_forward(_p(probs), _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]), _p(a[5]), r, c,
+                                  a[2].shape[0], _p(out))
+    return out, np.float32(out.sum() / np.float32(r))
+
+
+def pcl_loss_backward(probs, labels, cls_loss_weights, gt_assignment, pc_labels, pc_probs, pc_count,
+                      img_cls_loss_weights, im_labels):
+    """-> grad [R, C] / R  (pcl_loss_cpu.cpp:59-115, pcl_loss.py:84)."""
+    a = [_f32(x).reshape(-1) for x in (labels, cls_loss_weights, gt_assignment, pc_labels, pc_probs, pc_count,
+                                       img_cls_loss_weights, im_labels)]
+    probs = _f32(probs)
+    r, c = probs.shape
+    g = np.zeros((r, c), np.float32)
+    lib().oracle_pcl_loss_backward(_p(probs), *[_p(x) for x in a], r, c, _p(g))
+    return g / np.float32(r)

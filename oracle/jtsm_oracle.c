@@ -527,3 +527,47 @@ ORACLE_API int oracle_nms(const float* boxes, const float* scores, int n, float 
   free(sup);
   return nk;
 }
+
+/* ---------------------------------------------------------------------------------------------
+ * PCL loss -- restatement of projects/WSL/wsl/layers/csrc/pcl_loss/pcl_loss_cpu.cpp
+ *   forward  :8-57   (eps 1e-6, float accumulation in index order, logf of the clamped probability)
+ *   backward :59-115 (eps 1e-5; top_grad unused)
+ * Pinned bit for bit to the reference's own file built in place (oracle/_ref/libref_pclloss.so,
+ * tests/test_ref_native.py). */
+void oracle_pcl_loss_forward(const float* prob, const float* labels, const float* clw, const float* pc_labels,
+                             const float* pc_probs, const float* iclw, const float* im_labels, int batch,
+                             int channels, int num_positive, float* out) {
+  const float eps = 1e-6f;
+  for (int c = 0; c < channels; c++) {
+    out[c] = 0;
+    if (im_labels[c] != 0) {
+      if (c == 0) {
+        for (int i = 0; i < batch; i++)
+          if (labels[i] == 0) out[c] -= clw[i] * logf(fmaxf(prob[i * channels + c], eps));
+      } else {
+        for (int i = 0; i < num_positive; i++)
+          if (pc_labels[i] == c) out[c] -= iclw[i] * logf(fmaxf(pc_probs[i], eps));
+      }
+    }
+  }
+}
+
+void oracle_pcl_loss_backward(const float* prob, const float* labels, const float* clw, const float* gt_assignment,
+                              const float* pc_labels, const float* pc_probs, const float* pc_count,
+                              const float* iclw, const float* im_labels, int batch, int channels, float* grad) {
+  const float eps = 1e-5f;
+  (void)pc_labels;
+  for (int i = 0; i < batch; i++) {
+    for (int c = 0; c < channels; c++) {
+      grad[i * channels + c] = 0;
+      if (im_labels[c] != 0) {
+        if (c == 0) {
+          if (labels[i] == 0) grad[i * channels + c] = -clw[i] / fmaxf(prob[i * channels + c], eps);
+        } else if (labels[i] == c) {
+          int p = (int)gt_assignment[i];
+          grad[i * channels + c] = -iclw[p] / fmaxf(pc_count[p] * pc_probs[p], eps);
+        }
+      }
+    }
+  }
+}

@@ -7,6 +7,8 @@ TEST INFRASTRUCTURE ONLY (tests/, __graft_entry__.build()): never imported by jt
    runnable CPU path for these two ops (ROILoopPool.h:62, MOIPool.h:74 raise), so this is the only way to execute
    the reference's arithmetic for them without a GPU; it pins oracle/jtsm_oracle.c's restatement bit for bit.
 
+ * libref_pclloss.so -- projects/WSL/wsl/layers/csrc/pcl_loss/pcl_loss_cpu.cpp (the code the reference's PCL loss always
+   runs, on the CPU) behind plain pointers (oracle/ref_pclloss_driver.cpp).
  * libref_roialign.so -- detectron2/layers/csrc/ROIAlign/ROIAlign_cpu.cpp compiled where it lies against this image's
    ATen (oracle/ref_roialign_driver.cpp): the reference's CPU RoIAlign forward / backward behind plain pointers.
 
@@ -23,6 +25,7 @@ REF = os.environ.get("JTSM_REFERENCE", "/root/reference")
 OUT = os.path.join(HERE, "_ref")
 WSLPOOL = os.path.join(OUT, "libref_wslpool.so")
 ROIALIGN = os.path.join(OUT, "libref_roialign.so")
+PCLLOSS = os.path.join(OUT, "libref_pclloss.so")
 
 _wsl = None
 _align = None
@@ -35,16 +38,44 @@ def build():
     return WSLPOOL if os.path.exists(WSLPOOL) else None
 
 
-def build_roi_align():
-    if os.path.isfile(os.path.join(REF, "detectron2", "layers", "csrc", "ROIAlign", "ROIAlign_cpu.cpp")):
+def _build_aten(target, marker, path):
+    if os.path.isfile(os.path.join(REF, *marker)):
         import torch
         from torch.utils import cpp_extension as ce
 
         inc = " ".join(ce.include_paths())
         libdir = os.path.join(os.path.dirname(torch.__file__), "lib")
         subprocess.run(["make", "-s", "-f", "Makefile.ref", f"REF={REF}", f"TORCH_INC={inc}", f"TORCH_LIB={libdir}",
-                        "_ref/libref_roialign.so"], cwd=HERE, check=True)
-    return ROIALIGN if os.path.exists(ROIALIGN) else None
+                        "_ref/" + target], cwd=HERE, check=True)
+    return path if os.path.exists(path) else None
+
+
+def build_roi_align():
+    return _build_aten("libref_roialign.so", ("detectron2", "layers", "csrc", "ROIAlign", "ROIAlign_cpu.cpp"), ROIALIGN)
+
+
+def build_pcl_loss():
+    return _build_aten("libref_pclloss.so", ("projects", "WSL", "wsl", "layers", "csrc", "pcl_loss", "pcl_loss_cpu.cpp"),
+                       PCLLOSS)
+
+
+_pcl = None
+
+
+def pcl_loss_available():
+    return build_pcl_loss() is not None
+
+
+def pcl():
+    global _pcl
+    if _pcl is None:
+        path = build_pcl_loss()
+        if path is None:
+            raise RuntimeError("oracle/_ref/libref_pclloss.so missing and /root/reference not present")
+        import torch  # noqa: F401
+
+        _pcl = ctypes.CDLL(path)
+    return _pcl
 
 
 def available():
@@ -153,3 +184,24 @@ def roi_align_backward(grad_out, rois, spatial_scale, input_shape, sampling_rati
     align().ref_roi_align_backward(_p(grad_out), _p(rois), r, ctypes.c_float(spatial_scale), ph, pw, n, c, h, w,
                                    int(sampling_ratio), int(bool(aligned)), _p(gi))
     return gi
+
+
+def pcl_loss_forward(probs, labels, cls_loss_weights, pc_labels, pc_probs, img_cls_loss_weights, im_labels):
+    a = [_f32(x).reshape(-1) for x in (labels, cls_loss_weights, pc_labels, pc_probs, img_cls_loss_weights, im_labels)]
+    probs = _f32(probs)
+    r, c = probs.shape
+    out = np.zeros(c, np.float32)
+    pcl().ref_pcl_loss_forward(_p(probs), _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(a[4]), _p(a[5]), r, c,
+                               a[2].shape[0], _p(out))
+    return out
+
+
+def pcl_loss_backward(probs, labels, cls_loss_weights, gt_assignment, pc_labels, pc_probs, pc_count,
+                      img_cls_loss_weights, im_labels):
+    a = [_f32(x).reshape(-1) for x in (labels, cls_loss_weights, gt_assignment, pc_labels, pc_probs, pc_count,
+                                       img_cls_loss_weights, im_labels)]
+    probs = _f32(probs)
+    r, c = probs.shape
+    g = np.zeros((r, c), np.float32)
+    pcl().ref_pcl_loss_backward(_p(probs), *[_p(x) for x in a], r, c, a[3].shape[0], _p(g))
+    return g

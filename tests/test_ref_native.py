@@ -112,3 +112,26 @@ def test_roi_align_restatement_equals_reference_cpu(oracle, aligned, sampling_ra
     gi = oracle.roi_align_backward(go, rois, scale, x.shape, sampling_ratio, aligned)
     rgi = ref_native.roi_align_backward(go, rois, scale, x.shape, sampling_ratio, aligned)
     assert np.array_equal(gi, rgi)  # both serial, same visiting order
+
+
+# ---- PCL loss: the reference's own pcl_loss_cpu.cpp (oracle/_ref/libref_pclloss.so) ----
+_pcl = pytest.mark.skipif(not ref_native.pcl_loss_available(), reason="oracle/_ref/libref_pclloss.so not built")
+
+
+@_pcl
+@pytest.mark.parametrize("r,k,p", [(300, 20, 6), (2000, 20, 12), (50, 80, 1), (7, 3, 4)])
+def test_pcl_loss_restatement_equals_reference_cpu(oracle, r, k, p):
+    c = synth.pcl_case(synth.generator(60 + r), r, k, p)
+    n = {kk: v.numpy() for kk, v in c.items()}
+    out, _ = oracle.pcl_loss_forward(n["probs"], n["labels"], n["cls_loss_weights"], n["pc_labels"], n["pc_probs"],
+                                     n["img_cls_loss_weights"], n["im_labels"])
+    rout = ref_native.pcl_loss_forward(n["probs"], n["labels"], n["cls_loss_weights"], n["pc_labels"], n["pc_probs"],
+                                       n["img_cls_loss_weights"], n["im_labels"])
+    assert np.array_equal(out, rout)
+    g = oracle.pcl_loss_backward(n["probs"], n["labels"], n["cls_loss_weights"], n["gt_assignment"], n["pc_labels"],
+                                 n["pc_probs"], n["pc_count"], n["img_cls_loss_weights"], n["im_labels"])
+    rg = ref_native.pcl_loss_backward(n["probs"], n["labels"], n["cls_loss_weights"], n["gt_assignment"],
+                                      n["pc_labels"], n["pc_probs"], n["pc_count"], n["img_cls_loss_weights"],
+                                      n["im_labels"])
+    assert np.array_equal(g, rg / np.float32(r))
+    assert (out != 0).sum() >= 2 and (g != 0).sum() > 0
