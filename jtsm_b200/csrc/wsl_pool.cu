@@ -248,6 +248,87 @@ moi_pool_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int
   }
 }
 
+// Row bit masks: rowbits[r, h] = 128-bit mask over the columns of row h (bit w = mask[r, h, w]); W <= 128.
+// One warp per (RoI, row); four ballots.  15 MB of byte mask become 2.4 MB at config 2, and the pooling kernel
+// reads one 16-byte word per bin row instead of one byte per cell.
+__global__ void __launch_bounds__(256)
+moi_pack_kernel(const unsigned char* __restrict__ mask, int rows /* R*H */, int W, uint4* __restrict__ rowbits) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const unsigned char* m = mask + (size_t)row * W;
+  uint32_t b[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int w = k * 32 + lane;
+    b[k] = __ballot_sync(0xffffffffu, w < W && m[w] != 0);
+  }
+  if (lane == 0) rowbits[row] = make_uint4(b[0], b[1], b[2], b[3]);
+}
+
+// MOIPool forward over row bit masks: only the switched-on cells of a bin are visited (row-major, strict >, so the
+// value and the first arg-max are the reference's), no per-cell mask loads.
+template <typename T>
+__global__ void __launch_bounds__(kWslThreads)
+moi_pool_fwd_bits_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW, int splits,
+                         PoolWorkspace ws, const uint4* __restrict__ rowbits,
+                         const float* __restrict__ scales, int num_rois, T* __restrict__ output,
+                         int* __restrict__ argmax) {
+  extern __shared__ float plane_s[];
+  const int item = blockIdx.x;
+  const int s = item % splits;
+  const int nc = item / splits;
+  const int n = nc / channels;
+  const int c = nc - n * channels;
+  const int first = ws.first[n];
+  const int last = -ws.neg_last[n];
+  if (first > last) return;
+  const int len = last - first + 1;
+  const int r0 = first + (int)(((long long)len * s) / splits);
+  const int r1 = first + (int)(((long long)len * (s + 1)) / splits);
+  if (r0 >= r1) return;
+  const int hw = H * W;
+  const T* src = input + (size_t)nc * hw;
+  for (int p = threadIdx.x; p < hw; p += kWslThreads) plane_s[p] = Elem<T>::to_f(src[p]);
+  __syncthreads();
+  const int PP = PH * PW;
+  const int total = (r1 - r0) * PP;
+  for (int i = threadIdx.x; i < total; i += kWslThreads) {
+    const int rl = i / PP;
+    const int bin = i - rl * PP;
+    const int ph = bin / PW, pw = bin - ph * PW;
+    const int r = r0 + rl;
+    if (ws.batch_idx[r] != n) continue;
+    const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
+    const int w_lo = range_lo(wb), w_hi = range_hi(wb);
+    const uint4* rm = rowbits + (size_t)r * H;
+    float m = -FLT_MAX;
+    int mi = -1;
+    for (int h = range_lo(hb); h < range_hi(hb); ++h) {
+      const uint4 q = __ldg(rm + h);
+      for (int c0 = w_lo; c0 < w_hi; c0 += 32) {
+        const int word = c0 >> 5, sh = c0 & 31;
+        const uint32_t a = word == 0 ? q.x : word == 1 ? q.y : word == 2 ? q.z : q.w;
+        const uint32_t b = word == 0 ? q.y : word == 1 ? q.z : word == 2 ? q.w : 0u;
+        const int nb = min(32, w_hi - c0);
+        uint32_t bits = __funnelshift_r(a, b, sh) & (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
+        const int base = h * W + c0;
+        while (bits) {
+          const int j = __ffs(bits) - 1;
+          bits &= bits - 1;
+          const float v = plane_s[base + j];
+          if (v > m) { m = v; mi = base + j; }
+        }
+      }
+    }
+    const size_t o = ((size_t)r * channels + c) * PP + bin;
+    float v = mi == -1 ? 0.f : m;
+    if (scales) v = __fmul_rn(__fmul_rn(v, scales[r]), scales[num_rois + r]);
+    output[o] = Elem<T>::from_f(v);
+    argmax[o] = mi;
+  }
+}
+
 // Per-RoI scales of the JTSM heads (roi_heads_jtsm.py:615-633), fused into the pooling epilogue:
 //   mask_scale = P*P * 1 / (#bins with at least one switched-on cell + 1)   -- the bins whose arg-max is not -1
 //   row scale  = objectness_logits + 1 (caller supplied)
@@ -370,7 +451,8 @@ extern "C" size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width
                                                 int pooled_w) {
   if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 || height < 0 || width < 0) return 0;
   return pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 1) +
-         align_up((size_t)num_rois * height * width, 256) + 256;
+         align_up((size_t)num_rois * height * width, 256) + 256 +
+         align_up((size_t)num_rois * height * sizeof(uint4), 256);  // byte mask + row bit masks
 }
 
 extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const int* oh_labels, int len_labels,
@@ -413,8 +495,20 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
   const int splits = wsl_splits(planes, num_rois);
   const size_t smem = (size_t)hw * sizeof(float);
   const bool use_smem = smem <= 200 * 1024;
+  const bool use_bits = use_smem && width <= 128 && tuning("moi_bits", 1) != 0;
+  uint4* rowbits = (uint4*)(mask + align_up((size_t)num_rois * hw, 256));
+  if (use_bits) {
+    const int rows = num_rois * height;
+    moi_pack_kernel<<<(rows + 7) / 8, 256, 0, st>>>(mask, rows, width, rowbits);
+    count_launch();
+  }
   JTSM_DISPATCH_DTYPE(dtype, T, {
-    if (use_smem) {
+    if (use_bits) {
+      auto k = moi_pool_fwd_bits_kernel<T>;
+      if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
+                                                     splits, ws, rowbits, scales, num_rois, (T*)output, argmax);
+    } else if (use_smem) {
       auto k = moi_pool_fwd_kernel<T, true>;
       if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
