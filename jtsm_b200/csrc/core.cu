@@ -23,7 +23,8 @@ std::map<std::string, int>& tuning_map() {
       {"roi_align_bwd_algo", 0},   // 0 = auto (separable: column kernel for PH <= 16, else cell kernel), 1 = one RED per tap, 2 = cell kernel
       {"roi_align_fwd_algo", 0},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
       {"roi_align_force_gmem", 0},
-      {"moi_bits", 1},             // 1 = MOIPool forward over row bit masks (W <= 128), 0 = byte-mask scan
+      {"moi_planes", 2},           // channels per CTA of the MOIPool visit-list kernel (1 or 2)
+      {"moi_algo", 0},             // MOIPool forward: 0 = auto (per-bin visit lists), 1 = row bit masks, 2 = byte-mask scan
   };
   return m;
 }

@@ -248,6 +248,108 @@ moi_pool_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int
   }
 }
 
+// ---- superpixel mask straight into row bit masks (visit-list path) ------------------------------------------------
+// Which superpixels lie under a feature cell does not depend on the RoI: `moi_cell_ids_kernel` resolves it once per
+// image (up to kMoiCellIds distinct ids per cell; more -> the cell is flagged and its footprint is rescanned per RoI).
+// `moi_rowbits_kernel` then evaluates mask[r, h, w] = inside the RoI rectangle && some id of the cell is switched on
+// (MOIPool_cuda.cu:151-214) for the rows of the RoI rectangle only, a warp per (RoI, row), and ballots the result
+// into the 128-bit row word -- no [R, H, W] byte mask.
+constexpr int kMoiCellIds = 8;
+
+__device__ __forceinline__ void moi_footprint(int h, int w, float ss, int Hs, int Ws, int& hh0, int& hh1, int& ww0,
+                                              int& ww1) {
+  hh0 = (int)floorf(__fdiv_rn((float)h, ss));
+  ww0 = (int)floorf(__fdiv_rn((float)w, ss));
+  hh1 = (int)ceilf(__fdiv_rn((float)(h + 1), ss));
+  ww1 = (int)ceilf(__fdiv_rn((float)(w + 1), ss));
+  hh0 = min(max(hh0, 0), Hs); hh1 = min(max(hh1, 0), Hs);
+  ww0 = min(max(ww0, 0), Ws); ww1 = min(max(ww1, 0), Ws);
+}
+
+__global__ void __launch_bounds__(256)
+moi_cell_ids_kernel(const int* __restrict__ superpixels, int Hs, int Ws, int batch, int H, int W,
+                    int* __restrict__ cell_ids /* [batch, H*W, kMoiCellIds] */,
+                    unsigned char* __restrict__ cell_cnt /* [batch, H*W]; 255 = more than kMoiCellIds */) {
+  const int hw = H * W;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int b = blockIdx.y;
+  if (p >= hw) return;
+  const int h = p / W, w = p - h * W;
+  const float ss = (float)(1.0 * H / (double)Hs);  // MOIPool_cuda.cu:175
+  int hh0, hh1, ww0, ww1;
+  moi_footprint(h, w, ss, Hs, Ws, hh0, hh1, ww0, ww1);
+  const int* spp = superpixels + (size_t)b * Hs * Ws;
+  int ids[kMoiCellIds];
+  int cnt = 0;
+  bool over = false;
+  for (int hh = hh0; hh < hh1 && !over; ++hh)
+    for (int ww = ww0; ww < ww1; ++ww) {
+      const int id = __ldg(spp + (size_t)hh * Ws + ww);
+      bool seen = false;
+#pragma unroll
+      for (int k = 0; k < kMoiCellIds; ++k) seen |= (k < cnt && ids[k] == id);
+      if (seen) continue;
+      if (cnt == kMoiCellIds) { over = true; break; }
+#pragma unroll
+      for (int k = 0; k < kMoiCellIds; ++k)
+        if (k == cnt) ids[k] = id;
+      ++cnt;
+    }
+  int* dst = cell_ids + ((size_t)b * hw + p) * kMoiCellIds;
+#pragma unroll
+  for (int k = 0; k < kMoiCellIds; ++k) dst[k] = k < cnt ? ids[k] : -1;
+  cell_cnt[(size_t)b * hw + p] = over ? 255 : (unsigned char)cnt;
+}
+
+__global__ void __launch_bounds__(256)
+moi_rowbits_kernel(const float* __restrict__ rois, const int* __restrict__ oh_labels, int len_labels,
+                   const int* __restrict__ superpixels, int Hs, int Ws, int batch, int H, int W, float scale,
+                   int num_rois, const int* __restrict__ cell_ids, const unsigned char* __restrict__ cell_cnt,
+                   uint4* __restrict__ rowbits) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= num_rois * H) return;
+  const int r = row / H, h = row - r * H;
+  const float* q = rois + (size_t)r * 5;
+  const int b = (int)q[0];
+  const RoiRect rc = roi_rect(q[1], q[2], q[3], q[4], scale);
+  uint32_t bits[4] = {0u, 0u, 0u, 0u};
+  if (b >= 0 && b < batch && h >= rc.sh && h <= rc.eh) {
+    const int hw = H * W;
+    const int* ohl = oh_labels + (size_t)r * len_labels;
+    const float ss = (float)(1.0 * H / (double)Hs);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int w = k * 32 + lane;
+      bool v = false;
+      if (k * 32 <= rc.ew && k * 32 + 31 >= rc.sw) {  // warp-uniform: this 32-column chunk meets the rectangle
+        if (w < W && w >= rc.sw && w <= rc.ew) {
+          const size_t cell = (size_t)b * hw + (size_t)h * W + w;
+          const int cnt = cell_cnt[cell];
+          if (cnt != 255) {
+            const int* ids = cell_ids + cell * kMoiCellIds;
+            for (int j = 0; j < cnt && !v; ++j) {
+              const int id = __ldg(ids + j);
+              v = id >= 0 && id < len_labels && __ldg(ohl + id) == 1;
+            }
+          } else {  // many superpixels under this cell: scan the footprint like the reference
+            int hh0, hh1, ww0, ww1;
+            moi_footprint(h, w, ss, Hs, Ws, hh0, hh1, ww0, ww1);
+            const int* spp = superpixels + (size_t)b * Hs * Ws;
+            for (int hh = hh0; hh < hh1 && !v; ++hh)
+              for (int ww = ww0; ww < ww1; ++ww) {
+                const int id = __ldg(spp + (size_t)hh * Ws + ww);
+                if (id >= 0 && id < len_labels && __ldg(ohl + id) == 1) { v = true; break; }
+              }
+          }
+        }
+        bits[k] = __ballot_sync(0xffffffffu, v);
+      }
+    }
+  }
+  if (lane == 0) rowbits[row] = make_uint4(bits[0], bits[1], bits[2], bits[3]);
+}
+
 // Row bit masks: rowbits[r, h] = 128-bit mask over the columns of row h (bit w = mask[r, h, w]); W <= 128.
 // One warp per (RoI, row); four ballots.  15 MB of byte mask become 2.4 MB at config 2, and the pooling kernel
 // reads one 16-byte word per bin row instead of one byte per cell.
@@ -329,6 +431,175 @@ moi_pool_fwd_bits_kernel(const T* __restrict__ input, int channels, int H, int W
   }
 }
 
+// ---- visit lists -----------------------------------------------------------------------------------------------
+// Everything about "which cells does bin (r, ph, pw) look at" is channel independent, so it is resolved ONCE per call:
+// per bin a packed list of the switched-on cells' row-major indices (uint16, row-major order, padded to a multiple of
+// four with the sentinel index hw whose plane value is -FLT_MAX), and one descriptor word
+//   desc[r * PP + bin] = (first quad of the list inside the RoI's slot) << 15 | number of quads   (both < 2^15).
+// The per-plane kernel then runs one flat loop per bin: an 8-byte list load gives four indices, four shared-memory
+// loads, four ordered compares -- no mask tests, no bit scans, no row loop.  A RoI's slot holds
+// `cap_quads` uint2 entries (worst case: every cell of every bin switched on).
+constexpr int kMoiListThreads = 128;
+constexpr int kMoiSortMaxBins = 256;  // bins are sorted by list length up to 16 x 16 outputs per RoI
+
+__device__ __forceinline__ uint32_t moi_row_bits(const uint4 q, int c0, int w_hi) {
+  const int word = c0 >> 5, sh = c0 & 31;
+  const uint32_t a = word == 0 ? q.x : word == 1 ? q.y : word == 2 ? q.z : q.w;
+  const uint32_t b = word == 0 ? q.y : word == 1 ? q.z : word == 2 ? q.w : 0u;
+  const int nb = min(32, w_hi - c0);
+  return __funnelshift_r(a, b, sh) & (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
+}
+
+__global__ void __launch_bounds__(kMoiListThreads)
+moi_list_kernel(int H, int W, int PH, int PW, PoolWorkspace ws, const uint4* __restrict__ rowbits,
+                unsigned int cap_quads, uint32_t* __restrict__ desc, unsigned short* __restrict__ perm,
+                uint2* __restrict__ lists, const float* __restrict__ row_scale, int use_mask_scale, int num_rois,
+                float* __restrict__ scales /* [3R] or NULL: as moi_scale_kernel */) {
+  __shared__ uint32_t s_quads[64 * 64 + 1];
+  const int r = blockIdx.x;
+  const int PP = PH * PW;
+  const uint4* rm = rowbits + (size_t)r * H;
+  // 1. quads per bin
+  for (int bin = threadIdx.x; bin < PP; bin += kMoiListThreads) {
+    const int ph = bin / PW, pw = bin - ph * PW;
+    const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
+    int cnt = 0;
+    for (int h = range_lo(hb); h < range_hi(hb); ++h) {
+      const uint4 q = __ldg(rm + h);
+      for (int c0 = range_lo(wb); c0 < range_hi(wb); c0 += 32) cnt += __popc(moi_row_bits(q, c0, range_hi(wb)));
+    }
+    s_quads[bin] = (uint32_t)(cnt + 3) >> 2;
+  }
+  __syncthreads();
+  // 2. exclusive scan (PP <= 4096; serial by one thread is ~50 adds at 7 x 7)
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    int valid = 0;  // bins with at least one switched-on cell
+    for (int bin = 0; bin < PP; ++bin) {
+      const uint32_t n = s_quads[bin];
+      s_quads[bin] = run;
+      run += n;
+      valid += n != 0;
+    }
+    s_quads[PP] = run;
+    if (scales) {  // roi_heads_jtsm.py:615-633, same arithmetic as moi_scale_kernel
+      const float ms = use_mask_scale ? __fmul_rn((float)PP, __frcp_rn((float)valid + 1.f)) : 1.f;
+      const float rs = row_scale ? row_scale[r] : 1.f;
+      scales[r] = ms;
+      scales[num_rois + r] = rs;
+      scales[2 * (size_t)num_rois + r] = __fmul_rn(ms, rs);
+    }
+  }
+  __syncthreads();
+  // 3. fill the lists (slot layout in bin order) and emit descriptors in SORTED order: position k of a RoI holds the
+  //    bin with the k-th most quads (ties: lower bin first), so the lanes of a warp run similar trip counts; the
+  //    output run of a (RoI, channel) is still written by neighbouring lanes, only permuted.
+  const int hw = H * W;
+  uint2* slot = lists + (size_t)r * cap_quads;
+  for (int bin = threadIdx.x; bin < PP; bin += kMoiListThreads) {
+    const int ph = bin / PW, pw = bin - ph * PW;
+    const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
+    const uint32_t start = s_quads[bin];
+    const uint32_t nq = s_quads[bin + 1] - start;
+    int pos = bin;
+    if (PP <= kMoiSortMaxBins) {
+      pos = 0;
+      for (int o = 0; o < PP; ++o) {
+        const uint32_t no = s_quads[o + 1] - s_quads[o];
+        pos += (no > nq) || (no == nq && o < bin);
+      }
+    }
+    desc[(size_t)r * PP + pos] = (start << 15) | nq;
+    perm[(size_t)r * PP + pos] = (unsigned short)bin;
+    unsigned short* dst = (unsigned short*)(slot + start);
+    int k = 0;
+    for (int h = range_lo(hb); h < range_hi(hb); ++h) {
+      const uint4 q = __ldg(rm + h);
+      for (int c0 = range_lo(wb); c0 < range_hi(wb); c0 += 32) {
+        uint32_t bits = moi_row_bits(q, c0, range_hi(wb));
+        const int base = h * W + c0;
+        while (bits) {
+          dst[k++] = (unsigned short)(base + __ffs(bits) - 1);
+          bits &= bits - 1;
+        }
+      }
+    }
+    for (; k < (int)(nq * 4); ++k) dst[k] = (unsigned short)hw;
+  }
+}
+
+// NPL planes (channels of one image) per CTA: a list quad is loaded and unpacked once for NPL channels.
+constexpr int kMoiFwdThreads = 512;
+
+template <typename T, int NPL>
+__global__ void __launch_bounds__(kMoiFwdThreads)
+moi_pool_fwd_list_kernel(const T* __restrict__ input, int channels, int H, int W, int PP, int splits,
+                         PoolWorkspace ws, const uint32_t* __restrict__ desc,
+                         const unsigned short* __restrict__ perm, const uint2* __restrict__ lists,
+                         unsigned int cap_quads, const float* __restrict__ scales, int num_rois,
+                         T* __restrict__ output, int* __restrict__ argmax) {
+  extern __shared__ float plane_s[];
+  const int item = blockIdx.x;
+  const int s = item % splits;
+  const int grp = item / splits;                 // group of NPL consecutive channels of one image
+  const int groups_per_image = channels / NPL;   // channels % NPL == 0 (launcher)
+  const int n = grp / groups_per_image;
+  const int c0 = (grp - n * groups_per_image) * NPL;
+  const int first = ws.first[n];
+  const int last = -ws.neg_last[n];
+  if (first > last) return;
+  const int len = last - first + 1;
+  const int r0 = first + (int)(((long long)len * s) / splits);
+  const int r1 = first + (int)(((long long)len * (s + 1)) / splits);
+  if (r0 >= r1) return;
+  const int hw = H * W;
+  const int pitch = hw + 1;  // + the padding cell
+  const T* src = input + ((size_t)n * channels + c0) * hw;
+  for (int p = threadIdx.x; p < NPL * hw; p += kMoiFwdThreads) {
+    const int k = p / hw;
+    plane_s[p + k] = Elem<T>::to_f(src[p]);
+  }
+  if (threadIdx.x < NPL) plane_s[threadIdx.x * pitch + hw] = -FLT_MAX;  // never beats the running maximum
+  __syncthreads();
+  const int total = (r1 - r0) * PP;
+  for (int i = threadIdx.x; i < total; i += kMoiFwdThreads) {
+    const int rl = i / PP;
+    const int k = i - rl * PP;
+    const int r = r0 + rl;
+    if (ws.batch_idx[r] != n) continue;
+    const uint32_t d = __ldg(desc + (size_t)r * PP + k);
+    const int bin = __ldg(perm + (size_t)r * PP + k);
+    const uint2* lp = lists + (size_t)r * cap_quads + (d >> 15);
+    const int nq = (int)(d & 32767u);
+    float m[NPL];
+    int mi[NPL];
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) m[j] = -FLT_MAX, mi[j] = -1;
+    for (int q = 0; q < nq; ++q) {
+      const uint2 e = __ldg(lp + q);
+      const int i0 = e.x & 0xffff, i1 = e.x >> 16, i2 = e.y & 0xffff, i3 = e.y >> 16;
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) {
+        const float* pl = plane_s + j * pitch;
+        const float v0 = pl[i0], v1 = pl[i1], v2 = pl[i2], v3 = pl[i3];
+        if (v0 > m[j]) { m[j] = v0; mi[j] = i0; }
+        if (v1 > m[j]) { m[j] = v1; mi[j] = i1; }
+        if (v2 > m[j]) { m[j] = v2; mi[j] = i2; }
+        if (v3 > m[j]) { m[j] = v3; mi[j] = i3; }
+      }
+    }
+    float sc = 1.f, sr = 1.f;
+    if (scales) sc = scales[r], sr = scales[num_rois + r];
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+      const size_t o = ((size_t)r * channels + c0 + j) * PP + bin;
+      float v = mi[j] == -1 ? 0.f : m[j];
+      if (scales) v = __fmul_rn(__fmul_rn(v, sc), sr);  // (f * mask_scale) * (objectness + 1)
+      output[o] = Elem<T>::from_f(v);
+      argmax[o] = mi[j];
+    }
+  }
+}
 // Per-RoI scales of the JTSM heads (roi_heads_jtsm.py:615-633), fused into the pooling epilogue:
 //   mask_scale = P*P * 1 / (#bins with at least one switched-on cell + 1)   -- the bins whose arg-max is not -1
 //   row scale  = objectness_logits + 1 (caller supplied)
@@ -447,12 +718,27 @@ extern "C" int jtsm_roi_loop_pool_forward(const void* input, const float* rois, 
   return cuda_status();
 }
 
+namespace {
+// uint2 (= four uint16 cell indices) entries per RoI slot: the bins of a RoI overlap by at most one row / column,
+// so their cells sum to at most (H + PH)(W + PW); + 3 padding entries per bin.  0 = visit lists not applicable.
+size_t moi_cap_quads(int H, int W, int PH, int PW) {
+  if (W > 128 || (long long)H * W > 65534) return 0;
+  const size_t q = ((size_t)(H + PH) * (W + PW) + 3 * (size_t)PH * PW) / 4 + 1;
+  return q < 32768 ? q : 0;
+}
+}  // namespace
+
 extern "C" size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width, int num_rois, int pooled_h,
                                                 int pooled_w) {
   if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 || height < 0 || width < 0) return 0;
   return pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 1) +
          align_up((size_t)num_rois * height * width, 256) + 256 +
-         align_up((size_t)num_rois * height * sizeof(uint4), 256);  // byte mask + row bit masks
+         align_up((size_t)num_rois * height * sizeof(uint4), 256) +  // byte mask + row bit masks
+         align_up((size_t)num_rois * pooled_h * pooled_w * sizeof(uint32_t), 256) +  // list descriptors
+         align_up((size_t)num_rois * pooled_h * pooled_w * sizeof(unsigned short), 256) +  // sorted bin order
+         align_up((size_t)num_rois * moi_cap_quads(height, width, pooled_h, pooled_w) * sizeof(uint2), 256) +
+         align_up((size_t)batch * height * width * kMoiCellIds * sizeof(int), 256) +  // superpixel ids per cell
+         align_up((size_t)batch * height * width, 256);
 }
 
 extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const int* oh_labels, int len_labels,
@@ -479,31 +765,67 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
   moi_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width, spatial_scale,
                                                           pooled_h, pooled_w, ws);
   const int hw = height * width;
-  dim3 mgrid((hw + 255) / 256 > 32 ? 32 : (hw + 255) / 256, num_rois);
-  moi_mask_kernel<<<mgrid, 256, 0, st>>>(rois, oh_labels, len_labels, superpixels, height_sp, width_sp, batch,
-                                         height, width, spatial_scale, num_rois, mask);
-  count_launch(2);
-  const float* scales = nullptr;
-  if (row_scale || mask_scale) {
-    if (!scale_out) return JTSM_ERR_INVALID_ARGUMENT;  // [3 * num_rois]: the backward needs the product
-    moi_scale_kernel<<<(num_rois + 7) / 8, 256, 0, st>>>(num_rois, width, hw, pooled_h, pooled_w, ws, mask, row_scale,
-                                                        mask_scale, scale_out);
-    count_launch();
-    scales = scale_out;
-  }
   const int planes = batch * channels;
   const int splits = wsl_splits(planes, num_rois);
   const size_t smem = (size_t)hw * sizeof(float);
   const bool use_smem = smem <= 200 * 1024;
-  const bool use_bits = use_smem && width <= 128 && tuning("moi_bits", 1) != 0;
+  const int algo = tuning("moi_algo", 0);  // 0 = auto (visit lists), 1 = row bit masks, 2 = byte-mask scan
+  const bool use_bits = use_smem && width <= 128 && algo != 2;
+  const size_t cap_quads = moi_cap_quads(height, width, pooled_h, pooled_w);
+  const bool use_list = use_bits && cap_quads != 0 && algo == 0 && smem + sizeof(float) <= 200 * 1024;
+  // workspace after the bin tables: byte mask | row bit masks | list descriptors | sorted bin order | lists |
+  // per-cell superpixel ids | per-cell id counts
+  const size_t npp = (size_t)num_rois * pooled_h * pooled_w;
   uint4* rowbits = (uint4*)(mask + align_up((size_t)num_rois * hw, 256));
-  if (use_bits) {
+  uint32_t* desc = (uint32_t*)((unsigned char*)rowbits + align_up((size_t)num_rois * height * sizeof(uint4), 256));
+  unsigned short* perm = (unsigned short*)((unsigned char*)desc + align_up(npp * sizeof(uint32_t), 256));
+  uint2* lists = (uint2*)((unsigned char*)perm + align_up(npp * sizeof(unsigned short), 256));
+  int* cell_ids = (int*)((unsigned char*)lists + align_up((size_t)num_rois * cap_quads * sizeof(uint2), 256));
+  unsigned char* cell_cnt = (unsigned char*)cell_ids + align_up((size_t)batch * hw * kMoiCellIds * sizeof(int), 256);
+  if ((row_scale || mask_scale) && !scale_out) return JTSM_ERR_INVALID_ARGUMENT;  // [3 * num_rois]
+  const float* scales = (row_scale || mask_scale) ? scale_out : nullptr;
+  if (use_list) {
+    // RoI independent: superpixel ids under every cell; then the mask, straight into row bit masks
+    moi_cell_ids_kernel<<<dim3((hw + 255) / 256, batch), 256, 0, st>>>(superpixels, height_sp, width_sp, batch, height,
+                                                                      width, cell_ids, cell_cnt);
     const int rows = num_rois * height;
-    moi_pack_kernel<<<(rows + 7) / 8, 256, 0, st>>>(mask, rows, width, rowbits);
-    count_launch();
+    moi_rowbits_kernel<<<(rows + 7) / 8, 256, 0, st>>>(rois, oh_labels, len_labels, superpixels, height_sp, width_sp,
+                                                       batch, height, width, spatial_scale, num_rois, cell_ids,
+                                                       cell_cnt, rowbits);
+    moi_list_kernel<<<num_rois, kMoiListThreads, 0, st>>>(height, width, pooled_h, pooled_w, ws, rowbits,
+                                                          (unsigned int)cap_quads, desc, perm, lists, row_scale,
+                                                          mask_scale, num_rois, scales ? scale_out : nullptr);
+    count_launch(4);
+  } else {
+    dim3 mgrid((hw + 255) / 256 > 32 ? 32 : (hw + 255) / 256, num_rois);
+    moi_mask_kernel<<<mgrid, 256, 0, st>>>(rois, oh_labels, len_labels, superpixels, height_sp, width_sp, batch,
+                                           height, width, spatial_scale, num_rois, mask);
+    count_launch(2);
+    if (scales) {
+      moi_scale_kernel<<<(num_rois + 7) / 8, 256, 0, st>>>(num_rois, width, hw, pooled_h, pooled_w, ws, mask,
+                                                          row_scale, mask_scale, scale_out);
+      count_launch();
+    }
+    if (use_bits) {
+      const int rows = num_rois * height;
+      moi_pack_kernel<<<(rows + 7) / 8, 256, 0, st>>>(mask, rows, width, rowbits);
+      count_launch();
+    }
   }
   JTSM_DISPATCH_DTYPE(dtype, T, {
-    if (use_bits) {
+    if (use_list) {
+      const int npl_want = tuning("moi_planes", 2);
+      const bool two = npl_want >= 2 && channels % 2 == 0 && 2 * (smem + sizeof(float)) <= 200 * 1024;
+      const int npl = two ? 2 : 1;
+      const size_t sm = npl * (smem + sizeof(float));
+      const int groups = planes / npl;
+      const int lsplits = wsl_splits(groups, num_rois);
+      auto k = two ? moi_pool_fwd_list_kernel<T, 2> : moi_pool_fwd_list_kernel<T, 1>;
+      if (sm > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+      k<<<groups * lsplits, kMoiFwdThreads, sm, st>>>((const T*)input, channels, height, width, pooled_h * pooled_w,
+                                                      lsplits, ws, desc, perm, lists, (unsigned int)cap_quads, scales,
+                                                      num_rois, (T*)output, argmax);
+    } else if (use_bits) {
       auto k = moi_pool_fwd_bits_kernel<T>;
       if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,

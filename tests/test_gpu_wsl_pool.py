@@ -98,30 +98,32 @@ def test_moi_pool_fused_jtsm_scales(cuda, oracle):
     np.testing.assert_allclose(xg.grad.cpu().numpy(), gi_ref, rtol=1e-5, atol=1e-5 * float(np.abs(gi_ref).max()))
 
 
-@pytest.mark.parametrize("n,c,h,w,r,scale,pooled,img", [
-    (1, 5, 75, 100, 300, 1 / 8.0, (7, 7), (600, 800)),   # row bit masks (W <= 128), incl. RoIs wider than 32 cells
-    (1, 3, 75, 100, 50, 1 / 8.0, (1, 2), (600, 800)),    # bins wider than 32 cells: several 32-bit chunks per row
-    (1, 2, 60, 150, 60, 1 / 8.0, (7, 7), (480, 1200)),   # W > 128: byte-mask kernel
-    (1, 3, 32, 128, 60, 1 / 8.0, (7, 7), (256, 1024)),   # W == 128 exactly
+@pytest.mark.parametrize("n,c,h,w,r,scale,pooled,img,block", [
+    (1, 5, 75, 100, 300, 1 / 8.0, (7, 7), (600, 800), 24),   # visit lists / row bit masks (W <= 128), RoIs wider than 32 cells
+    (2, 4, 75, 100, 120, 1 / 8.0, (7, 7), (600, 800), 24),   # two images, two channels per CTA
+    (1, 3, 75, 100, 50, 1 / 8.0, (1, 2), (600, 800), 24),    # bins wider than 32 cells: several 32-bit chunks per row
+    (1, 3, 75, 100, 40, 1 / 8.0, (7, 7), (600, 800), 2),     # > 8 superpixels under a cell: footprint rescan
+    (1, 2, 60, 150, 60, 1 / 8.0, (7, 7), (480, 1200), 24),   # W > 128: byte-mask kernel
+    (1, 3, 32, 128, 60, 1 / 8.0, (7, 7), (256, 1024), 24),   # W == 128 exactly, odd channel count
 ])
-def test_moi_pool_bit_mask_path_equals_byte_mask_path_and_oracle(cuda, oracle, n, c, h, w, r, scale, pooled, img):
+def test_moi_pool_list_bits_and_byte_paths_equal_oracle(cuda, oracle, n, c, h, w, r, scale, pooled, img, block):
     from jtsm_b200 import _lib, ops
 
     g = synth.generator(75 + w)
     x = synth.feature_map(g, n, c, h, w)
     rois = synth.rois_from_boxes([synth.proposals(g, r, *img) for _ in range(n)])
     rois[0, 1:] = torch.tensor([0.0, 0.0, img[1] - 1.0, img[0] - 1.0])  # whole image
-    sp, s = synth.superpixels(g, n, img[0], img[1], 24)
+    sp, s = synth.superpixels(g, n, img[0], img[1], block)
     oh = synth.oh_labels(g, rois.shape[0], s)
     ref, rarg = oracle.moi_pool_forward(x.numpy(), rois.numpy(), oh.numpy(), sp.numpy(), scale, pooled)
     res = {}
     try:
-        for bits in (1, 0):
-            _lib.set_tuning("moi_bits", bits)
+        for bits in (0, 1, 2):
+            _lib.set_tuning("moi_algo", bits)
             out, arg = ops.moi_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1], oh.to(cuda), sp.to(cuda))
             res[bits] = (out.cpu().numpy(), arg.cpu().numpy())
     finally:
-        _lib.set_tuning("moi_bits", 1)
-    for bits in (1, 0):
+        _lib.set_tuning("moi_algo", 0)
+    for bits in (0, 1, 2):
         assert np.array_equal(res[bits][0], ref)
         assert np.array_equal(res[bits][1], rarg)
