@@ -136,6 +136,10 @@ def algorithmic_bytes(cfg, esz):
     n, c, h, w_, r, p, k, kr = cfg["N"], cfg["C"], cfg["H"], cfg["W"], cfg["N"] * cfg["R"], cfg["P"], cfg["K"], cfg["Kr"]
     pool_fwd = n * c * h * w_ * esz + 20 * r + r * c * p * p * esz
     pool_bwd = r * c * p * p * esz + n * c * h * w_ * esz + 20 * r
+    if cfg.get("pooler") == "MOIPool":  # API-visible int32 argmax, oh_labels [R, S], superpixels [N, Hs, Ws]
+        extra = r * c * p * p * 4
+        pool_fwd += extra + r * cfg["S"] * 4 + n * cfg["img_h"] * cfg["img_w"] * 4
+        pool_bwd += extra
     mil = 7 * r * k * 4
     refine = kr * (r * (16 + 12 + 3 * (k + 1) * 4) + (r * (16 + 2 * 4 * k * 4) if cfg.get("reg") else 0))
     return dict(pool_fwd=pool_fwd, pool_bwd=pool_bwd, mil=mil, refine=refine,
@@ -280,7 +284,7 @@ def run_b200(a):
             "data": "synthetic (seeded MCG-like proposals, relu(randn) conv5 map, random head logits)",
             "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
                        "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
-                       "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool",
+                       "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": cfg.get("pooler", "ROIPool"),
                        "l2": "flushed (256 MiB write) between timed steps (value, roofline); e2e: see e2e.l2", "stages": step.stages(), "schedule": step.schedule(),
                        "launch": "cuda_graph_replay" if use_graph else "eager"},
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
@@ -344,7 +348,7 @@ def run_reference(a):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
                    "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
-                   "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": "ROIPool"},
+                   "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": cfg.get("pooler", "ROIPool")},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": desc},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

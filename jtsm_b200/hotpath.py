@@ -20,6 +20,9 @@ class HotPathStep:
         self.dtype = dtype
         self.P = (cfg["P"], cfg["P"])
         self.scale = cfg["scale"]
+        self.pooler = cfg.get("pooler", "ROIPool")
+        if self.pooler not in ("ROIPool", "MOIPool"):
+            raise RuntimeError("HotPathStep: pooler %r not wired into the step (ROIPool, MOIPool)" % self.pooler)
         self._d2h = 0
         # side streams of the head: one per refinement branch + one for the MIL backward (heads.head_step)
         self.side_streams = [torch.cuda.Stream(device=device) for _ in range(cfg["Kr"] + 1)] \
@@ -37,6 +40,9 @@ class HotPathStep:
             oh[i, l] = 1.0
         src = dict(feat=wl["feat"].to(self.dtype), rois=wl["rois"], objectness=wl["objectness"], mil_cls=wl["mil_cls"],
                    mil_det=wl["mil_det"], labels_onehot=oh)
+        if self.pooler == "MOIPool":
+            src["oh_labels"] = wl["oh_labels"]
+            src["superpixels"] = wl["superpixels"]
         for k, t in enumerate(wl["ref_logits"]):
             src["ref_logits%d" % k] = t
         for k, t in enumerate(wl["ref_deltas"]):
@@ -76,11 +82,13 @@ class HotPathStep:
         return self._d2h
 
     def stages(self):
-        st = ["roi_pool_fwd(x objectness)", "wsddn_fwd+bce", "wsddn_bwd"]
+        pool = "roi_pool_fwd(x objectness)" if self.pooler == "ROIPool" else \
+            "moi_pool_fwd(cell ids, row bits, visit lists, pool x mask_scale x objectness)"
+        st = [pool, "wsddn_fwd+bce", "wsddn_bwd"]
         st += ["refine_assign", "refine_ce_fwd_bwd_softmax", "apply_deltas"] * self.cfg["Kr"]
         if self.cfg["reg"]:
             st += ["refine_box_reg"] * self.cfg["Kr"]
-        return st + ["roi_pool_bwd"]
+        return st + ["roi_pool_bwd" if self.pooler == "ROIPool" else "moi_pool_bwd(x scales)"]
 
     def schedule(self):
         """How the stages are ordered on the device."""
@@ -90,7 +98,7 @@ class HotPathStep:
                 "concurrently on side streams -> pool bwd")
 
     def dominant_kernel(self):
-        return "roi_pool_fwd_rmq_kernel"
+        return "roi_pool_fwd_rmq_kernel" if self.pooler == "ROIPool" else "moi_pool_fwd_list_kernel"
 
     def ncu_traffic(self, name=None):
         """DRAM bytes per launch of the dominant kernel from the committed ncu capture of this
@@ -105,9 +113,16 @@ class HotPathStep:
 
     # ------------------------------------------------------------------ the step
     def pool_forward(self, d):
+        """-> (pooled, argmax, row scale the backward multiplies by)."""
         x = d["feat"]
+        if self.pooler == "MOIPool":  # JTSM: roi_heads_jtsm.py:607-633
+            out, arg, scales = ops.moi_pool_forward(x, d["rois"], self.scale, self.P[0], self.P[1], d["oh_labels"],
+                                                    d["superpixels"], row_scale=d["row_scale"], mask_scale=True,
+                                                    return_scales=True)
+            return out, arg, scales[2]
         adt = torch.int16 if x.shape[2] * x.shape[3] < 65535 else torch.int32
-        return ops.roi_pool_forward(x, d["rois"], self.scale, self.P, row_scale=d["row_scale"], argmax_dtype=adt)
+        out, arg = ops.roi_pool_forward(x, d["rois"], self.scale, self.P, row_scale=d["row_scale"], argmax_dtype=adt)
+        return out, arg, d["row_scale"]
 
     def capture_dominant(self, d):
         """The dominant op (RoIPool forward: two memsets, prep kernel, pooling kernel) alone in a CUDA graph, so it
@@ -131,11 +146,11 @@ class HotPathStep:
 
     def run(self, d):
         x, rois = d["feat"], d["rois"]
-        pooled, argmax = self.pool_forward(d)
+        pooled, argmax, bwd_scale = self.pool_forward(d)
         cfg = self.cfg
         h = heads.head_step(d["mil_cls"], d["mil_det"], d["ref_logits"], d["ref_deltas"], d["proposals"], self.counts,
                             self.labels, cfg["K"], d["labels_onehot"], reg=cfg["reg"], streams=self.side_streams)
-        grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=d["row_scale"])
+        grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=bwd_scale)
         self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
 
     # ------------------------------------------------------------------ CUDA graph of the step

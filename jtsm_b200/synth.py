@@ -13,7 +13,16 @@ CONFIGS = {
     "c2": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=2000, P=7, K=20, Kr=3, reg=False),
     "c3": dict(N=2, C=2048, stride=8, img_h=600, img_w=800, R=4000, P=7, K=80, Kr=4, reg=True),
     "c4": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=4000, P=7, K=20, Kr=3, reg=False),
+    # c3 with JTSM's own pooler (POOLER_TYPE "MOIPool", jtsm_WSR_50_DC5_1x.yaml:17): superpixel-masked pooling with
+    # the heads' mask_scale x (objectness + 1) epilogue (roi_heads_jtsm.py:607-633); ~1000 superpixels per image
+    "c3m": dict(N=2, C=2048, stride=8, img_h=600, img_w=800, R=4000, P=7, K=80, Kr=4, reg=True, pooler="MOIPool",
+                sp_block=22),
 }
+
+
+def config_index(name):
+    """c2 -> 2, c3m -> 3 (seed / label rules follow the base configuration)."""
+    return int("".join(ch for ch in name[1:] if ch.isdigit()))
 
 
 def seed_for(config_index, sweep_index=0):
@@ -81,7 +90,8 @@ def pool_case(name, sweep_index=0, **over):
     """Feature map + rois (+ objectness) for a named config."""
     cfg = dict(CONFIGS[name])
     cfg.update(over)
-    g = generator(seed_for(int(name[1:]), sweep_index))
+    cfg.setdefault("pooler", "ROIPool")
+    g = generator(seed_for(config_index(name), sweep_index))
     h = int(math.ceil(cfg["img_h"] / cfg["stride"]))
     w = int(math.ceil(cfg["img_w"] / cfg["stride"]))
     feat = feature_map(g, cfg["N"], cfg["C"], h, w)
@@ -98,7 +108,7 @@ def step_case(name, sweep_index=0, **over):
     logits (+ deltas when box regression is on) and the gradient that fc6's backward would
     hand to the pooling op."""
     cfg, feat, boxes, rois, obj = pool_case(name, sweep_index, **over)
-    g = generator(seed_for(int(name[1:]), sweep_index) + 7)
+    g = generator(seed_for(config_index(name), sweep_index) + 7)
     r_total, k = rois.shape[0], cfg["K"]
     labels = image_labels(g, cfg["N"], k, max_classes=3 if k <= 20 else 7)
     sigma = 5.0
@@ -109,9 +119,15 @@ def step_case(name, sweep_index=0, **over):
     n_pooled = r_total * cfg["C"] * cfg["P"] * cfg["P"]
     # one [C,P,P] gradient tile per RoI-slot mod 64 keeps host memory bounded at config 3
     tile = torch.randn(min(r_total, 64), cfg["C"], cfg["P"], cfg["P"], generator=g)
-    return dict(name=name, cfg=cfg, feat=feat, boxes=boxes, rois=rois, objectness=obj, labels=labels,
-                mil_cls=mil_cls, mil_det=mil_det, ref_logits=ref_logits, ref_deltas=ref_deltas,
-                grad_tile=tile, n_pooled=n_pooled)
+    out = dict(name=name, cfg=cfg, feat=feat, boxes=boxes, rois=rois, objectness=obj, labels=labels,
+               mil_cls=mil_cls, mil_det=mil_det, ref_logits=ref_logits, ref_deltas=ref_deltas,
+               grad_tile=tile, n_pooled=n_pooled)
+    if cfg["pooler"] == "MOIPool":
+        sp, oh, cnt, s = superpixel_case(generator(seed_for(config_index(name), sweep_index) + 13), boxes,
+                                         cfg["img_h"], cfg["img_w"], cfg.get("sp_block", 22))
+        out.update(superpixels=sp, oh_labels=oh, cnt_sp=cnt, num_superpixels=s)
+        cfg["S"] = s
+    return out
 
 
 def expand_grad_tile(tile, num_rois):
@@ -161,3 +177,35 @@ def pcl_case(g, r, k, p):
     return dict(probs=probs, labels=labels, cls_loss_weights=cls_loss_weights, gt_assignment=gt_assignment,
                 pc_labels=pc_labels, pc_probs=pc_probs, pc_count=pc_count, img_cls_loss_weights=img_cls_loss_weights,
                 im_labels=im_labels)
+
+
+def superpixel_case(g, boxes_per_image, hs, ws, block=22):
+    """Superpixels + box-consistent oh_labels: blocky label images as `superpixels` and
+    oh_labels[r, s] = 1 iff at least half of segment s lies inside box r (segments are rectangles, so the overlap is
+    analytic).  -> (superpixels int32 [N, hs, ws], oh_labels int32 [R, S], cnt_sp int64 [N, S], S)."""
+    n = len(boxes_per_image)
+    rows, cols = (hs + block - 1) // block, (ws + block - 1) // block
+    s = rows * cols
+    sps, ohs, cnts = [], [], []
+    for i in range(n):
+        perm = torch.randperm(s, generator=g).to(torch.int32).view(rows, cols)
+        jy = torch.randint(0, block // 2 + 1, (1,), generator=g).item()
+        jx = torch.randint(0, block // 2 + 1, (1,), generator=g).item()
+        yy = ((torch.arange(hs) + jy) // block).clamp(max=rows - 1)
+        xx = ((torch.arange(ws) + jx) // block).clamp(max=cols - 1)
+        sp = perm[yy][:, xx]
+        sps.append(sp)
+        ys = torch.tensor([(yy == r_).nonzero()[0, 0].item() if (yy == r_).any() else hs for r_ in range(rows)]).float()
+        ye = torch.tensor([(yy == r_).nonzero()[-1, 0].item() + 1 if (yy == r_).any() else hs for r_ in range(rows)]).float()
+        xs = torch.tensor([(xx == c_).nonzero()[0, 0].item() if (xx == c_).any() else ws for c_ in range(cols)]).float()
+        xe = torch.tensor([(xx == c_).nonzero()[-1, 0].item() + 1 if (xx == c_).any() else ws for c_ in range(cols)]).float()
+        b = boxes_per_image[i]
+        ovy = (torch.minimum(ye[None], b[:, 3:4]) - torch.maximum(ys[None], b[:, 1:2])).clamp(min=0)  # [R, rows]
+        ovx = (torch.minimum(xe[None], b[:, 2:3]) - torch.maximum(xs[None], b[:, 0:1])).clamp(min=0)  # [R, cols]
+        area = (ye - ys)[:, None] * (xe - xs)[None]  # [rows, cols]
+        inside = ovy[:, :, None] * ovx[:, None, :] >= 0.5 * area[None].clamp(min=1.0)
+        oh = torch.zeros(b.shape[0], s, dtype=torch.int32)
+        oh[:, perm.reshape(-1).long()] = inside.reshape(b.shape[0], -1).to(torch.int32)
+        ohs.append(oh)
+        cnts.append(torch.bincount(sp.reshape(-1).long(), minlength=s))
+    return torch.stack(sps).contiguous(), torch.cat(ohs).contiguous(), torch.stack(cnts), s

@@ -45,6 +45,8 @@ def time_step(wl, sample_rois, threads, kind):
     head_in = dict(mil_cls=wl["mil_cls"][:r], mil_det=wl["mil_det"][:r], ref_logits=[x[:r] for x in wl["ref_logits"]],
                    ref_deltas=[x[:r] for x in wl["ref_deltas"]], proposal_boxes=[rois[:, 1:].contiguous()],
                    labels=wl["labels"][:1], num_classes=cfg["K"], reg=cfg["reg"])
+    if cfg.get("pooler", "ROIPool") == "MOIPool":
+        return _time_step_moi(wl, cfg, rois, x, P, g, scale, head_in, threads, kind, desc)
     if kind == "reference":
         import torchvision
 
@@ -71,3 +73,36 @@ def time_step(wl, sample_rois, threads, kind):
     ref_heads.head_step(**head_in)
     t = time.perf_counter() - t0
     return t, r, desc + ", oracle C port (pool) + eager restatement (heads)"
+
+
+def _time_step_moi(wl, cfg, rois, x, P, g, scale, head_in, threads, kind, desc):
+    """MOIPool configurations (JTSM).  The reference has no CPU entry point for MOIPool (MOIPool.h:74 raises), so
+    kind="reference" runs the reference's own kernels compiled as serial host code (oracle/_ref/libref_wslpool.so,
+    oracle/Makefile.ref) when that library is present, else the C port; both fanned out over host threads by RoI
+    range.  The per-RoI mask_scale factor (a scalar multiply per RoI) is left out of the CPU legs."""
+    from . import ref_native
+
+    r = rois.shape[0]
+    xn, rn, gn = x.numpy(), rois.numpy(), (g * scale.view(-1, 1, 1, 1)).numpy()
+    oh = wl["oh_labels"][:r].numpy()
+    sp = wl["superpixels"][:1].numpy()
+    use_ref = kind == "reference" and ref_native.available()
+    fwd = ref_native.moi_pool_forward if use_ref else capi.moi_pool_forward
+    capi.lib()
+    chunks = [(i * r // threads, (i + 1) * r // threads) for i in range(threads)]
+    t0 = time.perf_counter()
+
+    def work(rng):
+        a, b = rng
+        if a == b:
+            return np.zeros(x.shape, np.float32)
+        out, arg = fwd(xn, rn[a:b], oh[a:b], sp, cfg["scale"], P)
+        return capi.max_pool_backward(gn[a:b], arg, rn[a:b], tuple(x.shape))
+
+    with ThreadPoolExecutor(threads) as ex:
+        parts = list(ex.map(work, chunks))
+    np.sum(parts, axis=0)
+    ref_heads.head_step(**head_in)
+    t = time.perf_counter() - t0
+    how = "the reference's own MOIPool kernels built as serial host code (oracle/_ref)" if use_ref else "oracle C port of MOIPool"
+    return t, r, desc + ", " + how + " + eager PyTorch heads"
