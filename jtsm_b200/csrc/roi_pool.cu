@@ -316,13 +316,17 @@ constexpr size_t kMaxPlaneSmem = 200 * 1024;
 
 // The range-max-table kernel applies when plane + tables fit in shared memory (hw <= 9685, which also
 // keeps every descriptor field inside its bits), the batch index fits 11 bits and output offsets 32 bits.
-bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
+bool rmq_geometry_ok(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
   const long long hw = (long long)height * width;
-  const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
-  return (algo == 0 || algo == 3) && !tuning("roi_pool_force_gmem", 0) && hw < 65535 &&
-         rmq_smem_bytes((int)hw) <= 227 * 1024 && (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL &&
+  return hw < 65535 && rmq_smem_bytes((int)hw) <= 227 * 1024 &&
+         (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL &&
          (long long)num_rois * PH * PW * PH * PW < 0xFFFFFFFFLL &&  // exact magic division of a bin id by PH*PW
          (long long)num_rois * 64 < 0x7FFFFFFFLL;                  // chunk bounds in 32 bits (chunks <= 64)
+}
+bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
+  const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
+  return (algo == 0 || algo == 3) && !tuning("roi_pool_force_gmem", 0) &&
+         rmq_geometry_ok(batch, channels, height, width, num_rois, PH, PW);
 }
 
 template <typename T> constexpr bool dtype_is_f32() { return false; }
@@ -340,23 +344,22 @@ int pick_splits(int planes, int num_rois, int ctas_per_sm) {
   return (int)s;
 }
 
-template <typename T, typename A>
-int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, int width,
-                        int num_rois, int PH, int PW, const PoolWorkspace& ws,
-                        const float* row_scale, void* output, void* argmax, cudaStream_t st) {
+// range-max-table kernel: plane + 10 index tables in shared memory, persistent CTAs.  kMoi: MOIPool mode (MoiAux).
+template <typename T, typename A, bool kMoi>
+int launch_rmq(const void* input, int batch, int channels, int height, int width, int num_rois, int PH, int PW,
+               const PoolWorkspace& ws, const MoiAux& moi, void* output, void* argmax, cudaStream_t st) {
   const int planes = batch * channels;
-  // 1) range-max-table kernel: plane + 10 index tables in shared memory, persistent CTAs
   const int hw = height * width;
   const size_t rmq_smem = rmq_smem_bytes(hw);
-  const int algo = tuning("roi_pool_fwd_algo", 0);
-  if (rmq_eligible(batch, channels, height, width, num_rois, PH, PW)) {
+  {
     // a second plane buffer (fp32 inputs) lets the next plane stream in behind the queries of the current one
     const int two_planes = dtype_is_f32<T>() && rmq_smem + (size_t)hw * 4 <= 227 * 1024 &&
                            tuning("roi_pool_fwd_async", 1);
     const size_t smem = rmq_smem + (two_planes ? (size_t)hw * 4 : 0);
     static bool rmq_attr = false;
     if (!rmq_attr) {
-      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A, kMoi>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           227 * 1024);
       rmq_attr = true;
     }
     const int per_sm = (int)((227 * 1024) / (smem + 1024)) >= 2 ? 2 : 1;  // 1024-thread CTAs
@@ -378,11 +381,24 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
     if (chunks > 64) chunks = 64;
     const int items = planes * chunks;
     const int grid = items < max_grid ? items : max_grid;
-    roi_pool_fwd_rmq_kernel<T, A><<<grid, kRmqThreads, smem, st>>>(
-        (const T*)input, channels, height, width, PH, PW, chunks, items, two_planes, ws, (T*)output, (A*)argmax);
+    roi_pool_fwd_rmq_kernel<T, A, kMoi><<<grid, kRmqThreads, smem, st>>>(
+        (const T*)input, channels, height, width, PH, PW, chunks, items, two_planes, ws, moi, (T*)output,
+        (A*)argmax);
     count_launch();
     return cuda_status();
   }
+}
+
+template <typename T, typename A>
+int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, int width,
+                        int num_rois, int PH, int PW, const PoolWorkspace& ws,
+                        const float* row_scale, void* output, void* argmax, cudaStream_t st) {
+  const int planes = batch * channels;
+  const int hw = height * width;
+  const int algo = tuning("roi_pool_fwd_algo", 0);
+  if (rmq_eligible(batch, channels, height, width, num_rois, PH, PW))
+    return launch_rmq<T, A, false>(input, batch, channels, height, width, num_rois, PH, PW, ws, MoiAux{}, output,
+                                   argmax, st);
   const int pitch = (width & 1) ? width : width + 1;
   const size_t smem = (size_t)height * pitch * sizeof(float);
   if (smem <= kMaxPlaneSmem && algo != 2 && !tuning("roi_pool_force_gmem", 0)) {
@@ -408,10 +424,10 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
 }
 
 int run_prep(const float* rois, int num_rois, int batch, int channels, int height, int width, float scale,
-             int PH, int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st) {
+             int PH, int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st, int force_desc = 0) {
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
   cudaMemsetAsync(ws.ungrouped, 0, 2 * sizeof(int), st);  // ungrouped flag + slow-bin counter
-  const int want_desc = rmq_eligible(batch, channels, height, width, num_rois, PH, PW);
+  const int want_desc = force_desc || rmq_eligible(batch, channels, height, width, num_rois, PH, PW);
   roi_pool_prep_kernel<<<(num_rois + kPrepRois - 1) / kPrepRois, kPrepThreads, 0, st>>>(
       rois, num_rois, batch, height, width, scale, PH, PW, row_scale, want_desc, ws);
   count_launch();
@@ -419,6 +435,25 @@ int run_prep(const float* rois, int num_rois, int batch, int channels, int heigh
 }
 
 }  // namespace
+
+// ---- entry points for MOIPool's range-max mode (wsl_pool.cu) ----
+namespace jtsm {
+bool moi_rmq_eligible(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
+  return rmq_geometry_ok(batch, channels, height, width, num_rois, PH, PW);
+}
+int moi_rmq_prep(const float* rois, int num_rois, int batch, int channels, int height, int width, float scale, int PH,
+                 int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st) {
+  return run_prep(rois, num_rois, batch, channels, height, width, scale, PH, PW, row_scale, ws, st, 1);
+}
+int moi_rmq_launch(int dtype, const void* input, int batch, int channels, int height, int width, int num_rois, int PH,
+                   int PW, const PoolWorkspace& ws, const MoiAux& moi, void* output, int* argmax, cudaStream_t st) {
+  int rc = JTSM_OK;
+  JTSM_DISPATCH_DTYPE(dtype, T, {
+    rc = launch_rmq<T, int, true>(input, batch, channels, height, width, num_rois, PH, PW, ws, moi, output, argmax, st);
+  });
+  return rc;
+}
+}  // namespace jtsm
 
 extern "C" size_t jtsm_roi_pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w) {
   if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0) return 0;

@@ -55,6 +55,25 @@ __device__ __forceinline__ RmqCand rmq_best(const RmqCand a, const RmqCand b) {
   return take_b ? b : a;
 }
 
+// MOIPool mode of the range-max kernel (wsl_pool.cu): a bin whose cells are ALL switched on in the superpixel mask is a
+// plain RoIPool bin and keeps its fast descriptor; every other bin sits in the slow list and is answered from its
+// visit list (the switched-on cells in row-major order, see moi_list_kernel).  The kernel only runs when at most
+// `gate_pct` percent of the bins are slow (decided on the device: no host sync); the visit-list kernel runs otherwise.
+struct MoiAux {
+  const uint32_t* bin_desc;  // [R * PP] by bin id: (first quad of the list in the RoI's slot) << 15 | quads
+  const uint2* lists;        // R slots of cap_quads entries of four uint16 cell indices (index hw = padding)
+  unsigned cap_quads;
+  const float* mask_scale;   // [R]  P*P / (#non-empty bins + 1); the row scale stays in ws.rscale
+  const int* slow_list;            // global ids (r * PP + bin) of the slow bins, ascending
+  const int* slow_base;            // [R + 1] first list position of RoI r (exclusive scan of the per-RoI counts)
+  const int* slow_total;           // [1] number of slow bins (the gate)
+  int total_bins;
+  int gate_pct;
+};
+__device__ __forceinline__ bool moi_rmq_gate(const int* slow_count, int total_bins, int gate_pct) {
+  return (long long)__ldg(slow_count) * 100 <= (long long)total_bins * gate_pct;
+}
+
 // One build phase: from level (k, k) in `src` (window 2^k x 2^k, s = 2^k) to the three levels (k, k+1), (k+1, k)
 // and (k+1, k+1): the four (k, k) windows at p, p + s, p + s*W, p + s*W + s give all three with 4 index loads,
 // 4 value loads and 3 comparisons.  kIdentity: level (0, 0) is the cell itself, no index loads.
@@ -107,7 +126,7 @@ __device__ __forceinline__ void plane_prefetch_async(const T*, float*, int) {}
 
 // Slow path of one bin (empty, elongated or > 16-cell ranges) from the packed [start, end) ranges:
 // nearest stored level, as many windows as needed.  Empty bin -> value 0, index 0xFFFFFFFF.
-__device__ __noinline__ RmqCand rmq_query_slow(const float* plane, const unsigned short* tabs, int hw, int W,
+static __device__ __noinline__ RmqCand rmq_query_slow(const float* plane, const unsigned short* tabs, int hw, int W,
                                                uint32_t hb, uint32_t wb) {
   const int hs = range_lo(hb), he = range_hi(hb), wst = range_lo(wb), wen = range_hi(wb);
   const int lh = he - hs, lw = wen - wst;
@@ -180,10 +199,11 @@ __device__ __forceinline__ RmqItem rmq_item(int nc, int chunk, int chunks, int c
 // are loaded one round ahead (they come from L2: little L1 is left next to 180+ KB of shared memory; deeper
 // rings of 2 and 4 rounds measured the same).  x = 0 marks a slow bin (left to the list)
 // or an inactive thread: the branch-free look-ups then run on offset 0, which is harmless.
-template <typename T, typename A, bool kUngrouped>
+template <typename T, typename A, bool kUngrouped, bool kMoi>
 __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
                                               const RmqItem& it, int PP, int cpp, unsigned w2, unsigned magic_pp,
-                                              T* __restrict__ output, A* __restrict__ argmax) {
+                                              const float* __restrict__ mask_scale, T* __restrict__ output,
+                                              A* __restrict__ argmax) {
   const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
   const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
@@ -191,26 +211,27 @@ __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned
   constexpr int K = kRmqBinsPerThread;
   unsigned i = (unsigned)(it.r0 * PP) + threadIdx.x;
   unsigned xn[K];
-  float scn[K];
+  float scn[K], msn[K];
   auto fetch = [&](unsigned i0) {
 #pragma unroll
     for (int k = 0; k < K; ++k) {
       const unsigned ik = i0 + k * kRmqThreads;
-      xn[k] = 0u, scn[k] = 0.f;
+      xn[k] = 0u, scn[k] = 0.f, msn[k] = 0.f;
       if (ik < i_end) {
         xn[k] = __ldg(ws.bdesc + ik);
         scn[k] = __ldg(ws.rscale + __umulhi(ik, magic_pp));
+        if (kMoi) msn[k] = __ldg(mask_scale + __umulhi(ik, magic_pp));
       }
     }
   };
   fetch(i);
   while (i < i_end) {
     unsigned x[K], o[K];
-    float sc[K];
+    float sc[K], ms[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) {
       const unsigned ik = i + k * kRmqThreads;
-      x[k] = xn[k], sc[k] = scn[k];
+      x[k] = xn[k], sc[k] = scn[k], ms[k] = msn[k];
       o[k] = ik + __umulhi(ik, magic_pp) * o_r + o_c;
     }
     i += K * kRmqThreads;
@@ -224,7 +245,8 @@ __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned
       bool act = (int)x[k] < 0;  // x >= 0: slow bin (left to the list) or past the end
       if (kUngrouped && act) act = __ldg(ws.batch_idx + (o[k] - o_c) / (unsigned)cpp) == it.n;
       if (act) {
-        output[o[k]] = Elem<T>::from_f(__fmul_rn(best[k].v, sc[k]));
+        const float v = kMoi ? __fmul_rn(best[k].v, ms[k]) : best[k].v;  // (f * mask_scale) * (objectness + 1)
+        output[o[k]] = Elem<T>::from_f(__fmul_rn(v, sc[k]));
         argmax[o[k]] = (A)best[k].i;  // a fast bin always has a cell
       }
     }
@@ -234,33 +256,66 @@ __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned
 // The few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%) of RoIs [r_lo, r_hi) for the plane
 // whose tables are resident.  The prep kernel lists them, so no warp of the main loop diverges into the long
 // path; the list is short and every CTA filters it for the RoI range it has just served.
-template <typename T, typename A>
+template <typename T, typename A, bool kMoi>
 __device__ __forceinline__ void rmq_slow_pass(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
                                               int n, int c, int r_lo, int r_hi, bool ungrouped, int channels, int hw,
-                                              int W, int PH, int PW, T* __restrict__ output, A* __restrict__ argmax) {
+                                              int W, int PH, int PW, const MoiAux& moi, T* __restrict__ output,
+                                              A* __restrict__ argmax) {
   const int PP = PH * PW;
+  if (kMoi) {
+    // MOIPool: the slow bins are listed in ascending (RoI, bin) order, so every lane has work and neighbouring lanes
+    // write neighbouring outputs of the same 4 * PP byte run.  Each is answered from its visit list (switched-on cells in
+    // row-major order, strict >: value and first arg-max of the reference).
+    const int lo = __ldg(moi.slow_base + r_lo), hi = __ldg(moi.slow_base + r_hi);
+    for (int i = lo + (int)threadIdx.x; i < hi; i += kRmqThreads) {
+      const int id = __ldg(moi.slow_list + i);
+      const int rr = id / PP, b = id - rr * PP;
+      if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+      const uint32_t d = __ldg(moi.bin_desc + (size_t)rr * PP + b);
+      const uint2* lp = moi.lists + (size_t)rr * moi.cap_quads + (d >> 15);
+      const int nq = (int)(d & 32767u);
+      float m = -FLT_MAX;
+      int mi = -1;
+      for (int q = 0; q < nq; ++q) {
+        const uint2 e = __ldg(lp + q);
+        const int ix[4] = {(int)(e.x & 0xffff), (int)(e.x >> 16), (int)(e.y & 0xffff), (int)(e.y >> 16)};
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          if (ix[t] < hw) {  // hw = padding entry
+            const float v = plane[ix[t]];
+            if (v > m) { m = v; mi = ix[t]; }
+          }
+      }
+      const float v = mi == -1 ? 0.f : m;
+      const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
+      output[so] = Elem<T>::from_f(__fmul_rn(__fmul_rn(v, __ldg(moi.mask_scale + rr)), __ldg(ws.rscale + rr)));
+      argmax[so] = Arg<A>::enc(mi);
+    }
+    return;
+  }
   const int ns = __ldg(ws.slow_count);
   for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
     const int id = __ldg(ws.slow_list + j);
     const int rr = id / PP, b = id - rr * PP;
     if (rr < r_lo || rr >= r_hi) continue;
     if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+    const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
     const int ph = b / PW, pw = b - ph * PW;
     const RmqCand best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)rr * PH + ph),
                                         __ldg(ws.wbins + (size_t)rr * PW + pw));
-    const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
     output[so] = Elem<T>::from_f(__fmul_rn(best.v, __ldg(ws.rscale + rr)));
     argmax[so] = Arg<A>::enc((int)best.i);
   }
 }
 
 // dynamic smem: plane A (hw fp32) | 10 tables (hw uint16 each) | plane B (hw fp32, only when two_planes)
-template <typename T, typename A>
+template <typename T, typename A, bool kMoi = false>
 __global__ void __launch_bounds__(kRmqThreads, 1)
 roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW,
-                        int chunks, int num_items, int two_planes, PoolWorkspace ws, T* __restrict__ output,
-                        A* __restrict__ argmax) {
+                        int chunks, int num_items, int two_planes, PoolWorkspace ws, MoiAux moi,
+                        T* __restrict__ output, A* __restrict__ argmax) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  if (kMoi && !moi_rmq_gate(moi.slow_total, moi.total_bins, moi.gate_pct)) return;  // uniform: the list kernel runs
   const int hw = H * W;
   float* plane = (float*)smem_raw;
   unsigned short* tabs = (unsigned short*)(plane + hw);
@@ -306,8 +361,8 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
     const RmqItem it = rmq_item(nc, chunk, chunks, channels, ws);
     if (nc != cur_plane) {
       if (cur_plane >= 0)
-        rmq_slow_pass<T, A>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
-                            channels, hw, W, PH, PW, output, argmax);
+        rmq_slow_pass<T, A, kMoi>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
+                                  channels, hw, W, PH, PW, moi, output, argmax);
       if (async && in_flight == nc) {
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();  // everyone is done with the old plane and tables; the fetched plane is complete
@@ -339,13 +394,13 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
     }
     if (it.nr > 0) r_hi = it.r0 + it.nr;  // chunks of a plane are consecutive RoI ranges
     if (ungrouped)
-      rmq_main_loop<T, A, true>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, output, argmax);
+      rmq_main_loop<T, A, true, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, output, argmax);
     else
-      rmq_main_loop<T, A, false>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, output, argmax);
+      rmq_main_loop<T, A, false, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, output, argmax);
   }
   if (cur_plane >= 0)
-    rmq_slow_pass<T, A>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped, channels,
-                        hw, W, PH, PW, output, argmax);
+    rmq_slow_pass<T, A, kMoi>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
+                              channels, hw, W, PH, PW, moi, output, argmax);
   asm volatile("cp.async.wait_all;" ::: "memory");
 }
 

@@ -117,13 +117,50 @@ def test_moi_pool_list_bits_and_byte_paths_equal_oracle(cuda, oracle, n, c, h, w
     oh = synth.oh_labels(g, rois.shape[0], s)
     ref, rarg = oracle.moi_pool_forward(x.numpy(), rois.numpy(), oh.numpy(), sp.numpy(), scale, pooled)
     res = {}
+    modes = {"gated": (0, 50), "rmq": (0, 100), "lists": (0, -1), "bits": (1, -1), "bytes": (2, -1)}
     try:
-        for bits in (0, 1, 2):
-            _lib.set_tuning("moi_algo", bits)
+        for name, (algo, rmq) in modes.items():
+            _lib.set_tuning("moi_algo", algo)
+            _lib.set_tuning("moi_rmq", rmq)
             out, arg = ops.moi_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1], oh.to(cuda), sp.to(cuda))
-            res[bits] = (out.cpu().numpy(), arg.cpu().numpy())
+            res[name] = (out.cpu().numpy(), arg.cpu().numpy())
     finally:
         _lib.set_tuning("moi_algo", 0)
-    for bits in (0, 1, 2):
-        assert np.array_equal(res[bits][0], ref)
-        assert np.array_equal(res[bits][1], rarg)
+        _lib.set_tuning("moi_rmq", -1)
+    for name in modes:
+        assert np.array_equal(res[name][0], ref), name
+        assert np.array_equal(res[name][1], rarg), name
+
+
+def test_moi_pool_range_max_mode_dense_masks_and_scales(cuda, oracle):
+    """Box-consistent superpixels (most bins fully switched on -> range-max fast path) with the fused JTSM scales,
+    two images with interleaved batch indices; forced range-max, forced lists and auto agree with the oracle bit for bit."""
+    from jtsm_b200 import _lib, ops
+
+    g = synth.generator(311)
+    n, c, h, w = 2, 6, 75, 100
+    x = synth.feature_map(g, n, c, h, w)
+    boxes = [synth.proposals(g, 200, 600, 800) for _ in range(n)]
+    rois = synth.rois_from_boxes(boxes)
+    sp, oh, _, s = synth.superpixel_case(g, boxes, 600, 800, 22)
+    perm = torch.randperm(rois.shape[0], generator=g)
+    rois, oh = rois[perm].contiguous(), oh[perm].contiguous()
+    obj = torch.rand(rois.shape[0], generator=g)
+    ref, rarg = oracle.moi_pool_forward(x.numpy(), rois.numpy(), oh.numpy(), sp.numpy(), 1 / 8.0, (7, 7))
+    valid = (rarg[:, 0].reshape(rarg.shape[0], -1) != -1).sum(1).astype(np.float32)
+    ms = np.float32(49) * (np.float32(1.0) / (valid + np.float32(1.0)))
+    want = (ref * ms[:, None, None, None]) * (obj.numpy() + np.float32(1.0))[:, None, None, None]
+    full = (rarg != -1).mean()
+    assert full > 0.5
+    try:
+        for rmq in (100, -1, 50):
+            _lib.set_tuning("moi_rmq", rmq)
+            out, arg, scales = ops.moi_pool_forward(x.to(cuda), rois.to(cuda), 1 / 8.0, 7, 7, oh.to(cuda), sp.to(cuda),
+                                                    row_scale=(obj + 1.0).to(cuda), mask_scale=True, return_scales=True)
+            assert np.array_equal(arg.cpu().numpy(), rarg), rmq
+            assert np.array_equal(out.cpu().numpy(), want), rmq
+            assert np.array_equal(scales[0].cpu().numpy(), ms)
+            plain, parg = ops.moi_pool_forward(x.to(cuda), rois.to(cuda), 1 / 8.0, 7, 7, oh.to(cuda), sp.to(cuda))
+            assert np.array_equal(plain.cpu().numpy(), ref) and np.array_equal(parg.cpu().numpy(), rarg)
+    finally:
+        _lib.set_tuning("moi_rmq", -1)

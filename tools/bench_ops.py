@@ -91,6 +91,11 @@ def main():
         sp_d, oh_d = sp.to(dev), oh.to(dev)
         med, _ = timeit(lambda: ops.moi_pool_forward(x, rois_d, cfg["scale"], ph, pw, oh_d, sp_d), a.iters, flush)
         res["moi_pool_fwd_us"] = med
+        gen = torch.Generator().manual_seed(6)
+        sp2, oh2, _, _ = synth.superpixel_case(gen, boxes, cfg["img_h"], cfg["img_w"], 22)
+        sp2_d, oh2_d = sp2.to(dev), oh2.to(dev)
+        med, _ = timeit(lambda: ops.moi_pool_forward(x, rois_d, cfg["scale"], ph, pw, oh2_d, sp2_d), a.iters, flush)
+        res["moi_pool_fwd_box_consistent_masks_us"] = med
     if a.ops in ("all", "tta"):
         res.update(bench_tta(dev, a.iters, flush))
     print(json.dumps(res))
