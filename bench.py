@@ -224,6 +224,7 @@ def run_b200(a):
     # with an explicit 256 MiB flush before every step is timed as well and reported next to it.
     e2e_flush_ms = None
     h2d_gbps = None
+    io_graph_ms = None
     if use_graph:
         step.prepare_stream(host)
         # the link alone: the step's pinned arena copied 10 times back to back
@@ -238,6 +239,14 @@ def run_b200(a):
         h2d_gbps = 10 * step.h2d_bytes(host) / (c0.elapsed_time(c1) * 1e-3) / 1e9
         step.run_stream([host] * 3)
         barrier()
+        # the streamed step's graph alone (derive inputs + step + result packing), inputs resident, back to back
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(a.steps):
+            step.slots[0]["graph"].replay()
+        g1.record()
+        barrier()
+        io_graph_ms = g0.elapsed_time(g1) / a.steps
         seen = []
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -293,7 +302,7 @@ def run_b200(a):
                     "l2": "fresh H2D inputs every step; two alternating buffer sets, > 500 MB streamed per step "
                           "(126 MB L2) before a buffer is reused; no explicit flush" if use_graph else
                           "flushed (256 MiB write) before every step",
-                    "h2d_link_gbps": h2d_gbps,
+                    "h2d_link_gbps": h2d_gbps, "step_graph_ms_inputs_resident_l2_warm": io_graph_ms,
                     "value_with_l2_flush": (world * R * a.steps / (e2e_flush_ms * 1e-3)) if e2e_flush_ms else None},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": step.dominant_kernel(), "achieved": ach, "peak": peak, "unit": "GB/s",

@@ -186,6 +186,8 @@ class HotPathStep:
             self.run(d)
             self.launches_per_step = _lib.launch_count() - before
             self.graph_results = self.results() if with_io else None
+            # all host-bound results in ONE byte buffer: one D2H copy per step instead of one per tensor
+            self.graph_packed = self._pack(self.graph_results) if with_io else None
         self.static_inputs = d
         self.graph_last = self.last  # the graph's static output buffers
         return self.graph
@@ -203,6 +205,23 @@ class HotPathStep:
         for b in h["branches"]:
             res += [b["gt_classes"], b["counters"], b["acc"]]
         return res
+
+    def _pack(self, res):
+        self._res_layout, off = [], 0
+        for t in res:
+            nbytes = t.numel() * t.element_size()
+            self._res_layout.append((off, nbytes, t.dtype, tuple(t.shape)))
+            off += (nbytes + 15) & ~15
+        parts = []
+        for t, (o, nbytes, _, _) in zip(res, self._res_layout):
+            parts.append(t.contiguous().reshape(-1).view(torch.uint8))
+            pad = ((nbytes + 15) & ~15) - nbytes
+            if pad:
+                parts.append(torch.empty(pad, dtype=torch.uint8, device=t.device))  # alignment only
+        return torch.cat(parts)
+
+    def _unpack(self, buf):
+        return [buf[o:o + n].view(dt).view(shape) for o, n, dt, shape in self._res_layout]
 
     def replay_from_host(self, host):
         """H2D of the step's inputs into the graph's static buffers, replay, blocking D2H of the results."""
@@ -223,12 +242,13 @@ class HotPathStep:
             d = self.upload(host)
             torch.cuda.synchronize()
             graph = self.capture(d, with_io=True)
-            res = self.graph_results
-            self.slots.append(dict(graph=graph, inputs=d, last=self.graph_last, res=res,
-                                   out=[torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in res],
+            res = self.graph_packed
+            out_buf = torch.empty(res.shape, dtype=torch.uint8).pin_memory()
+            self.slots.append(dict(graph=graph, inputs=d, last=self.graph_last, res=res, out_buf=out_buf,
+                                   out=self._unpack(out_buf),
                                    ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event()))
         self.copy_stream, self.d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
-        self._d2h = sum(t.numel() * t.element_size() for t in self.slots[0]["out"])
+        self._d2h = self.slots[0]["out_buf"].numel()
 
     def run_stream(self, host_batches, consume=None, before_step=None):
         """Run one step per element of `host_batches` (dicts of pinned host tensors as from pin_host_inputs).
@@ -254,8 +274,7 @@ class HotPathStep:
             sl["ev_done"].record(comp)
             with torch.cuda.stream(self.d2h_stream):
                 self.d2h_stream.wait_event(sl["ev_done"])
-                for dst, src in zip(sl["out"], sl["res"]):
-                    dst.copy_(src, non_blocking=True)
+                sl["out_buf"].copy_(sl["res"], non_blocking=True)  # one copy: every host-bound result of the step
                 sl["ev_out"].record(self.d2h_stream)
             if i >= 1:
                 prev = self.slots[(i - 1) % 2]
