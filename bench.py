@@ -261,7 +261,7 @@ def run_b200(a):
         f1.record()
         barrier()
         e2e_flush_ms = f0.elapsed_time(f1)
-        e2e_mode = "pipelined: H2D(i+1) | step(i) | D2H(i-1) on three streams, two buffer sets"
+        e2e_mode = "pipelined: H2D(i+1) | step(i) | D2H(i-1) on three streams, %d buffer sets" % len(step.slots)
     else:
         for _ in range(3):
             step.run_from_host(host)
@@ -299,7 +299,7 @@ def run_b200(a):
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes(),
                     "mode": e2e_mode,
-                    "l2": "fresh H2D inputs every step; two alternating buffer sets, > 500 MB streamed per step "
+                    "l2": "fresh H2D inputs every step; alternating buffer sets, > 500 MB streamed per step "
                           "(126 MB L2) before a buffer is reused; no explicit flush" if use_graph else
                           "flushed (256 MiB write) before every step",
                     "h2d_link_gbps": h2d_gbps, "step_graph_ms_inputs_resident_l2_warm": io_graph_ms,

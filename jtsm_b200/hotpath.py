@@ -38,8 +38,21 @@ class HotPathStep:
         oh = torch.zeros(len(self.counts), cfg["K"])
         for i, l in enumerate(self.labels):
             oh[i, l] = 1.0
+        # image-level class lists (gt_classes_img_int) as device data: offsets [N+1] + ids padded to N * cap, so a
+        # captured step serves batches with different labels (the pseudo-gt seeds follow the uploaded lists)
+        n_img = len(self.counts)
+        self.cls_cap = min(cfg["K"], int(cfg.get("max_img_classes", 16)))
+        offs, ids = [0], []
+        for l in self.labels:
+            l = [int(v) for v in (l.tolist() if torch.is_tensor(l) else l)]
+            if len(l) > self.cls_cap:
+                raise RuntimeError("HotPathStep: %d image-level classes > max_img_classes=%d" % (len(l), self.cls_cap))
+            ids.extend(l)
+            offs.append(len(ids))
+        ids += [0] * (n_img * self.cls_cap - len(ids))
         src = dict(feat=wl["feat"].to(self.dtype), rois=wl["rois"], objectness=wl["objectness"], mil_cls=wl["mil_cls"],
-                   mil_det=wl["mil_det"], labels_onehot=oh)
+                   mil_det=wl["mil_det"], labels_onehot=oh, cls_off=torch.tensor(offs, dtype=torch.int32),
+                   cls_ids=torch.tensor(ids, dtype=torch.int64))
         if self.pooler == "MOIPool":
             src["oh_labels"] = wl["oh_labels"]
             src["superpixels"] = wl["superpixels"]
@@ -149,7 +162,8 @@ class HotPathStep:
         pooled, argmax, bwd_scale = self.pool_forward(d)
         cfg = self.cfg
         h = heads.head_step(d["mil_cls"], d["mil_det"], d["ref_logits"], d["ref_deltas"], d["proposals"], self.counts,
-                            self.labels, cfg["K"], d["labels_onehot"], reg=cfg["reg"], streams=self.side_streams)
+                            (d["cls_off"], d["cls_ids"], self.cls_cap, len(self.counts) * self.cls_cap), cfg["K"],
+                            d["labels_onehot"], reg=cfg["reg"], streams=self.side_streams)
         grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=bwd_scale)
         self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
 
@@ -234,11 +248,14 @@ class HotPathStep:
         return out
 
     # ------------------------------------------------------------------ pipelined stream of steps from host memory
-    def prepare_stream(self, host):
-        """Two captured copies of the step (two sets of static device buffers) + pinned result buffers, so that
-        step i + 1's inputs upload and step i - 1's results download while step i computes."""
+    def prepare_stream(self, host, depth=None):
+        """`depth` captured copies of the step (sets of static device buffers) + pinned result buffers, so that
+        step i + 1's inputs upload and step i - 1's results download while step i computes; the host runs
+        depth - 1 steps ahead of the results it consumes.  depth: JTSM_STREAM_DEPTH or 2 (3 and 4 measured the same:
+        the streamed rate is bound on the device, not by the host running ahead)."""
+        depth = int(depth or os.environ.get("JTSM_STREAM_DEPTH", "2"))
         self.slots = []
-        for _ in range(2):
+        for _ in range(max(2, depth)):
             d = self.upload(host)
             torch.cuda.synchronize()
             graph = self.capture(d, with_io=True)
@@ -258,15 +275,17 @@ class HotPathStep:
         comp = torch.cuda.current_stream()
         self.copy_stream.wait_stream(comp)
         n = 0
+        ns = len(self.slots)
+        lag = ns - 1
         for i, host in enumerate(host_batches):
-            sl = self.slots[i % 2]
+            sl = self.slots[i % ns]
             with torch.cuda.stream(self.copy_stream):
-                if i >= 2:
+                if i >= ns:
                     self.copy_stream.wait_event(sl["ev_done"])  # the slot's previous step no longer reads its inputs
                 sl["inputs"]["__arena"].copy_(host["__arena"], non_blocking=True)  # one copy: all inputs of the step
                 sl["ev_in"].record(self.copy_stream)
             comp.wait_event(sl["ev_in"])
-            if i >= 2:
+            if i >= ns:
                 comp.wait_event(sl["ev_out"])  # the slot's previous results have left the device
             if before_step is not None:
                 before_step()
@@ -276,18 +295,19 @@ class HotPathStep:
                 self.d2h_stream.wait_event(sl["ev_done"])
                 sl["out_buf"].copy_(sl["res"], non_blocking=True)  # one copy: every host-bound result of the step
                 sl["ev_out"].record(self.d2h_stream)
-            if i >= 1:
-                prev = self.slots[(i - 1) % 2]
+            if i >= lag:
+                prev = self.slots[(i - lag) % ns]
                 prev["ev_out"].synchronize()
                 if consume is not None:
-                    consume(i - 1, prev["out"])
+                    consume(i - lag, prev["out"])
             n = i + 1
-        if n:
-            lastslot = self.slots[(n - 1) % 2]
-            lastslot["ev_out"].synchronize()
+        for j in range(max(0, n - lag), n):  # drain: the last results, in order
+            sl = self.slots[j % ns]
+            sl["ev_out"].synchronize()
             if consume is not None:
-                consume(n - 1, lastslot["out"])
-            comp.wait_event(lastslot["ev_out"])  # so that an event recorded on `comp` now covers the last D2H
+                consume(j, sl["out"])
+        if n:
+            comp.wait_event(self.slots[(n - 1) % ns]["ev_out"])  # an event recorded on `comp` now covers the last D2H
         return n
 
     def run_from_host(self, host):

@@ -191,7 +191,12 @@ _CLS_CACHE = {}
 
 
 def image_class_lists(gt_classes_img_int, device):
-    """(offsets int32 [N+1], ids int64 [total], max per image) on `device` for ragged per-image class lists."""
+    """(offsets int32 [N+1], ids int64 [total], max per image, total) on `device` for ragged per-image class lists.
+    A ready (offsets, ids, max per image, capacity) tuple of DEVICE tensors passes through: the lists then live in
+    device memory that the caller refreshes per step (CUDA-graph streaming, hotpath.HotPathStep) and `capacity`
+    only bounds the pseudo-gt output rows."""
+    if isinstance(gt_classes_img_int, tuple) and len(gt_classes_img_int) == 4 and torch.is_tensor(gt_classes_img_int[0]):
+        return gt_classes_img_int
     key = (tuple(tuple(int(v) for v in (c.tolist() if torch.is_tensor(c) else c)) for c in gt_classes_img_int), str(device))
     hit = _CLS_CACHE.get(key)
     if hit is None:
