@@ -121,6 +121,22 @@ JTSM_API int jtsm_roi_align_backward(const void* grad_output, long long stride_n
                                      int pooled_h, int pooled_w, int sampling_ratio, int aligned,
                                      void* grad_input, void* workspace, size_t workspace_bytes,
                                      void* stream);
+/* Deterministic backward (opt-in): a segmented reduction instead of atomics -- channel-independent tap list, stable
+ * radix sort by map cell, one fixed-order sum per (channel, cell).  Run-to-run bit-identical and bit-equal to the
+ * reference's serial CPU backward (ROIAlign_cpu.cpp:168-263: same operands (g * w / count), same order).
+ * sampling_ratio > 0 only (JTSM_ERR_UNSUPPORTED otherwise: the adaptive grid has no a-priori tap count).
+ * grad_input is fully overwritten. */
+JTSM_API size_t jtsm_roi_align_backward_det_workspace_bytes(int batch, int channels, int height,
+                                                            int width, int num_rois, int pooled_h,
+                                                            int pooled_w, int sampling_ratio);
+JTSM_API int jtsm_roi_align_backward_det(const void* grad_output, long long stride_n,
+                                         long long stride_c, long long stride_h,
+                                         long long stride_w, const float* rois, int dtype,
+                                         int batch, int channels, int height, int width,
+                                         int num_rois, float spatial_scale, int pooled_h,
+                                         int pooled_w, int sampling_ratio, int aligned,
+                                         void* grad_input, void* workspace,
+                                         size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------
  * ROILoopPool: three RoIPool-style max-pools per RoI -- the RoI, the "frame" (RoI minus the inner

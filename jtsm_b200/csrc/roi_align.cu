@@ -11,6 +11,8 @@
 // precomputed once per call (channel independent).  Arithmetic follows the reference's operation
 // order with explicit round-to-nearest intrinsics (no FMA contraction), so the forward is bit-exact
 // against the CPU oracle; the backward uses RED.ADD.F32 (sum order differs -> tolerance).
+#include <cub/cub.cuh>
+
 #include "common.cuh"
 
 namespace jtsm {
@@ -574,6 +576,125 @@ int launch_align_fwd(const void* input, int batch, int channels, int H, int W, i
 }
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------------------------
+// Deterministic backward: a segmented reduction instead of atomics (north_star; fixed sampling_ratio).
+// The tap pattern of RoIAlign is channel independent, so it is resolved once per call:
+//   1. `align_det_taps_kernel`: every (RoI, bin, sample, corner) tap -> key = image * H*W + cell, payload = (output
+//      element r * PP + bin, bilinear weight); tap id = ((((r * PH + ph) * PW + pw) * gh + iy) * gw + ix) * 4 + corner;
+//   2. a STABLE radix sort by key (CUB): the taps of a cell end up contiguous and in tap-id order -- exactly the order
+//      in which the reference's serial CPU backward (ROIAlign_cpu.cpp:168-263: for n, c, ph, pw, iy, ix; add w1..w4)
+//      adds to that cell;  `align_det_bounds_kernel`: first tap of every cell by binary search;
+//   3. `align_det_transpose_kernel`: grad_output (any strides, any dtype) -> fp32 [R * PP][C], channel last;
+//   4. `align_det_reduce_kernel`: a warp per cell, lanes along channels: acc += (g * w) / count tap by tap in list
+//      order (coalesced 128-byte reads of the transposed gradient), then a shared-memory transpose so the map is
+//      written with lanes along cells.  No atomics, every element of grad_input written exactly once (no memset),
+//      run-to-run bit-identical, and bit-EQUAL to the reference's CPU backward (same operands, same order).
+// Cost: the sort and the 4-byte-per-channel tap walk make it ~2-3x slower than the RED kernels; it is an opt-in.
+struct AlignDetTap {
+  unsigned out;  // r * PP + bin
+  float w;
+};
+
+__global__ void __launch_bounds__(256)
+align_det_taps_kernel(int num_rois, int H, int W, int PH, int PW, int S, AlignWorkspace ws, unsigned sentinel,
+                      unsigned* __restrict__ keys, unsigned long long* __restrict__ vals, float* __restrict__ counts) {
+  const int PP = PH * PW, per_roi = PP * S * S;
+  const long long total = (long long)num_rois * per_roi;
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= total) return;
+  const int r = (int)(i / per_roi);
+  int rem = (int)(i - (long long)r * per_roi);
+  const int bin = rem / (S * S);
+  rem -= bin * S * S;
+  const int iy = rem / S, ix = rem - iy * S;
+  const int ph = bin / PW, pw = bin - ph * PW;
+  const AlignGeom g = ws.geom[r];
+  if (rem == 0 && bin == 0) counts[r] = (float)(g.grid_h * g.grid_w);
+  Taps t;
+  bool ok = g.batch >= 0;
+  if (ok) {
+    const float y = sample_coord(g.start_h, ph, g.bin_h, iy, g.grid_h);
+    const float x = sample_coord(g.start_w, pw, g.bin_w, ix, g.grid_w);
+    ok = bilinear_taps(H, W, y, x, t);
+  }
+  const unsigned base = ok ? (unsigned)g.batch * (unsigned)(H * W) : 0u;
+  const unsigned out = (unsigned)r * (unsigned)PP + (unsigned)bin;
+  const int pos[4] = {t.p1, t.p2, t.p3, t.p4};
+  const float wt[4] = {t.w1, t.w2, t.w3, t.w4};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    keys[i * 4 + k] = ok ? base + (unsigned)pos[k] : sentinel;  // samples outside the map contribute nothing
+    vals[i * 4 + k] = ((unsigned long long)out << 32) | (unsigned long long)__float_as_uint(ok ? wt[k] : 0.f);
+  }
+}
+
+// first[k] = index of the first sorted tap with key >= k, for k in [0, cells]
+__global__ void align_det_bounds_kernel(const unsigned* __restrict__ keys, long long num_taps, int cells,
+                                        int* __restrict__ first) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k > cells) return;
+  long long lo = 0, hi = num_taps;
+  while (lo < hi) {
+    const long long mid = (lo + hi) >> 1;
+    if (keys[mid] < (unsigned)k) lo = mid + 1; else hi = mid;
+  }
+  first[k] = (int)lo;
+}
+
+// gT[(r * PP + bin) * C + c] = float(grad_output[r, c, ph, pw]); 32 x 32 tiles through shared memory
+template <typename T>
+__global__ void __launch_bounds__(1024)
+align_det_transpose_kernel(const T* __restrict__ g, long long sn, long long sc, long long sh, long long sw, int C,
+                           int PH, int PW, float* __restrict__ gT) {
+  __shared__ float tile[32][33];
+  const int PP = PH * PW;
+  const int r = blockIdx.z;
+  const int c0 = blockIdx.y * 32, b0 = blockIdx.x * 32;
+  {
+    const int c = c0 + threadIdx.y, bin = b0 + threadIdx.x;
+    if (c < C && bin < PP) {
+      const int ph = bin / PW, pw = bin - ph * PW;
+      tile[threadIdx.y][threadIdx.x] = Elem<T>::to_f(g[r * sn + c * sc + ph * sh + pw * sw]);
+    }
+  }
+  __syncthreads();
+  const int bin = b0 + threadIdx.y, c = c0 + threadIdx.x;
+  if (c < C && bin < PP) gT[((size_t)r * PP + bin) * C + c] = tile[threadIdx.x][threadIdx.y];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(1024)
+align_det_reduce_kernel(const unsigned long long* __restrict__ vals, const int* __restrict__ first,
+                        const float* __restrict__ counts, const float* __restrict__ gT, int C, int hw, int cells, int PP,
+                        T* __restrict__ grad_input) {
+  __shared__ float tile[32][33];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cell = blockIdx.x * 32 + warp;  // global cell id = image * hw + cell in image
+  const int c = blockIdx.y * 32 + lane;
+  const unsigned magic_pp = (unsigned)((0x100000000ull + PP - 1) / PP);
+  float acc = 0.f;
+  if (cell < cells) {
+    const int t0 = first[cell], t1 = first[cell + 1];
+    const bool live = c < C;
+    for (int t = t0; t < t1; ++t) {
+      const unsigned long long v = __ldg(vals + t);  // same address in every lane
+      const unsigned out = (unsigned)(v >> 32);
+      const float w = __uint_as_float((unsigned)v);
+      const float cnt = __ldg(counts + __umulhi(out, magic_pp));
+      const float gv = live ? __ldg(gT + (size_t)out * C + c) : 0.f;
+      acc = __fadd_rn(acc, __fdiv_rn(__fmul_rn(gv, w), cnt));  // grad * w / count, ROIAlign_cpu.cpp:238-247
+    }
+  }
+  tile[warp][lane] = acc;
+  __syncthreads();
+  // transposed write: lanes along cells
+  const int oc = blockIdx.y * 32 + warp, ocell = blockIdx.x * 32 + lane;
+  if (oc < C && ocell < cells) {
+    const int n = ocell / hw, p = ocell - n * hw;
+    grad_input[((size_t)n * C + oc) * hw + p] = Elem<T>::from_f(tile[lane][warp]);
+  }
+}
+
 extern "C" size_t jtsm_roi_align_workspace_bytes(int dtype, int batch, int channels, int height, int width,
                                                  int num_rois, int backward) {
   if (batch < 0 || num_rois < 0) return 0;
@@ -671,5 +792,95 @@ extern "C" int jtsm_roi_align_backward(const void* grad_output, long long stride
     align_convert_from_f32_kernel<__half><<<kNumSMs * 8, 256, 0, st>>>(acc, (__half*)grad_input, n_in);
     count_launch();
   }
+  return cuda_status();
+}
+
+// ---- deterministic backward: launcher ----
+namespace {
+struct DetLayout {
+  size_t taps, keys, vals, first, counts, gt, cub, total;
+};
+DetLayout det_layout(int batch, int channels, int height, int width, int num_rois, int PH, int PW, int S) {
+  DetLayout L;
+  L.taps = (size_t)num_rois * PH * PW * S * S * 4;
+  L.keys = align_up(L.taps * sizeof(unsigned), 256);
+  L.vals = align_up(L.taps * sizeof(unsigned long long), 256);
+  L.first = align_up(((size_t)batch * height * width + 1) * sizeof(int), 256);
+  L.counts = align_up((size_t)num_rois * sizeof(float), 256);
+  L.gt = align_up((size_t)num_rois * PH * PW * channels * sizeof(float), 256);
+  size_t tmp = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const unsigned*)nullptr, (unsigned*)nullptr,
+                                  (const unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                  (long long)(L.taps ? L.taps : 1));
+  L.cub = align_up(tmp, 256);
+  L.total = align_workspace_bytes(batch, num_rois) + 2 * L.keys + 2 * L.vals + L.first + L.counts + L.gt + L.cub + 512;
+  return L;
+}
+}  // namespace
+
+extern "C" size_t jtsm_roi_align_backward_det_workspace_bytes(int batch, int channels, int height, int width,
+                                                              int num_rois, int pooled_h, int pooled_w,
+                                                              int sampling_ratio) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 ||
+      sampling_ratio <= 0)
+    return 0;
+  return det_layout(batch, channels, height, width, num_rois, pooled_h, pooled_w, sampling_ratio).total;
+}
+
+extern "C" int jtsm_roi_align_backward_det(const void* grad_output, long long stride_n, long long stride_c,
+                                           long long stride_h, long long stride_w, const float* rois, int dtype,
+                                           int batch, int channels, int height, int width, int num_rois,
+                                           float spatial_scale, int pooled_h, int pooled_w, int sampling_ratio,
+                                           int aligned, void* grad_input, void* workspace, size_t workspace_bytes,
+                                           void* stream) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (sampling_ratio <= 0) return JTSM_ERR_UNSUPPORTED;  // the adaptive grid has no a-priori tap count
+  const size_t n_in = (size_t)batch * channels * height * width;
+  if (n_in == 0) return JTSM_OK;
+  if (!grad_input || !workspace) return JTSM_ERR_INVALID_ARGUMENT;
+  const long long cells_ll = (long long)batch * height * width;
+  const DetLayout L = det_layout(batch, channels, height, width, num_rois, pooled_h, pooled_w, sampling_ratio);
+  if (cells_ll >= 0x7FFFFFFFLL || L.taps >= 0x7FFFFFFFULL || (long long)num_rois * pooled_h * pooled_w >= 0x7FFFFFFFLL)
+    return JTSM_ERR_UNSUPPORTED;
+  if (workspace_bytes < L.total) return JTSM_ERR_WORKSPACE_TOO_SMALL;
+  if (num_rois > 0 && channels > 0 && (!grad_output || !rois)) return JTSM_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int cells = (int)cells_ll, hw = height * width, PP = pooled_h * pooled_w;
+  AlignWorkspace ws = carve_align_workspace(workspace, batch, num_rois);
+  char* p = (char*)(((uintptr_t)workspace + align_workspace_bytes(batch, num_rois) + 255) & ~(uintptr_t)255);
+  unsigned* keys_a = (unsigned*)p; p += L.keys;
+  unsigned* keys_b = (unsigned*)p; p += L.keys;
+  unsigned long long* vals_a = (unsigned long long*)p; p += L.vals;
+  unsigned long long* vals_b = (unsigned long long*)p; p += L.vals;
+  int* first = (int*)p; p += L.first;
+  float* counts = (float*)p; p += L.counts;
+  float* gT = (float*)p; p += L.gt;
+  void* cub_tmp = p;
+  int rc = JTSM_OK;
+  if (num_rois > 0) {
+    rc = align_prep(rois, num_rois, batch, spatial_scale, pooled_h, pooled_w, sampling_ratio, aligned, ws, st);
+    if (rc != JTSM_OK) return rc;
+    const long long samples = (long long)num_rois * PP * sampling_ratio * sampling_ratio;
+    align_det_taps_kernel<<<(unsigned)((samples + 255) / 256), 256, 0, st>>>(
+        num_rois, height, width, pooled_h, pooled_w, sampling_ratio, ws, (unsigned)cells, keys_a, vals_a, counts);
+    int end_bit = 1;
+    while (end_bit < 32 && (1ull << end_bit) <= (unsigned long long)cells) ++end_bit;  // keys <= cells (sentinel)
+    size_t tmp = L.cub;
+    cub::DeviceRadixSort::SortPairs(cub_tmp, tmp, keys_a, keys_b, vals_a, vals_b, (long long)L.taps, 0, end_bit, st);
+    dim3 tg((PP + 31) / 32, (channels + 31) / 32, num_rois);
+    JTSM_DISPATCH_DTYPE(dtype, T, {
+      align_det_transpose_kernel<T><<<tg, dim3(32, 32), 0, st>>>((const T*)grad_output, stride_n, stride_c, stride_h,
+                                                                 stride_w, channels, pooled_h, pooled_w, gT);
+    });
+    count_launch(3);
+  }
+  align_det_bounds_kernel<<<(cells + 1 + 255) / 256, 256, 0, st>>>(keys_b, (long long)L.taps, cells, first);
+  dim3 rg((cells + 31) / 32, (channels + 31) / 32);
+  JTSM_DISPATCH_DTYPE(dtype, T, {
+    align_det_reduce_kernel<T><<<rg, 1024, 0, st>>>(vals_b, first, counts, gT, channels, hw, cells, PP,
+                                                     (T*)grad_input);
+  });
+  count_launch(2);
   return cuda_status();
 }

@@ -441,8 +441,11 @@ def roi_align_forward(input, rois, spatial_scale, pooled_height, pooled_width, s
 
 
 def roi_align_backward(grad, rois, spatial_scale, pooled_height, pooled_width, batch_size, channels, height, width,
-                       sampling_ratio, aligned):
-    """Same signature as detectron2._C.roi_align_backward (ROIAlign.h:86-97)."""
+                       sampling_ratio, aligned, deterministic=None):
+    """Same signature as detectron2._C.roi_align_backward (ROIAlign.h:86-97).
+    deterministic: True = the segmented-reduction backward (no atomics; run-to-run bit-identical and bit-equal to
+    the reference's serial CPU backward; sampling_ratio > 0 only); None = follow
+    torch.are_deterministic_algorithms_enabled() where it applies; False = the RED kernels."""
     _require_cuda(grad, rois)
     n, c, h, w = int(batch_size), int(channels), int(height), int(width)
     r = rois.size(0)
@@ -452,6 +455,20 @@ def roi_align_backward(grad, rois, spatial_scale, pooled_height, pooled_width, b
         return grad_input
     L = lib()
     dt = _dtype_code(grad)
+    if deterministic and int(sampling_ratio) <= 0:
+        raise RuntimeError("jtsm_b200.roi_align_backward: the deterministic backward needs sampling_ratio > 0")
+    if deterministic is None:
+        deterministic = torch.are_deterministic_algorithms_enabled() and int(sampling_ratio) > 0
+    if deterministic:
+        ph, pw, sr = int(pooled_height), int(pooled_width), int(sampling_ratio)
+        wsb = L.jtsm_roi_align_backward_det_workspace_bytes(n, c, h, w, r, ph, pw, sr)
+        ws = _workspace(wsb, grad.device)
+        sn, sc, sh, sw = grad.stride() if grad.numel() else (0, 0, 0, 0)
+        with torch.cuda.device(grad.device):
+            check(L.jtsm_roi_align_backward_det(_ptr(grad), sn, sc, sh, sw, _ptr(rois), dt, n, c, h, w, r,
+                                                float(spatial_scale), ph, pw, sr, int(bool(aligned)), _ptr(grad_input),
+                                                _ptr(ws), wsb, _stream()), "roi_align_backward_det")
+        return grad_input
     wsb = L.jtsm_roi_align_workspace_bytes(dt, n, c, h, w, r, 1)
     ws = _workspace(wsb, grad.device)
     sn, sc, sh, sw = grad.stride() if grad.numel() else (0, 0, 0, 0)

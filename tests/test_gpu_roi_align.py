@@ -82,3 +82,63 @@ def test_roi_align_module_autograd_noncontiguous_and_bf16(cuda, oracle):
     outb = ROIAlign((7, 7), 1 / 16.0, 0, aligned=True)(xb.to(cuda), rois.to(cuda))
     assert outb.dtype == torch.bfloat16
     np.testing.assert_allclose(outb.float().cpu().numpy(), ref, rtol=1e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize("n,c,h,w,r,scale,pooled,sr,aligned", [
+    (2, 6, 38, 50, 200, 1 / 16.0, (7, 7), 2, True), (1, 37, 75, 100, 150, 1 / 8.0, (7, 7), 2, False),
+    (1, 4, 19, 25, 60, 1 / 32.0, (14, 14), 1, True), (2, 3, 38, 50, 90, 1 / 16.0, (3, 5), 3, True)])
+def test_roi_align_deterministic_backward_bit_equal_to_reference_cpu_order(cuda, oracle, n, c, h, w, r, scale, pooled,
+                                                                           sr, aligned):
+    """The segmented-reduction backward adds the taps of a cell in the order of the reference's serial CPU backward
+    (ROIAlign_cpu.cpp:168-263) with the same operands -> BIT-equal to it (the oracle C restatement is itself bit-equal
+    to the reference's ROIAlign_cpu.cpp built in place, tests/test_ref_native.py), and bit-identical run to run."""
+    from jtsm_b200 import ops
+
+    g = synth.generator(900 + r)
+    x = synth.feature_map(g, n, c, h, w)
+    boxes = [synth.proposals(g, r // n, 600, 800) for _ in range(n)]
+    rois = synth.rois_from_boxes(boxes)
+    rois = rois[torch.randperm(rois.shape[0], generator=g)].contiguous()  # un-grouped batch indices
+    rois[3, 1:] = torch.tensor([-300.0, -200.0, -250.0, -150.0])  # outside the map
+    go = torch.randn(rois.shape[0], c, *pooled, generator=g)
+    want = oracle.roi_align_backward(go.numpy(), rois.numpy(), scale, tuple(x.shape), sr, aligned)
+    a = ops.roi_align_backward(go.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1], n, c, h, w, sr, aligned,
+                               deterministic=True)
+    b = ops.roi_align_backward(go.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1], n, c, h, w, sr, aligned,
+                               deterministic=True)
+    assert torch.equal(a, b)
+    assert np.array_equal(a.cpu().numpy(), want)
+    # non-contiguous upstream gradient (explicit strides, ROIAlign_cpu.cpp:478-482)
+    gnc = go.to(cuda).permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)
+    assert not gnc.is_contiguous()
+    assert torch.equal(ops.roi_align_backward(gnc, rois.to(cuda), scale, pooled[0], pooled[1], n, c, h, w, sr, aligned,
+                                              deterministic=True), a)
+    # the RED kernels agree within the atomic-sum tolerance
+    red = ops.roi_align_backward(go.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1], n, c, h, w, sr, aligned,
+                                 deterministic=False)
+    np.testing.assert_allclose(red.cpu().numpy(), want, rtol=1e-5, atol=1e-5 * float(np.abs(want).max()))
+
+
+def test_roi_align_deterministic_backward_follows_torch_flag_and_rejects_adaptive_grid(cuda):
+    from jtsm_b200 import ops
+    from jtsm_b200.layers import ROIAlign
+
+    g = synth.generator(77)
+    x = synth.feature_map(g, 1, 8, 38, 50).to(cuda).requires_grad_()
+    rois = synth.rois_from_boxes([synth.proposals(g, 64, 600, 800)]).to(cuda)
+    go = torch.randn(64, 8, 7, 7, generator=g).to(cuda)
+    with pytest.raises(RuntimeError, match="sampling_ratio"):
+        ops.roi_align_backward(go, rois, 1 / 16.0, 7, 7, 1, 8, 38, 50, 0, True, deterministic=True)
+    prev = torch.are_deterministic_algorithms_enabled()
+    try:
+        torch.use_deterministic_algorithms(True)
+        outs = []
+        for _ in range(2):
+            x.grad = None
+            ROIAlign((7, 7), 1 / 16.0, 2, True)(x, rois).backward(go)
+            outs.append(x.grad.clone())
+        assert torch.equal(outs[0], outs[1])
+    finally:
+        torch.use_deterministic_algorithms(prev)
+    want = ops.roi_align_backward(go, rois, 1 / 16.0, 7, 7, 1, 8, 38, 50, 2, True, deterministic=True)
+    assert torch.equal(outs[0], want)

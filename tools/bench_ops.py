@@ -75,6 +75,10 @@ def main():
             res["roi_align_fwd_sr%d_us" % sr] = med
             med, _ = timeit(lambda: ops.roi_align_backward(g, rois_d, cfg["scale"], ph, pw, n, c, h, w, sr, True), a.iters, flush)
             res["roi_align_bwd_sr%d_us" % sr] = med
+            if sr > 0:
+                med, _ = timeit(lambda: ops.roi_align_backward(g, rois_d, cfg["scale"], ph, pw, n, c, h, w, sr, True,
+                                                               deterministic=True), a.iters, flush)
+                res["roi_align_bwd_deterministic_sr%d_us" % sr] = med
             if a.tv:
                 import torchvision
                 med, _ = timeit(lambda: torchvision.ops.roi_align(x, rois_d, P, cfg["scale"], sr, True), a.iters, flush)
