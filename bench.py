@@ -159,6 +159,7 @@ def run_b200(a):
         raise RuntimeError("bench.py (impl=b200) needs a CUDA device; there is no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_bound = bind_to_gpu_numa_node(local) if world > 1 else False
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()  # fail loudly if libjtsm_b200.so is missing
@@ -302,7 +303,7 @@ def run_b200(a):
                     "l2": "fresh H2D inputs every step; alternating buffer sets, > 500 MB streamed per step "
                           "(126 MB L2) before a buffer is reused; no explicit flush" if use_graph else
                           "flushed (256 MiB write) before every step",
-                    "h2d_link_gbps": h2d_gbps, "step_graph_ms_inputs_resident_l2_warm": io_graph_ms,
+                    "h2d_link_gbps": h2d_gbps, "cpu_affinity_gpu_local": numa_bound, "step_graph_ms_inputs_resident_l2_warm": io_graph_ms,
                     "value_with_l2_flush": (world * R * a.steps / (e2e_flush_ms * 1e-3)) if e2e_flush_ms else None},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": step.dominant_kernel(), "achieved": ach, "peak": peak, "unit": "GB/s",
@@ -315,7 +316,7 @@ def run_b200(a):
         }
         if not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(wl, a, kind="port")
-        print(json.dumps(out), flush=True)
+        emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 
@@ -362,11 +363,37 @@ def run_reference(a):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out), flush=True)
+    emit(json.dumps(out))
+
+
+_JSON_OUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything libraries print meanwhile (e.g. NCCL's version banner,
+    which lands on fd 1) was redirected to stderr by main()."""
+    os.write(_JSON_OUT, (line + "\n").encode())
+
+
+def bind_to_gpu_numa_node(local):
+    """Run this rank (and allocate its pinned host buffers) on the CPUs next to its GPU: with 8 ranks streaming
+    16 MB per step each, pinned memory on the far socket costs the H2D copies their bandwidth."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+        return True
+    except Exception:
+        return False
 
 
 def main():
+    global _JSON_OUT
     a = parse()
+    sys.stdout.flush()
+    _JSON_OUT = os.dup(1)
+    os.dup2(2, 1)  # stray prints of libraries -> stderr
     if a.impl == "reference":
         run_reference(a)
     else:
