@@ -109,16 +109,35 @@ def bench_tta(dev, iters, flush):
     """c4: R = 4000, K = 20, 10 augmentations: device merge vs the reference's composition on the same GPU
     (per augmentation D2H -> numpy apply_box -> H2D, then torch.cat + torch.mean; test_time_augmentation_avg.py:364-390)."""
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import numpy as np
+
+    from jtsm_b200 import ops as _ops
     from jtsm_b200 import tta
-    from oracle import ref_tta  # timed beside it as the reference's own composition, not part of the product path
 
     g = synth.generator(synth.seed_for(4))
     hw = (600, 800)
     sizes = (480, 576, 688, 864, 1200)
-    tf_o = ref_tta.tta_transforms(hw, hw, sizes, 4000, True)
     tf = tta.tta_transforms(hw, hw, sizes, 4000, True)
-    pb = synth.proposals(g, 4000, *hw)
-    boxes, scores = ref_tta.synth_augmented_outputs(g, pb, tf_o, 20)
+    pb = synth.proposals(g, 4000, *hw).to(dev)
+    boxes, scores = [], []
+    for t in tf:  # per-augmentation outputs: the proposals mapped into the augmented image, per-class jitter
+        fwd = t.apply_box(pb)
+        pc = fwd[:, None, :].repeat(1, 20, 1) + (torch.rand(4000, 20, 4, generator=g).to(dev) - 0.5) * 2.0
+        lo, hi = torch.minimum(pc[..., :2], pc[..., 2:]), torch.maximum(pc[..., :2], pc[..., 2:]) + 1.0
+        boxes.append(torch.cat([lo, hi], -1).reshape(1, 4000, 80).contiguous())
+        scores.append(torch.softmax(torch.randn(4000, 21, generator=g).to(dev) * 3, 1).reshape(1, 4000, 21))
+
+    def host_apply_box(stages, b):
+        """What the reference does per augmentation on the host (fvcore apply_box per stage, numpy float32)."""
+        for ty, fa, fb in stages:
+            x0, y0, x1, y1 = b[:, 0].copy(), b[:, 1].copy(), b[:, 2].copy(), b[:, 3].copy()
+            if ty == _ops.TTA_HFLIP:
+                x0, x1 = np.float32(fa) - x0, np.float32(fa) - x1
+            elif ty == _ops.TTA_SCALE:
+                x0, x1, y0, y1 = x0 * np.float32(fa), x1 * np.float32(fa), y0 * np.float32(fb), y1 * np.float32(fb)
+            b = np.stack([np.minimum(x0, x1), np.minimum(y0, y1), np.maximum(x0, x1), np.maximum(y0, y1)], 1)
+        return b
+
     bd, sd = [b.to(dev) for b in boxes], [s.to(dev) for s in scores]
     out = {}
     med, _ = timeit(lambda: tta.get_augmented_boxes(bd, sd, tf), iters, flush)
@@ -133,9 +152,9 @@ def bench_tta(dev, iters, flush):
 
     def ref_path():
         ab = list(bd)
-        for i, t in enumerate(tf_o):
+        for i, t in enumerate(tf):
             pbx = ab[i]
-            o = t.inverse().apply_box(pbx.reshape(-1, 4).cpu().numpy())
+            o = host_apply_box(t.inverse().stages(), pbx.reshape(-1, 4).cpu().numpy())
             ab[i] = torch.from_numpy(o).to(dev).reshape(pbx.shape)
         return torch.mean(torch.cat(ab, 0), 0), torch.mean(torch.cat(sd, 0), 0)
 
