@@ -23,7 +23,7 @@ std::map<std::string, int>& tuning_map() {
       {"roi_align_bwd_algo", 0},   // 0 = auto (separable: column kernel for PH <= 16, else cell kernel), 1 = one RED per tap, 2 = cell kernel
       {"roi_align_fwd_algo", 0},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
       {"roi_align_force_gmem", 0},
-      {"moi_rmq", -1},             // MOIPool range-max mode: run it when <= this % of the bins are partially masked; -1 = off (default: measured 680 vs 727 us on box-consistent masks, +20 us on sparse ones, profiles/r1u)
+      {"moi_rmq", 60},             // MOIPool: fully switched-on bins go to the RoIPool range-max kernel when <= this % of the bins are partially masked (device-side gate); -1 = off
       {"moi_planes", 2},           // channels per CTA of the MOIPool visit-list kernel (1 or 2)
       {"moi_algo", 0},             // MOIPool forward: 0 = auto (per-bin visit lists), 1 = row bit masks, 2 = byte-mask scan
   };

@@ -56,17 +56,13 @@ __device__ __forceinline__ RmqCand rmq_best(const RmqCand a, const RmqCand b) {
 }
 
 // MOIPool mode of the range-max kernel (wsl_pool.cu): a bin whose cells are ALL switched on in the superpixel mask is a
-// plain RoIPool bin and keeps its fast descriptor; every other bin sits in the slow list and is answered from its
-// visit list (the switched-on cells in row-major order, see moi_list_kernel).  The kernel only runs when at most
-// `gate_pct` percent of the bins are slow (decided on the device: no host sync); the visit-list kernel runs otherwise.
+// plain RoIPool bin and keeps its fast descriptor; this kernel answers exactly those (main loop only, no slow pass)
+// and the visit-list kernel (moi_pool_fwd_list_kernel, two planes per CTA) answers the rest.  It only runs when at
+// most `gate_pct` percent of the bins are left to the lists (decided on the device, no host sync; the list kernel
+// makes the same test and then answers every bin itself).
 struct MoiAux {
-  const uint32_t* bin_desc;  // [R * PP] by bin id: (first quad of the list in the RoI's slot) << 15 | quads
-  const uint2* lists;        // R slots of cap_quads entries of four uint16 cell indices (index hw = padding)
-  unsigned cap_quads;
-  const float* mask_scale;   // [R]  P*P / (#non-empty bins + 1); the row scale stays in ws.rscale
-  const int* slow_list;            // global ids (r * PP + bin) of the slow bins, ascending
-  const int* slow_base;            // [R + 1] first list position of RoI r (exclusive scan of the per-RoI counts)
-  const int* slow_total;           // [1] number of slow bins (the gate)
+  const float* mask_scale;  // [R]  P*P / (#non-empty bins + 1); the row scale stays in ws.rscale
+  const int* slow_total;    // [1] number of bins left to the visit lists (the gate)
   int total_bins;
   int gate_pct;
 };
@@ -262,37 +258,7 @@ __device__ __forceinline__ void rmq_slow_pass(const float* plane, const unsigned
                                               int W, int PH, int PW, const MoiAux& moi, T* __restrict__ output,
                                               A* __restrict__ argmax) {
   const int PP = PH * PW;
-  if (kMoi) {
-    // MOIPool: the slow bins are listed in ascending (RoI, bin) order, so every lane has work and neighbouring lanes
-    // write neighbouring outputs of the same 4 * PP byte run.  Each is answered from its visit list (switched-on cells in
-    // row-major order, strict >: value and first arg-max of the reference).
-    const int lo = __ldg(moi.slow_base + r_lo), hi = __ldg(moi.slow_base + r_hi);
-    for (int i = lo + (int)threadIdx.x; i < hi; i += kRmqThreads) {
-      const int id = __ldg(moi.slow_list + i);
-      const int rr = id / PP, b = id - rr * PP;
-      if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
-      const uint32_t d = __ldg(moi.bin_desc + (size_t)rr * PP + b);
-      const uint2* lp = moi.lists + (size_t)rr * moi.cap_quads + (d >> 15);
-      const int nq = (int)(d & 32767u);
-      float m = -FLT_MAX;
-      int mi = -1;
-      for (int q = 0; q < nq; ++q) {
-        const uint2 e = __ldg(lp + q);
-        const int ix[4] = {(int)(e.x & 0xffff), (int)(e.x >> 16), (int)(e.y & 0xffff), (int)(e.y >> 16)};
-#pragma unroll
-        for (int t = 0; t < 4; ++t)
-          if (ix[t] < hw) {  // hw = padding entry
-            const float v = plane[ix[t]];
-            if (v > m) { m = v; mi = ix[t]; }
-          }
-      }
-      const float v = mi == -1 ? 0.f : m;
-      const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
-      output[so] = Elem<T>::from_f(__fmul_rn(__fmul_rn(v, __ldg(moi.mask_scale + rr)), __ldg(ws.rscale + rr)));
-      argmax[so] = Arg<A>::enc(mi);
-    }
-    return;
-  }
+  if (kMoi) return;  // the visit-list kernel answers every bin without a fast descriptor
   const int ns = __ldg(ws.slow_count);
   for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
     const int id = __ldg(ws.slow_list + j);

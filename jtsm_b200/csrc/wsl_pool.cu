@@ -463,10 +463,9 @@ moi_list_kernel(int H, int W, int PH, int PW, PoolWorkspace ws, const uint4* __r
                 unsigned int cap_quads, uint32_t* __restrict__ desc, unsigned short* __restrict__ perm,
                 uint2* __restrict__ lists, const float* __restrict__ row_scale, int use_mask_scale, int num_rois,
                 float* __restrict__ scales /* [3R] or NULL: as moi_scale_kernel */,
-                uint32_t* __restrict__ desc_by_bin /* [R * PP] or NULL: range-max mode (ws.bdesc / slow list valid) */,
+                int range_max_mode /* ws.bdesc holds RoIPool descriptors: decide which bins keep them */,
                 float* __restrict__ ms_out /* [R] or NULL: mask scale (1 when off) for the range-max kernel */,
-                unsigned short* __restrict__ slow_ids /* [R * PP] */, int* __restrict__ slow_n /* [R] */,
-                int* __restrict__ slow_total /* [1] */) {
+                int* __restrict__ slow_total /* [1]: bins left to the visit lists (the gate) */) {
   __shared__ uint32_t s_quads[64 * 64 + 1];
   __shared__ unsigned char s_slow[64 * 64];
   const int r = blockIdx.x;
@@ -482,19 +481,32 @@ moi_list_kernel(int H, int W, int PH, int PW, PoolWorkspace ws, const uint4* __r
       for (int c0 = range_lo(wb); c0 < range_hi(wb); c0 += 32) cnt += __popc(moi_row_bits(q, c0, range_hi(wb)));
     }
     s_quads[bin] = (uint32_t)(cnt + 3) >> 2;
+    // range-max mode: a bin keeps its fast RoIPool descriptor only if every one of its cells is switched on; then the
+    // range-max kernel answers it and the visit-list kernel skips it
+    bool fast = false;
+    if (range_max_mode) {
+      const size_t id = (size_t)r * PP + bin;
+      const int cells = (range_hi(hb) - range_lo(hb)) * (range_hi(wb) - range_lo(wb));
+      fast = cnt > 0 && cnt == cells && (int)ws.bdesc[id] < 0;
+      if (!fast) ws.bdesc[id] = 0u;  // the range-max main loop skips it
+    }
+    s_slow[bin] = !fast;
   }
   __syncthreads();
   // 2. exclusive scan (PP <= 4096; serial by one thread is ~50 adds at 7 x 7)
   if (threadIdx.x == 0) {
     uint32_t run = 0;
     int valid = 0;  // bins with at least one switched-on cell
+    int slow = 0;
     for (int bin = 0; bin < PP; ++bin) {
       const uint32_t n = s_quads[bin];
       s_quads[bin] = run;
       run += n;
       valid += n != 0;
+      slow += s_slow[bin];
     }
     s_quads[PP] = run;
+    if (range_max_mode) atomicAdd(slow_total, slow);
     if (ms_out) ms_out[r] = use_mask_scale ? __fmul_rn((float)PP, __frcp_rn((float)valid + 1.f)) : 1.f;
     if (scales) {  // roi_heads_jtsm.py:615-633, same arithmetic as moi_scale_kernel
       const float ms = use_mask_scale ? __fmul_rn((float)PP, __frcp_rn((float)valid + 1.f)) : 1.f;
@@ -515,15 +527,17 @@ moi_list_kernel(int H, int W, int PH, int PW, PoolWorkspace ws, const uint4* __r
     const uint32_t hb = ws.hbins[(size_t)r * PH + ph], wb = ws.wbins[(size_t)r * PW + pw];
     const uint32_t start = s_quads[bin];
     const uint32_t nq = s_quads[bin + 1] - start;
+    // sort key: list length, the bins the range-max kernel answers last (key 0)
+    const uint32_t key = s_slow[bin] ? nq + 1 : 0u;
     int pos = bin;
     if (PP <= kMoiSortMaxBins) {
       pos = 0;
       for (int o = 0; o < PP; ++o) {
-        const uint32_t no = s_quads[o + 1] - s_quads[o];
-        pos += (no > nq) || (no == nq && o < bin);
+        const uint32_t ko = s_slow[o] ? s_quads[o + 1] - s_quads[o] + 1 : 0u;
+        pos += (ko > key) || (ko == key && o < bin);
       }
     }
-    desc[(size_t)r * PP + pos] = (start << 15) | nq;
+    desc[(size_t)r * PP + pos] = (s_slow[bin] ? 0u : 0x80000000u) | (start << 15) | nq;  // bit 31: range-max bin
     perm[(size_t)r * PP + pos] = (unsigned short)bin;
     unsigned short* dst = (unsigned short*)(slot + start);
     int k = 0;
@@ -538,78 +552,8 @@ moi_list_kernel(int H, int W, int PH, int PW, PoolWorkspace ws, const uint4* __r
         }
       }
     }
-    const int cells_on = k;
     for (; k < (int)(nq * 4); ++k) dst[k] = (unsigned short)hw;
-    if (desc_by_bin) {
-      // range-max mode: a bin keeps its fast descriptor only if every one of its cells is switched on (then it is a
-      // plain RoIPool bin); all others are answered from their visit list in the slow pass
-      const size_t id = (size_t)r * PP + bin;
-      desc_by_bin[id] = (start << 15) | nq;
-      const int cells = (range_hi(hb) - range_lo(hb)) * (range_hi(wb) - range_lo(wb));
-      const bool full = cells_on > 0 && cells_on == cells;
-      const bool fast = full && (int)ws.bdesc[id] < 0;
-      if (!fast) ws.bdesc[id] = 0u;  // the main loop skips it
-      s_slow[bin] = !fast;
-    }
   }
-  if (desc_by_bin) {  // the RoI's slow bins, ascending
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      int cnt = 0;
-      for (int bin = 0; bin < PP; ++bin)
-        if (s_slow[bin]) slow_ids[(size_t)r * PP + cnt++] = (unsigned short)bin;
-      slow_n[r] = cnt;
-      atomicAdd(slow_total, cnt);
-    }
-  }
-}
-
-// Range-max mode: global, ascending list of the slow bins from the per-RoI compacted ids.
-__global__ void __launch_bounds__(1024) moi_slow_scan_kernel(const int* __restrict__ slow_n, int num_rois,
-                                                             int* __restrict__ slow_base /* [R + 1] */) {
-  __shared__ int s_warp[32];
-  __shared__ int s_run;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) s_run = 0;
-  __syncthreads();
-  for (int base = 0; base < num_rois; base += 1024) {
-    const int r = base + threadIdx.x;
-    const int v = r < num_rois ? slow_n[r] : 0;
-    int x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) s_warp[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-      int w = s_warp[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int y = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += y;
-      }
-      s_warp[lane] = w;
-    }
-    __syncthreads();
-    const int run = s_run;
-    const int incl = x + (warp ? s_warp[warp - 1] : 0);
-    if (r < num_rois) slow_base[r] = run + incl - v;
-    __syncthreads();
-    if (threadIdx.x == 1023) s_run = run + incl;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) slow_base[num_rois] = s_run;
-}
-
-__global__ void __launch_bounds__(64) moi_slow_gather_kernel(const unsigned short* __restrict__ slow_ids,
-                                                             const int* __restrict__ slow_n,
-                                                             const int* __restrict__ slow_base, int PP,
-                                                             int* __restrict__ slow_list) {
-  const int r = blockIdx.x;
-  const int n = slow_n[r], base = slow_base[r];
-  for (int k = threadIdx.x; k < n; k += 64) slow_list[base + k] = r * PP + slow_ids[(size_t)r * PP + k];
 }
 
 // NPL planes (channels of one image) per CTA: a list quad is loaded and unpacked once for NPL channels.
@@ -624,8 +568,9 @@ moi_pool_fwd_list_kernel(const T* __restrict__ input, int channels, int H, int W
                          const int* __restrict__ gate_count, int gate_total, int gate_pct,
                          T* __restrict__ output, int* __restrict__ argmax) {
   extern __shared__ float plane_s[];
-  // range-max mode available: this kernel only runs when too many bins are partially masked for it (device decision)
-  if (gate_count && moi_rmq_gate(gate_count, gate_total, gate_pct)) return;
+  // range-max mode (device decision, same test in roi_pool_fwd_rmq_kernel): the fully switched-on bins (descriptor bit
+  // 31) are answered there and skipped here; otherwise this kernel answers every bin
+  const bool skip_fast = gate_count && moi_rmq_gate(gate_count, gate_total, gate_pct);
   const int item = blockIdx.x;
   const int s = item % splits;
   const int grp = item / splits;                 // group of NPL consecutive channels of one image
@@ -655,8 +600,9 @@ moi_pool_fwd_list_kernel(const T* __restrict__ input, int channels, int H, int W
     const int r = r0 + rl;
     if (ws.batch_idx[r] != n) continue;
     const uint32_t d = __ldg(desc + (size_t)r * PP + k);
+    if (skip_fast && (int)d < 0) continue;
     const int bin = __ldg(perm + (size_t)r * PP + k);
-    const uint2* lp = lists + (size_t)r * cap_quads + (d >> 15);
+    const uint2* lp = lists + (size_t)r * cap_quads + ((d >> 15) & 0xFFFFu);
     const int nq = (int)(d & 32767u);
     float m[NPL];
     int mi[NPL];
@@ -826,10 +772,7 @@ extern "C" size_t jtsm_moi_pool_workspace_bytes(int batch, int height, int width
          align_up((size_t)num_rois * moi_cap_quads(height, width, pooled_h, pooled_w) * sizeof(uint2), 256) +
          align_up((size_t)batch * height * width * kMoiCellIds * sizeof(int), 256) +  // superpixel ids per cell
          align_up((size_t)batch * height * width, 256) +
-         align_up((size_t)num_rois * pooled_h * pooled_w * sizeof(uint32_t), 256) +  // list descriptors by bin id
-         align_up((size_t)num_rois * sizeof(float), 256) +                          // mask scales (range-max mode)
-         align_up((size_t)num_rois * pooled_h * pooled_w * sizeof(unsigned short), 256) +  // slow bins per RoI
-         2 * align_up((size_t)(num_rois + 1) * sizeof(int), 256) + 256;             // their counts + scan, the total
+         align_up((size_t)num_rois * sizeof(float), 256) + 256;  // mask scales + counter (range-max mode)
 }
 
 extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const int* oh_labels, int len_labels,
@@ -861,10 +804,10 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
   const bool use_bits = use_smem && width <= 128 && algo != 2;
   const size_t cap_quads = moi_cap_quads(height, width, pooled_h, pooled_w);
   const bool use_list = use_bits && cap_quads != 0 && algo == 0 && smem + sizeof(float) <= 200 * 1024;
-  // range-max mode (roi_pool_rmq.cuh): fully switched-on bins are plain RoIPool bins; the device decides per call
-  // between it and the visit-list kernel by the share of partially masked bins.
-  // moi_rmq: -1 = off, 0..100 = run the range-max kernel when at most that many percent of the bins are slow
-  const int gate_pct = tuning("moi_rmq", -1);
+  // range-max mode (roi_pool_rmq.cuh): fully switched-on bins are plain RoIPool bins and go to the range-max kernel,
+  // the visit-list kernel answers the rest; decided per call on the device by the share of partially masked bins.
+  // moi_rmq: -1 = off, 0..100 = use the range-max kernel when at most that many percent of the bins are left to the lists
+  const int gate_pct = tuning("moi_rmq", 60);
   const bool use_rmq = use_list && gate_pct >= 0 &&
                        moi_rmq_eligible(batch, channels, height, width, num_rois, pooled_h, pooled_w);
   if (use_rmq) {
@@ -885,12 +828,8 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
   uint2* lists = (uint2*)((unsigned char*)perm + align_up(npp * sizeof(unsigned short), 256));
   int* cell_ids = (int*)((unsigned char*)lists + align_up((size_t)num_rois * cap_quads * sizeof(uint2), 256));
   unsigned char* cell_cnt = (unsigned char*)cell_ids + align_up((size_t)batch * hw * kMoiCellIds * sizeof(int), 256);
-  uint32_t* desc_by_bin = (uint32_t*)(cell_cnt + align_up((size_t)batch * hw, 256));
-  float* ms_buf = (float*)((unsigned char*)desc_by_bin + align_up(npp * sizeof(uint32_t), 256));
-  unsigned short* slow_ids = (unsigned short*)((unsigned char*)ms_buf + align_up((size_t)num_rois * sizeof(float), 256));
-  int* slow_n = (int*)((unsigned char*)slow_ids + align_up(npp * sizeof(unsigned short), 256));
-  int* slow_base = (int*)((unsigned char*)slow_n + align_up((size_t)(num_rois + 1) * sizeof(int), 256));
-  int* slow_total = (int*)((unsigned char*)slow_base + align_up((size_t)(num_rois + 1) * sizeof(int), 256));
+  float* ms_buf = (float*)(cell_cnt + align_up((size_t)batch * hw, 256));
+  int* slow_total = (int*)((unsigned char*)ms_buf + align_up((size_t)num_rois * sizeof(float), 256));
   if ((row_scale || mask_scale) && !scale_out) return JTSM_ERR_INVALID_ARGUMENT;  // [3 * num_rois]
   const float* scales = (row_scale || mask_scale) ? scale_out : nullptr;
   if (use_list) {
@@ -905,20 +844,11 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
     moi_list_kernel<<<num_rois, kMoiListThreads, 0, st>>>(height, width, pooled_h, pooled_w, ws, rowbits,
                                                           (unsigned int)cap_quads, desc, perm, lists, row_scale,
                                                           mask_scale, num_rois, scales ? scale_out : nullptr,
-                                                          use_rmq ? desc_by_bin : nullptr, use_rmq ? ms_buf : nullptr,
-                                                          slow_ids, slow_n, slow_total);
+                                                          use_rmq ? 1 : 0, use_rmq ? ms_buf : nullptr, slow_total);
     count_launch(use_rmq ? 3 : 4);  // (moi_rmq_prep counts its own launch)
     if (use_rmq) {
       MoiAux aux;
-      aux.bin_desc = desc_by_bin;
-      aux.lists = lists;
-      aux.cap_quads = (unsigned int)cap_quads;
       aux.mask_scale = ms_buf;
-      moi_slow_scan_kernel<<<1, 1024, 0, st>>>(slow_n, num_rois, slow_base);
-      moi_slow_gather_kernel<<<num_rois, 64, 0, st>>>(slow_ids, slow_n, slow_base, pooled_h * pooled_w, ws.slow_list);
-      count_launch(2);
-      aux.slow_list = ws.slow_list;
-      aux.slow_base = slow_base;
       aux.slow_total = slow_total;
       aux.total_bins = (int)npp;
       aux.gate_pct = gate_pct;

@@ -126,7 +126,7 @@ def test_moi_pool_list_bits_and_byte_paths_equal_oracle(cuda, oracle, n, c, h, w
             res[name] = (out.cpu().numpy(), arg.cpu().numpy())
     finally:
         _lib.set_tuning("moi_algo", 0)
-        _lib.set_tuning("moi_rmq", -1)
+        _lib.set_tuning("moi_rmq", 60)
     for name in modes:
         assert np.array_equal(res[name][0], ref), name
         assert np.array_equal(res[name][1], rarg), name
@@ -153,7 +153,7 @@ def test_moi_pool_range_max_mode_dense_masks_and_scales(cuda, oracle):
     full = (rarg != -1).mean()
     assert full > 0.5
     try:
-        for rmq in (100, -1, 50):
+        for rmq in (100, -1, 60):
             _lib.set_tuning("moi_rmq", rmq)
             out, arg, scales = ops.moi_pool_forward(x.to(cuda), rois.to(cuda), 1 / 8.0, 7, 7, oh.to(cuda), sp.to(cuda),
                                                     row_scale=(obj + 1.0).to(cuda), mask_scale=True, return_scales=True)
@@ -163,4 +163,4 @@ def test_moi_pool_range_max_mode_dense_masks_and_scales(cuda, oracle):
             plain, parg = ops.moi_pool_forward(x.to(cuda), rois.to(cuda), 1 / 8.0, 7, 7, oh.to(cuda), sp.to(cuda))
             assert np.array_equal(plain.cpu().numpy(), ref) and np.array_equal(parg.cpu().numpy(), rarg)
     finally:
-        _lib.set_tuning("moi_rmq", -1)
+        _lib.set_tuning("moi_rmq", 60)
