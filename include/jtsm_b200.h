@@ -148,8 +148,8 @@ JTSM_API int jtsm_roi_align_backward_det(const void* grad_output, long long stri
  * Backward (ROILoopPool.h:67-77, _cuda.cu:207-248) = jtsm_roi_pool_backward over 3R rows with
  * rois repeated three times.
  * ------------------------------------------------------------------------ */
-JTSM_API size_t jtsm_roi_loop_pool_workspace_bytes(int batch, int num_rois, int pooled_h,
-                                                   int pooled_w);
+JTSM_API size_t jtsm_roi_loop_pool_workspace_bytes(int batch, int height, int width,
+                                                    int num_rois, int pooled_h, int pooled_w);
 JTSM_API int jtsm_roi_loop_pool_forward(const void* input, const float* rois, int dtype, int batch,
                                         int channels, int height, int width, int num_rois,
                                         float spatial_scale, float context_ratio, int pooled_h,

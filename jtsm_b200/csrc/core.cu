@@ -24,6 +24,7 @@ std::map<std::string, int>& tuning_map() {
       {"roi_align_fwd_algo", 0},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
       {"roi_align_force_gmem", 0},
       {"moi_rmq", 60},             // MOIPool: fully switched-on bins go to the RoIPool range-max kernel when <= this % of the bins are partially masked (device-side gate); -1 = off
+      {"loop_algo", 0},            // ROILoopPool forward: 0 = auto (virtual RoIs: range-max + visit lists), 1 = direct scans
       {"moi_planes", 2},           // channels per CTA of the MOIPool visit-list kernel (1 or 2)
       {"moi_algo", 0},             // MOIPool forward: 0 = auto (per-bin visit lists), 1 = row bit masks, 2 = byte-mask scan
   };

@@ -65,6 +65,7 @@ struct MoiAux {
   const int* slow_total;    // [1] number of bins left to the visit lists (the gate)
   int total_bins;
   int gate_pct;
+  int zero_floor;           // ROILoopPool: values <= 0 give (0, -1) -- its running maximum starts at 0
 };
 __device__ __forceinline__ bool moi_rmq_gate(const int* slow_count, int total_bins, int gate_pct) {
   return (long long)__ldg(slow_count) * 100 <= (long long)total_bins * gate_pct;
@@ -198,8 +199,8 @@ __device__ __forceinline__ RmqItem rmq_item(int nc, int chunk, int chunks, int c
 template <typename T, typename A, bool kUngrouped, bool kMoi>
 __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
                                               const RmqItem& it, int PP, int cpp, unsigned w2, unsigned magic_pp,
-                                              const float* __restrict__ mask_scale, T* __restrict__ output,
-                                              A* __restrict__ argmax) {
+                                              const float* __restrict__ mask_scale, int zero_floor,
+                                              T* __restrict__ output, A* __restrict__ argmax) {
   const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
   const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
@@ -242,8 +243,13 @@ __device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned
       if (kUngrouped && act) act = __ldg(ws.batch_idx + (o[k] - o_c) / (unsigned)cpp) == it.n;
       if (act) {
         const float v = kMoi ? __fmul_rn(best[k].v, ms[k]) : best[k].v;  // (f * mask_scale) * (objectness + 1)
-        output[o[k]] = Elem<T>::from_f(__fmul_rn(v, sc[k]));
-        argmax[o[k]] = (A)best[k].i;  // a fast bin always has a cell
+        if (kMoi && zero_floor && !(best[k].v > 0.f)) {
+          output[o[k]] = Elem<T>::from_f(0.f);
+          argmax[o[k]] = Arg<A>::enc(-1);
+        } else {
+          output[o[k]] = Elem<T>::from_f(__fmul_rn(v, sc[k]));
+          argmax[o[k]] = (A)best[k].i;  // a fast bin always has a cell
+        }
       }
     }
   }
@@ -360,9 +366,9 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W,
     }
     if (it.nr > 0) r_hi = it.r0 + it.nr;  // chunks of a plane are consecutive RoI ranges
     if (ungrouped)
-      rmq_main_loop<T, A, true, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, output, argmax);
+      rmq_main_loop<T, A, true, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, moi.zero_floor, output, argmax);
     else
-      rmq_main_loop<T, A, false, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, output, argmax);
+      rmq_main_loop<T, A, false, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, moi.zero_floor, output, argmax);
   }
   if (cur_plane >= 0)
     rmq_slow_pass<T, A, kMoi>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,

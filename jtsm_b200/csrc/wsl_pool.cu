@@ -566,6 +566,7 @@ moi_pool_fwd_list_kernel(const T* __restrict__ input, int channels, int H, int W
                          const unsigned short* __restrict__ perm, const uint2* __restrict__ lists,
                          unsigned int cap_quads, const float* __restrict__ scales, int num_rois,
                          const int* __restrict__ gate_count, int gate_total, int gate_pct,
+                         int zero_floor /* ROILoopPool: the running maximum starts at 0 (ROILoopPool_cuda.cu:109) */,
                          T* __restrict__ output, int* __restrict__ argmax) {
   extern __shared__ float plane_s[];
   // range-max mode (device decision, same test in roi_pool_fwd_rmq_kernel): the fully switched-on bins (descriptor bit
@@ -626,6 +627,7 @@ moi_pool_fwd_list_kernel(const T* __restrict__ input, int channels, int H, int W
 #pragma unroll
     for (int j = 0; j < NPL; ++j) {
       const size_t o = ((size_t)r * channels + c0 + j) * PP + bin;
+      if (zero_floor && !(m[j] > 0.f)) mi[j] = -1;
       float v = mi[j] == -1 ? 0.f : m[j];
       if (scales) v = __fmul_rn(__fmul_rn(v, sc), sr);  // (f * mask_scale) * (objectness + 1)
       output[o] = Elem<T>::from_f(v);
@@ -703,53 +705,6 @@ __global__ void moi_prep_kernel(const float* __restrict__ rois, int num_rois, in
   }
 }
 }  // namespace jtsm
-
-extern "C" size_t jtsm_roi_loop_pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w) {
-  if (batch < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0) return 0;
-  return pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 2) +
-         align_up((size_t)num_rois * sizeof(LoopRects), 256) + 256;
-}
-
-extern "C" int jtsm_roi_loop_pool_forward(const void* input, const float* rois, int dtype, int batch,
-                                          int channels, int height, int width, int num_rois,
-                                          float spatial_scale, float context_ratio, int pooled_h,
-                                          int pooled_w, void* output, int* argmax, void* workspace,
-                                          size_t workspace_bytes, void* stream) {
-  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 ||
-      pooled_h > 64 || pooled_w > 64 || !(context_ratio > 0.f))
-    return JTSM_ERR_INVALID_ARGUMENT;
-  if (height > 32767 || width > 32767) return JTSM_ERR_UNSUPPORTED;
-  if (num_rois == 0 || channels == 0) return JTSM_OK;
-  if (!input || !rois || !output || !argmax || !workspace || batch == 0 || height == 0 || width == 0)
-    return JTSM_ERR_INVALID_ARGUMENT;
-  if (workspace_bytes < jtsm_roi_loop_pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w))
-    return JTSM_ERR_WORKSPACE_TOO_SMALL;
-  cudaStream_t st = (cudaStream_t)stream;
-  PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 2);
-  LoopRects* rects = (LoopRects*)(((uintptr_t)workspace + pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 2) + 255) &
-                                  ~(uintptr_t)255);
-  cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
-  loop_pool_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width, spatial_scale,
-                                                                context_ratio, pooled_h, pooled_w, ws, rects);
-  count_launch();
-  const int planes = batch * channels;
-  const int splits = wsl_splits(planes, num_rois);
-  const size_t smem = (size_t)height * width * sizeof(float);
-  const bool use_smem = smem <= 200 * 1024;
-  JTSM_DISPATCH_DTYPE(dtype, T, {
-    if (use_smem) {
-      auto k = loop_pool_fwd_kernel<T, true>;
-      if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
-                                                     splits, num_rois, ws, rects, (T*)output, argmax);
-    } else {
-      loop_pool_fwd_kernel<T, false><<<planes * splits, kWslThreads, 0, st>>>(
-          (const T*)input, channels, height, width, pooled_h, pooled_w, splits, num_rois, ws, rects, (T*)output, argmax);
-    }
-  });
-  count_launch();
-  return cuda_status();
-}
 
 namespace {
 // uint2 (= four uint16 cell indices) entries per RoI slot: the bins of a RoI overlap by at most one row / column,
@@ -850,6 +805,7 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
       MoiAux aux;
       aux.mask_scale = ms_buf;
       aux.slow_total = slow_total;
+      aux.zero_floor = 0;
       aux.total_bins = (int)npp;
       aux.gate_pct = gate_pct;
       const int rc = moi_rmq_launch(dtype, input, batch, channels, height, width, num_rois, pooled_h, pooled_w, ws, aux,
@@ -884,7 +840,7 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
       if (sm > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
       k<<<groups * lsplits, kMoiFwdThreads, sm, st>>>((const T*)input, channels, height, width, pooled_h * pooled_w,
                                                       lsplits, ws, desc, perm, lists, (unsigned int)cap_quads, scales,
-                                                      num_rois, use_rmq ? slow_total : nullptr, (int)npp, gate_pct,
+                                                      num_rois, use_rmq ? slow_total : nullptr, (int)npp, gate_pct, 0,
                                                       (T*)output, argmax);
     } else if (use_bits) {
       auto k = moi_pool_fwd_bits_kernel<T>;
@@ -905,3 +861,213 @@ extern "C" int jtsm_moi_pool_forward(const void* input, const float* rois, const
   count_launch();
   return cuda_status();
 }
+
+// ---------------------------------------------------------------------------------------------
+// ROILoopPool entry points (after the MOIPool machinery they reuse)
+// ---------------------------------------------------------------------------------------------
+namespace jtsm {
+// ROILoopPool as a masked max-pool over 3R virtual RoIs (v = set * R + r, the op's own output order):
+//   set 0: bins of the RoI rectangle, every cell allowed;
+//   set 1: bins of the RoI rectangle, cells strictly inside the inner rectangle excluded (frame pool);
+//   set 2: bins of the outer rectangle, cells strictly inside the RoI rectangle excluded (context pool)
+// (ROILoopPool_cuda.cu:35-203).  One CTA per RoI writes the bin tables, the RoIPool range-max descriptors and the
+// 128-bit row masks of its three virtual RoIs; moi_list_kernel / the range-max kernel / the visit-list kernel then run
+// unchanged, with the running maximum floored at 0 (zero_floor).
+__global__ void __launch_bounds__(128)
+loop_virtual_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, int H, int W, float scale,
+                         float ratio, int PH, int PW, PoolWorkspace ws, uint4* __restrict__ rowbits) {
+  __shared__ int s_rect[3][4];  // roi, inner, outer: (sw, sh, ew, eh)
+  __shared__ int s_b;
+  const int r = blockIdx.x;
+  if (threadIdx.x == 0) {
+    const float* q = rois + (size_t)r * 5;
+    const float x1 = q[1], y1 = q[2], x2 = q[3], y2 = q[4];
+    const float rw = __fsub_rn(x2, x1), rh = __fsub_rn(y2, y1);
+    const float iw = __fdiv_rn(rw, ratio), ih = __fdiv_rn(rh, ratio);
+    const float ow = __fmul_rn(rw, ratio), oh = __fmul_rn(rh, ratio);
+    const float irw = __fsub_rn(rw, iw), irh = __fsub_rn(rh, ih);
+    const float orw = __fsub_rn(ow, rw), orh = __fsub_rn(oh, rh);
+    const float lim_w = (float)(1.0 * W / (double)scale), lim_h = (float)(1.0 * H / (double)scale);
+    const RoiRect roi = roi_rect(x1, y1, x2, y2, scale);
+    const RoiRect inner = roi_rect(clampf_(__fadd_rn(x1, __fdiv_rn(irw, 2.f)), 0.f, lim_w),
+                                   clampf_(__fadd_rn(y1, __fdiv_rn(irh, 2.f)), 0.f, lim_h),
+                                   clampf_(__fsub_rn(x2, __fdiv_rn(irw, 2.f)), 0.f, lim_w),
+                                   clampf_(__fsub_rn(y2, __fdiv_rn(irh, 2.f)), 0.f, lim_h), scale);
+    const RoiRect outer = roi_rect(clampf_(__fsub_rn(x1, __fdiv_rn(orw, 2.f)), 0.f, lim_w),
+                                   clampf_(__fsub_rn(y1, __fdiv_rn(orh, 2.f)), 0.f, lim_h),
+                                   clampf_(__fadd_rn(x2, __fdiv_rn(orw, 2.f)), 0.f, lim_w),
+                                   clampf_(__fadd_rn(y2, __fdiv_rn(orh, 2.f)), 0.f, lim_h), scale);
+    const RoiRect rc[3] = {roi, inner, outer};
+    for (int k = 0; k < 3; ++k) {
+      s_rect[k][0] = rc[k].sw; s_rect[k][1] = rc[k].sh; s_rect[k][2] = rc[k].ew; s_rect[k][3] = rc[k].eh;
+    }
+    const int b = (int)q[0];
+    s_b = (b >= 0 && b < batch) ? b : -1;
+    if (r == 0) *ws.ungrouped = batch > 1;  // virtual RoIs of an image are not one contiguous run
+  }
+  __syncthreads();
+  const int hw = H * W, PP = PH * PW;
+  for (int set = 0; set < 3; ++set) {
+    const int v = set * num_rois + r;
+    const int* base = s_rect[set == 2 ? 2 : 0];  // rectangle whose bins are pooled
+    const int* ex = s_rect[set == 1 ? 1 : 0];    // exclusion rectangle (sets 1 and 2)
+    const int w_ = max(base[2] - base[0] + 1, 1), h_ = max(base[3] - base[1] + 1, 1);
+    for (int p = threadIdx.x; p < PH; p += 128) ws.hbins[(size_t)v * PH + p] = bin_range(p, base[1], h_, PH, H);
+    for (int p = threadIdx.x; p < PW; p += 128) ws.wbins[(size_t)v * PW + p] = bin_range(p, base[0], w_, PW, W);
+    if (threadIdx.x == 0) {
+      ws.batch_idx[v] = s_b;
+      ws.rscale[v] = 1.f;
+      if (s_b >= 0) {
+        atomicMin(ws.first + s_b, v);
+        atomicMin(ws.neg_last + s_b, -v);
+      }
+    }
+    for (int h = threadIdx.x; h < H; h += 128) {
+      uint32_t m[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int nb = min(32, max(0, W - 32 * k));
+        m[k] = nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u);
+      }
+      if (set > 0 && h > ex[1] && h < ex[3]) {  // clear the columns strictly inside the exclusion rectangle
+        const int lo = max(ex[0] + 1, 0), hi = min(ex[2] - 1, W - 1);
+        for (int w = lo; w <= hi; ++w) m[w >> 5] &= ~(1u << (w & 31));
+      }
+      rowbits[(size_t)v * H + h] = make_uint4(m[0], m[1], m[2], m[3]);
+    }
+  }
+  __syncthreads();  // the bin tables written above are read back below
+  for (int j = threadIdx.x; j < 3 * PP; j += 128) {
+    const int set = j / PP, bin = j - set * PP, ph = bin / PW, pw = bin - ph * PW;
+    const int v = set * num_rois + r;
+    ws.bdesc[(size_t)v * PP + bin] =
+        rmq_bin_desc(ws.hbins[(size_t)v * PH + ph], ws.wbins[(size_t)v * PW + pw], W, hw);
+  }
+}
+}  // namespace jtsm
+
+namespace {
+// Workspace of the virtual-RoI path: bin tables / descriptors for 3R virtual RoIs, their row bit masks, visit lists,
+// sorted descriptors, unit mask scales and the gate counter.
+struct LoopVirtLayout {
+  size_t pool, rowbits, desc, perm, lists, ms, total;
+  size_t cap_quads;
+};
+LoopVirtLayout loop_virt_layout(int batch, int height, int width, int num_rois, int PH, int PW) {
+  LoopVirtLayout L;
+  const size_t v = 3 * (size_t)num_rois, npp = v * PH * PW;
+  L.cap_quads = moi_cap_quads(height, width, PH, PW);
+  L.pool = pool_workspace_bytes(batch, (int)v, PH, PW, 1);
+  L.rowbits = align_up(v * height * sizeof(uint4), 256);
+  L.desc = align_up(npp * sizeof(uint32_t), 256);
+  L.perm = align_up(npp * sizeof(unsigned short), 256);
+  L.lists = align_up(v * L.cap_quads * sizeof(uint2), 256);
+  L.ms = align_up(v * sizeof(float), 256);
+  L.total = L.pool + L.rowbits + L.desc + L.perm + L.lists + L.ms + 512;
+  return L;
+}
+bool loop_virt_ok(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
+  return tuning("loop_algo", 0) == 0 && width <= 128 && moi_cap_quads(height, width, PH, PW) != 0 &&
+         (long long)num_rois * 3 < 0x7FFFFFFFLL / (PH * PW) &&
+         ((size_t)height * width + 1) * sizeof(float) * 2 <= 200 * 1024 &&
+         moi_rmq_eligible(batch, channels, height, width, 3 * num_rois, PH, PW);
+}
+}  // namespace
+
+extern "C" size_t jtsm_roi_loop_pool_workspace_bytes(int batch, int height, int width, int num_rois, int pooled_h,
+                                                     int pooled_w) {
+  if (batch < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0) return 0;
+  const size_t direct = pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 2) +
+                        align_up((size_t)num_rois * sizeof(LoopRects), 256) + 256;
+  const size_t virt = loop_virt_layout(batch, height, width, num_rois, pooled_h, pooled_w).total;
+  return direct > virt ? direct : virt;
+}
+
+extern "C" int jtsm_roi_loop_pool_forward(const void* input, const float* rois, int dtype, int batch,
+                                          int channels, int height, int width, int num_rois,
+                                          float spatial_scale, float context_ratio, int pooled_h,
+                                          int pooled_w, void* output, int* argmax, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+  if (batch < 0 || channels < 0 || height < 0 || width < 0 || num_rois < 0 || pooled_h <= 0 || pooled_w <= 0 ||
+      pooled_h > 64 || pooled_w > 64 || !(context_ratio > 0.f))
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (height > 32767 || width > 32767) return JTSM_ERR_UNSUPPORTED;
+  if (num_rois == 0 || channels == 0) return JTSM_OK;
+  if (!input || !rois || !output || !argmax || !workspace || batch == 0 || height == 0 || width == 0)
+    return JTSM_ERR_INVALID_ARGUMENT;
+  if (workspace_bytes < jtsm_roi_loop_pool_workspace_bytes(batch, height, width, num_rois, pooled_h, pooled_w))
+    return JTSM_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (loop_virt_ok(batch, channels, height, width, num_rois, pooled_h, pooled_w)) {
+    // The three pools as 3R virtual RoIs of a masked max-pool (mask = cells outside the exclusion rectangle):
+    // fully allowed bins -> RoIPool range-max kernel, the rest -> visit lists; values <= 0 give (0, -1).
+    const int V = 3 * num_rois, PP = pooled_h * pooled_w, hw = height * width;
+    const LoopVirtLayout L = loop_virt_layout(batch, height, width, num_rois, pooled_h, pooled_w);
+    PoolWorkspace vw = carve_pool_workspace(workspace, batch, V, pooled_h, pooled_w, 1);
+    char* p = (char*)(((uintptr_t)workspace + L.pool + 255) & ~(uintptr_t)255);
+    uint4* rowbits = (uint4*)p; p += L.rowbits;
+    uint32_t* desc = (uint32_t*)p; p += L.desc;
+    unsigned short* perm = (unsigned short*)p; p += L.perm;
+    uint2* lists = (uint2*)p; p += L.lists;
+    float* ms_buf = (float*)p; p += L.ms;
+    int* slow_total = (int*)p;
+    cudaMemsetAsync(vw.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
+    cudaMemsetAsync(vw.ungrouped, 0, 2 * sizeof(int), st);
+    cudaMemsetAsync(slow_total, 0, sizeof(int), st);
+    loop_virtual_prep_kernel<<<num_rois, 128, 0, st>>>(rois, num_rois, batch, height, width, spatial_scale,
+                                                       context_ratio, pooled_h, pooled_w, vw, rowbits);
+    moi_list_kernel<<<V, kMoiListThreads, 0, st>>>(height, width, pooled_h, pooled_w, vw, rowbits,
+                                                   (unsigned int)L.cap_quads, desc, perm, lists, nullptr, 0, V, nullptr,
+                                                   1, ms_buf, slow_total);
+    count_launch(2);
+    MoiAux aux;
+    aux.mask_scale = ms_buf;
+    aux.slow_total = slow_total;
+    aux.total_bins = V * PP;
+    aux.gate_pct = 100;  // the RoI set alone is a third of the bins and all of it is fully allowed
+    aux.zero_floor = 1;
+    int rc = moi_rmq_launch(dtype, input, batch, channels, height, width, V, pooled_h, pooled_w, vw, aux, output, argmax,
+                            st);
+    if (rc != JTSM_OK) return rc;
+    const size_t plane_b = ((size_t)hw + 1) * sizeof(float);
+    const bool two = channels % 2 == 0;
+    const int npl = two ? 2 : 1;
+    const int groups = batch * channels / npl;
+    const int lsplits = wsl_splits(groups, V);
+    JTSM_DISPATCH_DTYPE(dtype, T, {
+      auto k = two ? moi_pool_fwd_list_kernel<T, 2> : moi_pool_fwd_list_kernel<T, 1>;
+      if (npl * plane_b > 48 * 1024)
+        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(npl * plane_b));
+      k<<<groups * lsplits, kMoiFwdThreads, npl * plane_b, st>>>(
+          (const T*)input, channels, height, width, PP, lsplits, vw, desc, perm, lists, (unsigned int)L.cap_quads,
+          nullptr, V, slow_total, V * PP, 100, 1, (T*)output, argmax);
+    });
+    count_launch();
+    return cuda_status();
+  }
+  PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 2);
+  LoopRects* rects = (LoopRects*)(((uintptr_t)workspace + pool_workspace_bytes(batch, num_rois, pooled_h, pooled_w, 2) + 255) &
+                                  ~(uintptr_t)255);
+  cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
+  loop_pool_prep_kernel<<<(num_rois + 127) / 128, 128, 0, st>>>(rois, num_rois, batch, height, width, spatial_scale,
+                                                                context_ratio, pooled_h, pooled_w, ws, rects);
+  count_launch();
+  const int planes = batch * channels;
+  const int splits = wsl_splits(planes, num_rois);
+  const size_t smem = (size_t)height * width * sizeof(float);
+  const bool use_smem = smem <= 200 * 1024;
+  JTSM_DISPATCH_DTYPE(dtype, T, {
+    if (use_smem) {
+      auto k = loop_pool_fwd_kernel<T, true>;
+      if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      k<<<planes * splits, kWslThreads, smem, st>>>((const T*)input, channels, height, width, pooled_h, pooled_w,
+                                                     splits, num_rois, ws, rects, (T*)output, argmax);
+    } else {
+      loop_pool_fwd_kernel<T, false><<<planes * splits, kWslThreads, 0, st>>>(
+          (const T*)input, channels, height, width, pooled_h, pooled_w, splits, num_rois, ws, rects, (T*)output, argmax);
+    }
+  });
+  count_launch();
+  return cuda_status();
+}
+

@@ -494,7 +494,7 @@ def roi_loop_pool_forward(input, rois, spatial_scale, pooled_height, pooled_widt
     if r == 0 or c == 0:
         return output, argmax
     L = lib()
-    wsb = L.jtsm_roi_loop_pool_workspace_bytes(n, r, ph, pw)
+    wsb = L.jtsm_roi_loop_pool_workspace_bytes(n, h, w, r, ph, pw)
     ws = _workspace(wsb, input.device)
     with torch.cuda.device(input.device):
         check(L.jtsm_roi_loop_pool_forward(_ptr(input), _ptr(rois), _dtype_code(input), n, c, h, w, r,

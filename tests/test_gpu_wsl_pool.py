@@ -164,3 +164,33 @@ def test_moi_pool_range_max_mode_dense_masks_and_scales(cuda, oracle):
             assert np.array_equal(plain.cpu().numpy(), ref) and np.array_equal(parg.cpu().numpy(), rarg)
     finally:
         _lib.set_tuning("moi_rmq", 60)
+
+
+@pytest.mark.parametrize("n,c,h,w,r,scale,pooled", [(1, 6, 75, 100, 200, 1 / 8.0, (7, 7)), (2, 4, 38, 50, 120, 1 / 16.0, (7, 7)),
+                                                    (2, 3, 75, 100, 60, 1 / 8.0, (14, 14)), (1, 5, 38, 50, 40, 1 / 16.0, (3, 5)),
+                                                    (1, 2, 60, 150, 50, 1 / 8.0, (7, 7))])
+def test_roi_loop_pool_virtual_roi_path_equals_direct_scans_and_oracle(cuda, oracle, n, c, h, w, r, scale, pooled):
+    """ROILoopPool as 3R virtual RoIs on the range-max + visit-list kernels (default when W <= 128) against the direct
+    scans and the oracle (itself bit-equal to the reference's kernel, tests/test_ref_native.py): values and argmax
+    bit-exact, incl. extreme boxes (context rectangle leaves the map, degenerate boxes) and shuffled batch indices."""
+    from jtsm_b200 import _lib, ops
+
+    g = synth.generator(400 + r)
+    img = (int(h / scale), int(w / scale))
+    x = synth.feature_map(g, n, c, h, w)
+    x[:, 0] = 0.0  # an all-zero channel: nothing beats the 0 the running maximum starts at -> argmax -1
+    rois = synth.rois_from_boxes([synth.proposals(g, r // n, *img) for _ in range(n)])
+    rois = rois[torch.randperm(rois.shape[0], generator=g)].contiguous()
+    rois[0, 1:] = torch.tensor([0.0, 0.0, img[1] - 1.0, img[0] - 1.0])
+    rois[1, 1:] = torch.tensor([100.0, 100.0, 100.0, 100.0])
+    rois[2, 1:] = torch.tensor([-50.0, -40.0, 30.0, 20.0])
+    rois[3, 1:] = torch.tensor([img[1] - 100.0, img[0] - 100.0, img[1] + 100.0, img[0] + 100.0])
+    ref, rarg = oracle.roi_loop_pool_forward(x.numpy(), rois.numpy(), scale, pooled)
+    try:
+        for algo in (0, 1):
+            _lib.set_tuning("loop_algo", algo)
+            out, arg = ops.roi_loop_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled[0], pooled[1])
+            assert np.array_equal(out.cpu().numpy(), ref), algo
+            assert np.array_equal(arg.cpu().numpy(), rarg), algo
+    finally:
+        _lib.set_tuning("loop_algo", 0)
