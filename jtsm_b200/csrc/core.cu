@@ -23,6 +23,7 @@ std::map<std::string, int>& tuning_map() {
       {"roi_align_bwd_algo", 0},   // 0 = auto (separable: column kernel for PH <= 16, else cell kernel), 1 = one RED per tap, 2 = cell kernel
       {"roi_align_fwd_algo", 0},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
       {"roi_align_force_gmem", 0},
+      {"roi_align_fwd_pairs", 1},  // 1 = staged plane as (x, x+1) pairs: one 8-byte shared load per row of a sample
       {"moi_rmq", 60},             // MOIPool: fully switched-on bins go to the RoIPool range-max kernel when <= this % of the bins are partially masked (device-side gate); -1 = off
       {"loop_algo", 0},            // ROILoopPool forward: 0 = auto (virtual RoIs: range-max + visit lists), 1 = direct scans
       {"moi_planes", 2},           // channels per CTA of the MOIPool visit-list kernel (1 or 2)

@@ -184,7 +184,9 @@ __global__ void roi_align_taps_kernel(int num_rois, int H, int W, int PH, int PW
 constexpr int kAlignThreads = 512;
 
 // grid: persistent CTAs over (plane, chunk) items.  kSmem: plane staged in shared memory.
-template <typename T, bool kSmem>
+// kPairs: the staged plane holds (p[y][x], p[y][min(x + 1, W - 1)]) pairs, so the two taps of a row come from ONE 8-byte
+// shared load (the reference's x_high is exactly min(x_low + 1, W - 1)): 2 loads per sample instead of 4.
+template <typename T, bool kSmem, bool kPairs = false>
 __global__ void __launch_bounds__(kAlignThreads)
 roi_align_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW, int chunks,
                      int num_items, AlignWorkspace ws, T* __restrict__ output) {
@@ -209,7 +211,15 @@ roi_align_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, in
     if (kSmem && nc != cur_plane) {
       __syncthreads();
       cur_plane = nc;
-      for (int p = threadIdx.x; p < hw; p += kAlignThreads) plane_s[p] = Elem<T>::to_f(src[p]);
+      if (kPairs) {
+        float2* pp = (float2*)plane_s;
+        for (int p = threadIdx.x; p < hw; p += kAlignThreads) {
+          const int x = p % W;
+          pp[p] = make_float2(Elem<T>::to_f(src[p]), Elem<T>::to_f(src[x + 1 < W ? p + 1 : p]));
+        }
+      } else {
+        for (int p = threadIdx.x; p < hw; p += kAlignThreads) plane_s[p] = Elem<T>::to_f(src[p]);
+      }
       __syncthreads();
     }
     const int first = ws.first[n];
@@ -252,7 +262,10 @@ roi_align_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, in
             float hx, lx;
             align_tap_cells(x, W, xl, xh, hx, lx);
             float v1, v2, v3, v4;
-            if (kSmem) {
+            if (kPairs) {
+              const float2 a = ((const float2*)plane_s)[yl + xl], b = ((const float2*)plane_s)[yh + xl];
+              v1 = a.x; v2 = a.y; v3 = b.x; v4 = b.y;
+            } else if (kSmem) {
               v1 = plane_s[yl + xl]; v2 = plane_s[yl + xh]; v3 = plane_s[yh + xl]; v4 = plane_s[yh + xh];
             } else {
               v1 = Elem<T>::to_f(__ldg(src + yl + xl)); v2 = Elem<T>::to_f(__ldg(src + yl + xh));
@@ -275,7 +288,10 @@ roi_align_fwd_kernel(const T* __restrict__ input, int channels, int H, int W, in
           float val = 0.f;
           if (bilinear_taps(H, W, y, x, t)) {
             float v1, v2, v3, v4;
-            if (kSmem) {
+            if (kPairs) {
+              const float2 a = ((const float2*)plane_s)[t.p1], b = ((const float2*)plane_s)[t.p3];
+              v1 = a.x; v2 = a.y; v3 = b.x; v4 = b.y;
+            } else if (kSmem) {
               v1 = plane_s[t.p1]; v2 = plane_s[t.p2]; v3 = plane_s[t.p3]; v4 = plane_s[t.p4];
             } else {
               v1 = Elem<T>::to_f(__ldg(src + t.p1)); v2 = Elem<T>::to_f(__ldg(src + t.p2));
@@ -553,8 +569,12 @@ template <typename T>
 int launch_align_fwd(const void* input, int batch, int channels, int H, int W, int num_rois, int PH, int PW,
                      const AlignWorkspace& ws, void* output, cudaStream_t st) {
   const int planes = batch * channels;
-  const size_t smem = (size_t)H * W * sizeof(float);
-  const bool use_smem = smem <= 200 * 1024 && !tuning("roi_align_force_gmem", 0);
+  const size_t plane_b = (size_t)H * W * sizeof(float);
+  const bool use_smem = plane_b <= 200 * 1024 && !tuning("roi_align_force_gmem", 0);
+  // pairs only while four CTAs still fit per SM: at c2 (30 KB planes) the lost occupancy costs more than the halved
+  // load count saves (sr 2: 673 vs 614 us; adaptive 1972 vs 2085), at c1 (7.6 KB) it wins 5-7 % (profiles/r1q)
+  const bool pairs = use_smem && 2 * plane_b <= 52 * 1024 && tuning("roi_align_fwd_pairs", 1) != 0;
+  const size_t smem = pairs ? 2 * plane_b : plane_b;
   int per_sm = use_smem ? (int)((220 * 1024) / (smem + 1024)) : 4;
   per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
   const int max_grid = num_sms() * per_sm;
@@ -564,7 +584,7 @@ int launch_align_fwd(const void* input, int batch, int channels, int H, int W, i
   const int items = planes * chunks;
   const int grid = items < max_grid ? items : max_grid;
   if (use_smem) {
-    auto k = roi_align_fwd_kernel<T, true>;
+    auto k = pairs ? roi_align_fwd_kernel<T, true, true> : roi_align_fwd_kernel<T, true, false>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k<<<grid, kAlignThreads, smem, st>>>((const T*)input, channels, H, W, PH, PW, chunks, items, ws, (T*)output);
   } else {
