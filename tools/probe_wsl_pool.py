@@ -14,7 +14,10 @@ gen = torch.Generator().manual_seed(5)
 sp, S = synth.superpixels(gen, x.shape[0], cfg["img_h"], cfg["img_w"])
 oh = synth.oh_labels(gen, rois.shape[0], S)
 sp_d, oh_d = sp.to(dev), oh.to(dev)
+sp2, oh2, _, _ = synth.superpixel_case(torch.Generator().manual_seed(6), boxes, cfg["img_h"], cfg["img_w"], 22)
+sp2_d, oh2_d = sp2.to(dev), oh2.to(dev)
 for _ in range(3):
+    ops.moi_pool_forward(x, rois_d, cfg["scale"], cfg["P"], cfg["P"], oh2_d, sp2_d)  # box-consistent (dense) masks
     ops.moi_pool_forward(x, rois_d, cfg["scale"], cfg["P"], cfg["P"], oh_d, sp_d)
     ops.roi_loop_pool_forward(x, rois_d, cfg["scale"], cfg["P"], cfg["P"])
 torch.cuda.synchronize()
