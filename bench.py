@@ -244,7 +244,11 @@ def run_b200(a):
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         g0.record()
         for _ in range(a.steps):
-            step.slots[0]["graph"].replay()
+            if step.slots[0]["graph"] is not None:
+                step.slots[0]["graph"].replay()
+            else:
+                step.slots[0]["graph_a"].replay()
+                step.slots[0]["graph_b"].replay()
         g1.record()
         barrier()
         io_graph_ms = g0.elapsed_time(g1) / a.steps
@@ -262,7 +266,9 @@ def run_b200(a):
         f1.record()
         barrier()
         e2e_flush_ms = f0.elapsed_time(f1)
-        e2e_mode = "pipelined: H2D(i+1) | step(i) | D2H(i-1) on three streams, %d buffer sets" % len(step.slots)
+        e2e_mode = "pipelined: H2D | step | D2H on three streams, %d buffer sets, uploads %s" % (
+            len(step.slots), "held back until the running step's pooling forward has finished (two half-arena copies "
+            "per step)" if step.overlap == "after_forward" else "as soon as queued")
     else:
         for _ in range(3):
             step.run_from_host(host)

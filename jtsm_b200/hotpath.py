@@ -157,15 +157,22 @@ class HotPathStep:
         e1.record()
         return e0, e1
 
-    def run(self, d):
-        x, rois = d["feat"], d["rois"]
+    def run_forward(self, d):
+        """pool fwd + the whole head (everything up to the point where fc6's backward would hand back its gradient)."""
         pooled, argmax, bwd_scale = self.pool_forward(d)
         cfg = self.cfg
         h = heads.head_step(d["mil_cls"], d["mil_det"], d["ref_logits"], d["ref_deltas"], d["proposals"], self.counts,
                             (d["cls_off"], d["cls_ids"], self.cls_cap, len(self.counts) * self.cls_cap), cfg["K"],
                             d["labels_onehot"], reg=cfg["reg"], streams=self.side_streams)
-        grad_feat = ops.roi_pool_backward(d["_grad_pooled"], rois, argmax, x.shape, self.P, row_scale=bwd_scale)
-        self.last = dict(pooled=pooled, grad_feat=grad_feat, heads=h)
+        return dict(pooled=pooled, argmax=argmax, bwd_scale=bwd_scale, heads=h)
+
+    def run_backward(self, d, st):
+        grad_feat = ops.roi_pool_backward(d["_grad_pooled"], d["rois"], st["argmax"], d["feat"].shape, self.P,
+                                          row_scale=st["bwd_scale"])
+        self.last = dict(pooled=st["pooled"], grad_feat=grad_feat, heads=st["heads"])
+
+    def run(self, d):
+        self.run_backward(d, self.run_forward(d))
 
     # ------------------------------------------------------------------ CUDA graph of the step
     def derive_inputs(self, d):
@@ -205,6 +212,31 @@ class HotPathStep:
         self.static_inputs = d
         self.graph_last = self.last  # the graph's static output buffers
         return self.graph
+
+    def capture_split(self, d):
+        """The streamed step as TWO graphs over the same buffers: A = derive inputs + pool forward + heads, B = pool
+        backward + result packing.  The streaming loop records an event between them so that uploads can be held back
+        until the pooling forward -- the one kernel a concurrent H2D copy slows down (221 -> 260 us at c2: the DMA
+        writes disturb the L2 write-combining its output relies on) -- has finished."""
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):
+                self.derive_inputs(d)
+                self.run(d)
+                self.results()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(ga):
+            self.derive_inputs(d)
+            st = self.run_forward(d)
+        with torch.cuda.graph(gb, pool=ga.pool()):
+            self.run_backward(d, st)
+            self.graph_results = self.results()
+            self.graph_packed = self._pack(self.graph_results)
+        self.graph_last = self.last
+        return ga, gb
 
     def replay(self):
         self.graph.replay()
@@ -248,30 +280,47 @@ class HotPathStep:
         return out
 
     # ------------------------------------------------------------------ pipelined stream of steps from host memory
-    def prepare_stream(self, host, depth=None):
+    def prepare_stream(self, host, depth=None, overlap=None):
         """`depth` captured copies of the step (sets of static device buffers) + pinned result buffers, so that
-        step i + 1's inputs upload and step i - 1's results download while step i computes; the host runs
-        depth - 1 steps ahead of the results it consumes.  depth: JTSM_STREAM_DEPTH or 2 (3 and 4 measured the same:
-        the streamed rate is bound on the device, not by the host running ahead)."""
-        depth = int(depth or os.environ.get("JTSM_STREAM_DEPTH", "2"))
+        step i + 1's inputs upload and step i - 1's results download while step i computes.
+        overlap: "any" (default; JTSM_STREAM_OVERLAP) = the upload of step i + 1 starts as soon as the host has queued
+        it (depth: JTSM_STREAM_DEPTH or 2; 3 and 4 measured the same); "after_forward" = three buffer sets, each step
+        captured as two graphs and every upload cut in two halves that only run between a pooling forward's end and
+        the next one's start.  A concurrent H2D copy slows the pooling forward by 17 % when the two run back to back
+        (tools/probe_dma.py), but holding the uploads back measured the same end-to-end rate (3.36 M RoIs/s either
+        way at c2), so the simpler schedule stays the default."""
+        self.overlap = overlap or os.environ.get("JTSM_STREAM_OVERLAP", "any")
+        if self.overlap == "after_forward":
+            depth = 3
+        else:
+            depth = int(depth or os.environ.get("JTSM_STREAM_DEPTH", "2"))
         self.slots = []
         for _ in range(max(2, depth)):
             d = self.upload(host)
             torch.cuda.synchronize()
-            graph = self.capture(d, with_io=True)
+            if self.overlap == "after_forward":
+                ga, gb = self.capture_split(d)
+                graph = None
+            else:
+                graph, ga, gb = self.capture(d, with_io=True), None, None
             res = self.graph_packed
             out_buf = torch.empty(res.shape, dtype=torch.uint8).pin_memory()
-            self.slots.append(dict(graph=graph, inputs=d, last=self.graph_last, res=res, out_buf=out_buf,
-                                   out=self._unpack(out_buf),
-                                   ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event()))
+            self.slots.append(dict(graph=graph, graph_a=ga, graph_b=gb, inputs=d, last=self.graph_last, res=res,
+                                   out_buf=out_buf, out=self._unpack(out_buf),
+                                   ev_in=torch.cuda.Event(), ev_done=torch.cuda.Event(), ev_out=torch.cuda.Event(),
+                                   ev_fwd=torch.cuda.Event()))
         self.copy_stream, self.d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
         self._d2h = self.slots[0]["out_buf"].numel()
+        n = self.slots[0]["inputs"]["__arena"].numel()
+        self._half = (n // 2 + 255) & ~255
 
     def run_stream(self, host_batches, consume=None, before_step=None):
         """Run one step per element of `host_batches` (dicts of pinned host tensors as from pin_host_inputs).
         Per step: H2D of its inputs on a copy stream, graph replay on the current stream, D2H of its results
         (losses, pseudo-labels, counters) into pinned buffers on a third stream; `consume(i, results)` is called on
-        the host once step i's results have landed (one step behind the submission)."""
+        the host once step i's results have landed (len(slots) - 1 steps behind the submission)."""
+        if self.overlap == "after_forward":
+            return self._run_stream_after_forward(list(host_batches), consume, before_step)
         comp = torch.cuda.current_stream()
         self.copy_stream.wait_stream(comp)
         n = 0
@@ -291,23 +340,85 @@ class HotPathStep:
                 before_step()
             sl["graph"].replay()  # derive inputs, the step, pack the results: all inside the slot's graph
             sl["ev_done"].record(comp)
-            with torch.cuda.stream(self.d2h_stream):
-                self.d2h_stream.wait_event(sl["ev_done"])
-                sl["out_buf"].copy_(sl["res"], non_blocking=True)  # one copy: every host-bound result of the step
-                sl["ev_out"].record(self.d2h_stream)
+            self._download(sl)
             if i >= lag:
                 prev = self.slots[(i - lag) % ns]
                 prev["ev_out"].synchronize()
                 if consume is not None:
                     consume(i - lag, prev["out"])
             n = i + 1
-        for j in range(max(0, n - lag), n):  # drain: the last results, in order
+        self._drain(n, lag, consume)
+        return n
+
+    def _download(self, sl):
+        with torch.cuda.stream(self.d2h_stream):
+            self.d2h_stream.wait_event(sl["ev_done"])
+            sl["out_buf"].copy_(sl["res"], non_blocking=True)  # one copy: every host-bound result of the step
+            sl["ev_out"].record(self.d2h_stream)
+
+    def _drain(self, n, lag, consume):
+        ns = len(self.slots)
+        for j in range(max(0, n - lag), n):  # the last results, in order
             sl = self.slots[j % ns]
             sl["ev_out"].synchronize()
             if consume is not None:
                 consume(j, sl["out"])
         if n:
-            comp.wait_event(self.slots[(n - 1) % ns]["ev_out"])  # an event recorded on `comp` now covers the last D2H
+            torch.cuda.current_stream().wait_event(self.slots[(n - 1) % ns]["ev_out"])  # covers the last D2H
+
+    def _run_stream_after_forward(self, hosts, consume, before_step):
+        """Uploads only between the end of a pooling forward and the start of the next one.  Step j's arena goes up in
+        two halves: the first after the forward of step j - 2, the second after the forward of step j - 1 (each half
+        takes ~0.15 ms at c2 against the ~0.3 ms of heads + pooling backward it hides behind)."""
+        comp = torch.cuda.current_stream()
+        cs = self.copy_stream
+        cs.wait_stream(comp)
+        ns, lag, half = 3, 2, self._half
+        total = len(hosts)
+
+        def up(j, part):
+            sl = self.slots[j % ns]
+            dst, src = sl["inputs"]["__arena"], hosts[j]["__arena"]
+            if part == 0:
+                dst[:half].copy_(src[:half], non_blocking=True)
+            else:
+                dst[half:].copy_(src[half:], non_blocking=True)
+                sl["ev_in"].record(cs)
+
+        with torch.cuda.stream(cs):  # start-up: step 0 in full, the first half of step 1
+            if total > 0:
+                up(0, 0)
+                up(0, 1)
+            if total > 1:
+                up(1, 0)
+        n = 0
+        for i in range(total):
+            sl = self.slots[i % ns]
+            comp.wait_event(sl["ev_in"])
+            if i >= ns:
+                comp.wait_event(sl["ev_out"])  # the slot's previous results have left the device
+            if before_step is not None:
+                before_step()
+            sl["graph_a"].replay()  # derive inputs, pooling forward, heads
+            sl["ev_fwd"].record(comp)
+            with torch.cuda.stream(cs):
+                # behind this step's forward: the second half of step i + 1 and the first half of step i + 2 (its buffer
+                # set was last read by step i - 1, which ended before this step began)
+                cs.wait_event(sl["ev_fwd"])
+                if i + 1 < total:
+                    up(i + 1, 1)
+                if i + 2 < total:
+                    up(i + 2, 0)
+            sl["graph_b"].replay()  # pooling backward, result packing
+            sl["ev_done"].record(comp)
+            self._download(sl)
+            if i >= lag:
+                prev = self.slots[(i - lag) % ns]
+                prev["ev_out"].synchronize()
+                if consume is not None:
+                    consume(i - lag, prev["out"])
+            n = i + 1
+        self._drain(n, lag, consume)
         return n
 
     def run_from_host(self, host):

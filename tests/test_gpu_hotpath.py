@@ -69,25 +69,25 @@ def test_hot_path_step_matches_oracle(cuda, oracle, name, over):
         assert torch.equal(step.graph_last["heads"]["losses"][k], h["losses"][k])
 
 
-@pytest.mark.parametrize("depth", [2, 3])
-def test_streamed_steps_deliver_every_steps_results_in_order(cuda, depth):
+@pytest.mark.parametrize("depth,overlap", [(2, "any"), (3, "any"), (3, "after_forward")])
+def test_streamed_steps_deliver_every_steps_results_in_order(cuda, depth, overlap):
     """HotPathStep.run_stream (what bench.py's e2e times): distinct host batches streamed through the captured
     graphs; every step's losses / pseudo-labels arrive, in order, and equal the un-pipelined path's -- including the image-level
     labels, which travel with the batch (device-side class lists), not with the captured graph."""
     from jtsm_b200 import hotpath
 
-    wls = [synth.step_case("c2", sweep_index=i, C=4, R=200) for i in range(5)]
+    wls = [synth.step_case("c2", sweep_index=i, C=4, R=200) for i in range(7)]
     for w in wls[1:]:  # the upstream gradient (fc6's backward) is device-resident state of the step, not a host input
         w["grad_tile"] = wls[0]["grad_tile"]
     step = hotpath.HotPathStep(wls[0]["cfg"], cuda)
     hosts = [step.pin_host_inputs(w) for w in wls]
     want0 = [[t.clone() for t in step.run_from_host(h)] for h in hosts]
     assert any(not torch.equal(want0[0][2], w[2]) for w in want0[1:])  # the batches really differ (labels too)
-    step.prepare_stream(hosts[0], depth=depth)
+    step.prepare_stream(hosts[0], depth=depth, overlap=overlap)
     got = {}
     n = step.run_stream(hosts, consume=lambda i, out: got.__setitem__(i, [t.clone() for t in out]))
-    assert n == 5 and sorted(got) == list(range(5))
-    for i in range(5):
+    assert n == 7 and sorted(got) == list(range(7))
+    for i in range(7):
         for a, b in zip(got[i], want0[i]):
             if a.dtype.is_floating_point:
                 np.testing.assert_allclose(a.numpy(), b.numpy(), rtol=1e-5, atol=1e-5 * max(1.0, float(b.abs().max())))
