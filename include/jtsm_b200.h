@@ -15,6 +15,13 @@
  *     (JTSM_F32 / JTSM_BF16 / JTSM_F16); boxes, scores, losses are fp32;
  *     labels / indices are int64 where the reference exposes int64
  *     (gt_classes, keep indices) and int32 for argmax (reference: at::kInt).
+ *   - RoI dtype rule: `rois` is ALWAYS fp32 at this boundary, whatever `dtype` the features have, and the
+ *     kernels use the coordinate values as passed.  The reference's ROIAlign module rounds the coordinates
+ *     through the feature dtype before its op sees them (`rois.to(dtype=input.dtype)`,
+ *     detectron2/layers/roi_align.py:108); a binding that wants that behaviour does the same cast on its
+ *     side and widens the result back to fp32 (exact) -- jtsm_b200/layers/roi_align.py does.
+ *   - class-column limits: the MIL / refinement kernels hold a row's class columns in registers and
+ *     support num_classes <= 256 (JTSM_ERR_INVALID_ARGUMENT above that).
  *
  * Each function cites the reference interface it replaces; paths are relative
  * to the reference checkout (shenyunhang/JTSM).

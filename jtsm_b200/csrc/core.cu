@@ -1,9 +1,6 @@
 // Library-wide state: ABI version, error strings, launch counter, tuning knobs.
 #include <string.h>
 
-#include <map>
-#include <mutex>
-#include <string>
 
 #include "common.cuh"
 
@@ -12,45 +9,60 @@ namespace jtsm {
 std::atomic<unsigned long long> g_launch_count{0};
 
 namespace {
-std::mutex g_tuning_mu;
-std::map<std::string, int>& tuning_map() {
-  static std::map<std::string, int> m = {
-      {"roi_pool_splits", 0},      // 0 = auto
-      {"roi_pool_force_gmem", 0},  // 1 = skip the smem-plane kernel
-      {"roi_pool_bwd_algo", 0},    // 0 = auto
-      {"roi_pool_fwd_algo", 0},    // 0 = auto, 1 = direct smem scan, 2 = gmem scan, 3 = range-max tables
-      {"roi_pool_fwd_async", 1},   // 1 = fetch the next plane with cp.async when a second plane buffer fits
-      {"roi_align_bwd_algo", 0},   // 0 = auto (separable: column kernel for PH <= 16, else cell kernel), 1 = one RED per tap, 2 = cell kernel
-      {"roi_align_fwd_algo", 0},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
-      {"roi_align_force_gmem", 0},
-      {"roi_align_fwd_pairs", 1},  // 1 = staged plane as (x, x+1) pairs: one 8-byte shared load per row of a sample
-      {"moi_rmq", 60},             // MOIPool: fully switched-on bins go to the RoIPool range-max kernel when <= this % of the bins are partially masked (device-side gate); -1 = off
-      {"loop_algo", 0},            // ROILoopPool forward: 0 = auto (virtual RoIs: range-max + visit lists), 1 = direct scans
-      {"moi_planes", 2},           // channels per CTA of the MOIPool visit-list kernel (1 or 2)
-      {"moi_algo", 0},             // MOIPool forward: 0 = auto (per-bin visit lists), 1 = row bit masks, 2 = byte-mask scan
-  };
-  return m;
+// Tuning knobs: a fixed table of atomics (no lock, no allocation on the launch path); a launcher resolves a key by
+// comparing at most kNumKnobs short strings, and the hot launchers cache the slot index in a function-local static.
+struct Knob {
+  const char* key;
+  std::atomic<int> value;
+};
+Knob g_knobs[] = {
+    {"roi_pool_splits", {0}},      // 0 = auto
+    {"roi_pool_force_gmem", {0}},  // 1 = skip the smem-plane kernel
+    {"roi_pool_bwd_algo", {0}},    // 0 = auto (vec4 + register folding), 1 = one RED per element, 2 = vec4 + warp match folding
+    {"roi_pool_fwd_algo", {0}},    // 0 = auto, 1 = direct smem scan, 2 = gmem scan, 3 = range-max tables
+    {"roi_pool_fwd_keys", {0}},    // range-max tables: 0 = absolute indices, 8 look-ups per bin (default); 1 = (key10 | rel6) entries, 5 look-ups, ALU bound
+    {"roi_pool_fwd_tma", {1}},     // 1 = planes arrive by cp.async.bulk (TMA 1-D) + mbarrier into a staging buffer; 0 = plain loads
+    {"roi_align_bwd_algo", {0}},   // 0 = auto (separable: column kernel for PH <= 16, else cell kernel), 1 = one RED per tap, 2 = cell kernel
+    {"roi_align_fwd_algo", {0}},   // 0 = auto (tap tables), 1 = coordinates recomputed per sample
+    {"roi_align_force_gmem", {0}},
+    {"roi_align_fwd_pairs", {1}},  // 1 = staged plane as (x, x+1) pairs: one 8-byte shared load per row of a sample
+    {"moi_rmq", {60}},             // MOIPool: fully switched-on bins go to the RoIPool range-max kernel when <= this % of the bins are partially masked (device-side gate); -1 = off
+    {"loop_algo", {0}},            // ROILoopPool forward: 0 = auto (virtual RoIs: range-max + visit lists), 1 = direct scans
+    {"moi_planes", {2}},           // channels per CTA of the MOIPool visit-list kernel (1 or 2)
+    {"moi_algo", {0}},             // MOIPool forward: 0 = auto (per-bin visit lists), 1 = row bit masks, 2 = byte-mask scan
+    {"nms_algo", {0}},             // 0 = auto (cluster of CTAs per class when classes are few), 1 = one CTA per class
+    {"infer_filter_algo", {0}},    // reserved
+};
+constexpr int kNumKnobs = (int)(sizeof(g_knobs) / sizeof(g_knobs[0]));
+Knob* find_knob(const char* key) {
+  for (int i = 0; i < kNumKnobs; ++i)
+    if (strcmp(g_knobs[i].key, key) == 0) return &g_knobs[i];
+  return nullptr;
 }
 }  // namespace
 
-int tuning(const char* key, int dflt) {
-  std::lock_guard<std::mutex> lk(g_tuning_mu);
-  auto& m = tuning_map();
-  auto it = m.find(key);
-  return it == m.end() ? dflt : it->second;
+std::atomic<int>* find_knob_public(const char* key) {
+  Knob* k = find_knob(key);
+  return k ? &k->value : nullptr;
 }
 
+int tuning(const char* key, int dflt) {
+  const Knob* k = find_knob(key);
+  return k ? k->value.load(std::memory_order_relaxed) : dflt;
+}
+
+// SM count of the CURRENT device (cached per device ordinal: one process may drive several GPUs).
 int num_sms() {
-  static int cached = 0;
-  if (cached == 0) {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-      cached = n;
-    else
-      cached = kNumSMs;
+  constexpr int kMaxDev = 64;
+  static std::atomic<int> cached[kMaxDev];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) return kNumSMs;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = kNumSMs;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached;
+  return n;
 }
 
 }  // namespace jtsm
@@ -75,20 +87,16 @@ extern "C" unsigned long long jtsm_launch_count(void) {
 
 extern "C" int jtsm_set_tuning(const char* key, int value) {
   if (!key) return JTSM_ERR_INVALID_ARGUMENT;
-  std::lock_guard<std::mutex> lk(jtsm::g_tuning_mu);
-  auto& m = jtsm::tuning_map();
-  auto it = m.find(key);
-  if (it == m.end()) return JTSM_ERR_INVALID_ARGUMENT;
-  it->second = value;
+  auto* k = jtsm::find_knob_public(key);
+  if (!k) return JTSM_ERR_INVALID_ARGUMENT;
+  k->store(value, std::memory_order_relaxed);
   return JTSM_OK;
 }
 
 extern "C" int jtsm_get_tuning(const char* key, int* value) {
   if (!key || !value) return JTSM_ERR_INVALID_ARGUMENT;
-  std::lock_guard<std::mutex> lk(jtsm::g_tuning_mu);
-  auto& m = jtsm::tuning_map();
-  auto it = m.find(key);
-  if (it == m.end()) return JTSM_ERR_INVALID_ARGUMENT;
-  *value = it->second;
+  auto* k = jtsm::find_knob_public(key);
+  if (!k) return JTSM_ERR_INVALID_ARGUMENT;
+  *value = k->load(std::memory_order_relaxed);
   return JTSM_OK;
 }

@@ -245,7 +245,7 @@ extern "C" int jtsm_batched_nms(const float* boxes, const float* scores, const l
   nms_segments_kernel<<<gb, tb, 0, st>>>(boxes, w.order1, w.order2, w.cls_b, n, w.sboxes, w.seg_start,
                                          w.num_seg);
   // CTAs stride over segments; the segment count is only known on the device.
-  const int max_seg = n < 2 * kNumSMs ? n : 2 * kNumSMs;
+  const int max_seg = n < 2 * num_sms() ? n : 2 * num_sms();
   const size_t smem = ((size_t)n / 32 + 2) * 4;
   if (smem > 160 * 1024) return JTSM_ERR_UNSUPPORTED;
   if (smem > 40 * 1024)

@@ -791,6 +791,8 @@ extern "C" int jtsm_roi_align_backward(const void* grad_output, long long stride
                                                 channels, height, width, pooled_h, pooled_w, ws, acc);
       });
     } else {
+      const long long pp_ll = (long long)pooled_h * pooled_w;
+      if ((long long)channels * pp_ll * pp_ll >= 0xFFFFFFFFLL) return JTSM_ERR_UNSUPPORTED;  // exact magic division
       const int cpp = channels * pooled_h * pooled_w;
       int ysplit = (cpp + 255) / 256;
       const int want = (4 * num_sms() * 8 + num_rois - 1) / num_rois;
@@ -806,10 +808,10 @@ extern "C" int jtsm_roi_align_backward(const void* grad_output, long long stride
     if (rc != JTSM_OK) return rc;
   }
   if (dtype == JTSM_BF16) {
-    align_convert_from_f32_kernel<__nv_bfloat16><<<kNumSMs * 8, 256, 0, st>>>(acc, (__nv_bfloat16*)grad_input, n_in);
+    align_convert_from_f32_kernel<__nv_bfloat16><<<num_sms() * 8, 256, 0, st>>>(acc, (__nv_bfloat16*)grad_input, n_in);
     count_launch();
   } else if (dtype == JTSM_F16) {
-    align_convert_from_f32_kernel<__half><<<kNumSMs * 8, 256, 0, st>>>(acc, (__half*)grad_input, n_in);
+    align_convert_from_f32_kernel<__half><<<num_sms() * 8, 256, 0, st>>>(acc, (__half*)grad_input, n_in);
     count_launch();
   }
   return cuda_status();
@@ -861,7 +863,8 @@ extern "C" int jtsm_roi_align_backward_det(const void* grad_output, long long st
   if (!grad_input || !workspace) return JTSM_ERR_INVALID_ARGUMENT;
   const long long cells_ll = (long long)batch * height * width;
   const DetLayout L = det_layout(batch, channels, height, width, num_rois, pooled_h, pooled_w, sampling_ratio);
-  if (cells_ll >= 0x7FFFFFFFLL || L.taps >= 0x7FFFFFFFULL || (long long)num_rois * pooled_h * pooled_w >= 0x7FFFFFFFLL)
+  if (cells_ll >= 0x7FFFFFFFLL || L.taps >= 0x7FFFFFFFULL || (long long)num_rois * pooled_h * pooled_w >= 0x7FFFFFFFLL ||
+      (long long)num_rois * pooled_h * pooled_w * pooled_h * pooled_w >= 0xFFFFFFFFLL)  // exact magic division by PH*PW
     return JTSM_ERR_UNSUPPORTED;
   if (workspace_bytes < L.total) return JTSM_ERR_WORKSPACE_TOO_SMALL;
   if (num_rois > 0 && channels > 0 && (!grad_output || !rois)) return JTSM_ERR_INVALID_ARGUMENT;

@@ -61,6 +61,7 @@ struct PoolWorkspace {
 //   bits  0..17  base = 2 * (hs*W + ws + slot*hw)        (plane + tables <= 227 KB -> < 2^18)
 //   bits 18..21  hl - hs   (dh = 2 * W * that)
 //   bits 22..26  db = 2 * (wl - ws)
+//   bits 27..30  table slot kh + 2*kw (the keyed kernel recovers the window's cell position from base and slot)
 //   bit  31      fast path; 0 = empty bin or a shape the stored levels do not cover with 2 x 2
 //                windows (the kernel then re-derives the ranges from hbins / wbins)
 __device__ __forceinline__ bool rmq_axis(uint32_t packed, int& s, int& last, int& q) {
@@ -76,7 +77,7 @@ __device__ __forceinline__ uint32_t rmq_bin_desc(uint32_t hb, uint32_t wb, int W
   const bool okh = rmq_axis(hb, hs, hl, qh), okw = rmq_axis(wb, wst, wl, qw);
   if (!(okh && okw && abs(qh - qw) <= 1)) return 0u;
   return 0x80000000u | (2u * (uint32_t)(hs * W + wst + (qh + 2 * qw) * hw)) | ((uint32_t)(hl - hs) << 18) |
-         ((2u * (uint32_t)(wl - wst)) << 22);
+         ((2u * (uint32_t)(wl - wst)) << 22) | ((uint32_t)(qh + 2 * qw) << 27);
 }
 
 inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w, int sets) {

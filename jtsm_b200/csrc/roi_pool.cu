@@ -17,6 +17,7 @@
 //     warp writes contiguous 4*P*P-byte runs of the [R, C, P, P] output.
 #include "roi_bins.cuh"
 #include "roi_pool_rmq.cuh"
+#include "roi_pool_rmqk.cuh"
 
 namespace jtsm {
 
@@ -318,10 +319,11 @@ constexpr size_t kMaxPlaneSmem = 200 * 1024;
 // keeps every descriptor field inside its bits), the batch index fits 11 bits and output offsets 32 bits.
 bool rmq_geometry_ok(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
   const long long hw = (long long)height * width;
-  return hw < 65535 && rmq_smem_bytes((int)hw) <= 227 * 1024 &&
+  return hw < 65535 && rmq_smem_bytes((int)hw) <= 227 * 1024 && rk_smem_core((int)hw) <= 227 * 1024 &&
          (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL &&
          (long long)num_rois * PH * PW * PH * PW < 0xFFFFFFFFLL &&  // exact magic division of a bin id by PH*PW
-         (long long)num_rois * 64 < 0x7FFFFFFFLL;                  // chunk bounds in 32 bits (chunks <= 64)
+         (long long)num_rois * 64 < 0x7FFFFFFFLL &&                // chunk bounds in 32 bits (chunks <= 64)
+         (long long)batch * channels * hw * 4 < 0xFFFFFFF0LL;      // plane byte offsets in 32 bits
 }
 bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
   const int algo = tuning("roi_pool_fwd_algo", 0);  // 0 auto, 1 direct smem scan, 2 gmem scan, 3 rmq
@@ -329,14 +331,11 @@ bool rmq_eligible(int batch, int channels, int height, int width, int num_rois, 
          rmq_geometry_ok(batch, channels, height, width, num_rois, PH, PW);
 }
 
-template <typename T> constexpr bool dtype_is_f32() { return false; }
-template <> constexpr bool dtype_is_f32<float>() { return true; }
-
 int pick_splits(int planes, int num_rois, int ctas_per_sm) {
   // enough CTAs for ~4 waves, but keep >= 64 RoIs per CTA so the plane load amortises
   const int forced = tuning("roi_pool_splits", 0);
   if (forced > 0) return forced;
-  const long long target = 4LL * kNumSMs * ctas_per_sm;
+  const long long target = 4LL * num_sms() * ctas_per_sm;
   long long s = (target + planes - 1) / planes;
   const long long cap = num_rois / 64 > 1 ? num_rois / 64 : 1;
   if (s > cap) s = cap;
@@ -350,18 +349,19 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
                const PoolWorkspace& ws, const MoiAux& moi, void* output, void* argmax, cudaStream_t st) {
   const int planes = batch * channels;
   const int hw = height * width;
-  const size_t rmq_smem = rmq_smem_bytes(hw);
   {
-    // a second plane buffer (fp32 inputs) lets the next plane stream in behind the queries of the current one
-    const int two_planes = dtype_is_f32<T>() && rmq_smem + (size_t)hw * 4 <= 227 * 1024 &&
-                           tuning("roi_pool_fwd_async", 1);
-    const size_t smem = rmq_smem + (two_planes ? (size_t)hw * 4 : 0);
-    static bool rmq_attr = false;
-    if (!rmq_attr) {
-      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A, kMoi>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           227 * 1024);
-      rmq_attr = true;
-    }
+    // table format: index tables (8 look-ups per bin, LSU bound) by default; keyed entries (5 look-ups, ALU bound and
+    // slower on B200: profiles/r2_roi_pool_fwd_keyed.md) on request.  Planes arrive by bulk copy (TMA 1-D) into a raw
+    // staging buffer when one fits next to plane + tables.
+    const bool keyed = tuning("roi_pool_fwd_keys", 0) != 0;
+    const size_t stage = rk_stage_bytes(hw, (int)sizeof(T));
+    const int staged = rk_smem_core(hw) + stage <= 227 * 1024 && tuning("roi_pool_fwd_tma", 1);
+    const size_t smem = rk_smem_core(hw) + (staged ? stage : 0);
+    // per call: the attribute is per device, and one process may drive several GPUs
+    if (keyed)
+      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A, kMoi, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    else
+      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A, kMoi, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     const int per_sm = (int)((227 * 1024) / (smem + 1024)) >= 2 ? 2 : 1;  // 1024-thread CTAs
     const int max_grid = num_sms() * per_sm;
     // RoI chunks per plane: the planes of the last, partial round (planes % grid) are cut into chunks and dealt to
@@ -381,9 +381,15 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
     if (chunks > 64) chunks = 64;
     const int items = planes * chunks;
     const int grid = items < max_grid ? items : max_grid;
-    roi_pool_fwd_rmq_kernel<T, A, kMoi><<<grid, kRmqThreads, smem, st>>>(
-        (const T*)input, channels, height, width, PH, PW, chunks, items, two_planes, ws, moi, (T*)output,
-        (A*)argmax);
+    const unsigned long long in_bytes = (unsigned long long)planes * hw * sizeof(T);
+    if (keyed)
+      roi_pool_fwd_rmq_kernel<T, A, kMoi, true><<<grid, kRmqThreads, smem, st>>>(
+          (const T*)input, in_bytes, channels, height, width, PH, PW, chunks, items, staged, ws, moi, (T*)output,
+          (A*)argmax);
+    else
+      roi_pool_fwd_rmq_kernel<T, A, kMoi, false><<<grid, kRmqThreads, smem, st>>>(
+          (const T*)input, in_bytes, channels, height, width, PH, PW, chunks, items, staged, ws, moi, (T*)output,
+          (A*)argmax);
     count_launch();
     return cuda_status();
   }
@@ -394,7 +400,6 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
                         int num_rois, int PH, int PW, const PoolWorkspace& ws,
                         const float* row_scale, void* output, void* argmax, cudaStream_t st) {
   const int planes = batch * channels;
-  const int hw = height * width;
   const int algo = tuning("roi_pool_fwd_algo", 0);
   if (rmq_eligible(batch, channels, height, width, num_rois, PH, PW))
     return launch_rmq<T, A, false>(input, batch, channels, height, width, num_rois, PH, PW, ws, MoiAux{}, output,
@@ -403,11 +408,7 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
   const size_t smem = (size_t)height * pitch * sizeof(float);
   if (smem <= kMaxPlaneSmem && algo != 2 && !tuning("roi_pool_force_gmem", 0)) {
     auto k = roi_pool_fwd_kernel<T, A, kFwdThreads>;
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxPlaneSmem);
-      attr_set = true;
-    }
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxPlaneSmem);  // per device
     int per_sm = (int)((227 * 1024) / (smem + 1024));
     per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
     const int splits = pick_splits(planes, num_rois, per_sm);
@@ -525,7 +526,8 @@ extern "C" int jtsm_roi_pool_backward(const void* grad_output, long long stride_
     const int PP = pooled_h * pooled_w;
     const long long cpp = (long long)channels * PP;
     const bool contiguous = stride_w == 1 && stride_h == pooled_w && stride_c == PP && stride_n == cpp;
-    const bool vec_ok = contiguous && cpp % 4 == 0 && cpp < (1ll << 31) / 49 &&
+    const bool vec_ok = contiguous && cpp % 4 == 0 && cpp < (1ll << 31) && cpp * PP < (1ll << 32) &&  // exact magic division
+                        
                         (long long)channels * height * width < (1ll << 31) &&
                         ((uintptr_t)grad_output % 16 == 0) && ((uintptr_t)argmax % 16 == 0) &&
                         tuning("roi_pool_bwd_algo", 0) != 1;
@@ -542,7 +544,7 @@ extern "C" int jtsm_roi_pool_backward(const void* grad_output, long long stride_
                           }));
     } else {
       long long blocks = (total + 255) / 256;
-      const long long cap = (long long)kNumSMs * 8 * 4;
+      const long long cap = (long long)num_sms() * 8 * 4;
       if (blocks > cap) blocks = cap;
       JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
                             roi_pool_bwd_red_kernel<T, A><<<(int)blocks, 256, 0, st>>>(
@@ -556,10 +558,10 @@ extern "C" int jtsm_roi_pool_backward(const void* grad_output, long long stride_
     if (rc != JTSM_OK) return rc;
   }
   if (dtype == JTSM_BF16) {
-    convert_from_f32_kernel<__nv_bfloat16><<<kNumSMs * 8, 256, 0, st>>>(acc, (__nv_bfloat16*)grad_input, n_in);
+    convert_from_f32_kernel<__nv_bfloat16><<<num_sms() * 8, 256, 0, st>>>(acc, (__nv_bfloat16*)grad_input, n_in);
     count_launch();
   } else if (dtype == JTSM_F16) {
-    convert_from_f32_kernel<__half><<<kNumSMs * 8, 256, 0, st>>>(acc, (__half*)grad_input, n_in);
+    convert_from_f32_kernel<__half><<<num_sms() * 8, 256, 0, st>>>(acc, (__half*)grad_input, n_in);
     count_launch();
   }
   return cuda_status();

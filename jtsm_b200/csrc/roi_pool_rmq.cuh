@@ -20,11 +20,13 @@
 // kernel (roi_bins.cuh) and read with one coalesced load, one round ahead; the look-up chain of
 // the main loop is branch free and indexes only with 32-bit offsets from the kernel arguments.
 //
-// One persistent CTA per SM walks a contiguous range of (plane, RoI-chunk) items, rebuilding the
-// tables only when the plane changes (~3.5 builds per CTA at config 2); one thread per bin, lanes
-// along consecutive bins of a RoI.  The variants tried and dropped (thread per output row with
-// staged write-out, 16-byte per-bin descriptors, two bins per thread) and what each measured are
-// in profiles/r1f_roi_pool_fwd_experiments.md.
+// One persistent CTA per SM walks (plane, RoI-chunk) items, rebuilding the tables only when the plane
+// changes (~3.5 builds per CTA at config 2); one thread per bin, lanes along consecutive bins of a RoI.
+// The kernel frame (schedule, bulk-copy plane fetch, unpack, main loop, slow pass) is in
+// roi_pool_rmqk.cuh, shared with the keyed table format defined there; this file holds the index-table
+// format (build + queries) and what both formats share.  The variants tried and dropped (thread per
+// output row with staged write-out, 16-byte per-bin descriptors, keyed entries) and what each measured
+// are in profiles/r1f_roi_pool_fwd_experiments.md and profiles/r2_roi_pool_fwd_keyed.md.
 #pragma once
 #include "roi_bins.cuh"
 
@@ -108,19 +110,6 @@ __device__ __forceinline__ void rmq_build_tables(const float* plane, unsigned sh
 #undef TAB
 }
 
-// fp32 planes can be fetched asynchronously (4-byte cp.async per cell) into the spare plane buffer while the
-// queries of the current plane run.
-template <typename T> struct PlaneAsync { static constexpr bool ok = false; };
-template <> struct PlaneAsync<float> { static constexpr bool ok = true; };
-__device__ __forceinline__ void plane_prefetch_async(const float* __restrict__ src, float* dst, int hw) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
-  for (int p = threadIdx.x; p < hw; p += kRmqThreads)
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4u * p), "l"(src + p) : "memory");
-  asm volatile("cp.async.commit_group;" ::: "memory");
-}
-template <typename T>
-__device__ __forceinline__ void plane_prefetch_async(const T*, float*, int) {}
-
 // Slow path of one bin (empty, elongated or > 16-cell ranges) from the packed [start, end) ranges:
 // nearest stored level, as many windows as needed.  Empty bin -> value 0, index 0xFFFFFFFF.
 static __device__ __noinline__ RmqCand rmq_query_slow(const float* plane, const unsigned short* tabs, int hw, int W,
@@ -188,192 +177,6 @@ __device__ __forceinline__ RmqItem rmq_item(int nc, int chunk, int chunks, int c
     it.nr = first + (int)(len * (unsigned)(chunk + 1) / (unsigned)chunks) - it.r0;
   }
   return it;
-}
-
-// Main loop of one (plane, RoI-chunk) item: one fast bin per thread and round.  Everything is indexed with
-// 32-bit offsets from the kernel's own pointer arguments (the launcher checks the sizes): bin id i ->
-// RoI r = i / PP (magic multiply) -> output element i + r * (C - 1) * PP + c * PP.  Descriptor and row scale
-// are loaded one round ahead (they come from L2: little L1 is left next to 180+ KB of shared memory; deeper
-// rings of 2 and 4 rounds measured the same).  x = 0 marks a slow bin (left to the list)
-// or an inactive thread: the branch-free look-ups then run on offset 0, which is harmless.
-template <typename T, typename A, bool kUngrouped, bool kMoi>
-__device__ __forceinline__ void rmq_main_loop(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
-                                              const RmqItem& it, int PP, int cpp, unsigned w2, unsigned magic_pp,
-                                              const float* __restrict__ mask_scale, int zero_floor,
-                                              T* __restrict__ output, A* __restrict__ argmax) {
-  const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
-  const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
-  const unsigned plane_s = (unsigned)__cvta_generic_to_shared(plane);
-  const unsigned tabs_s = (unsigned)__cvta_generic_to_shared(tabs);
-  constexpr int K = kRmqBinsPerThread;
-  unsigned i = (unsigned)(it.r0 * PP) + threadIdx.x;
-  unsigned xn[K];
-  float scn[K], msn[K];
-  auto fetch = [&](unsigned i0) {
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const unsigned ik = i0 + k * kRmqThreads;
-      xn[k] = 0u, scn[k] = 0.f, msn[k] = 0.f;
-      if (ik < i_end) {
-        xn[k] = __ldg(ws.bdesc + ik);
-        scn[k] = __ldg(ws.rscale + __umulhi(ik, magic_pp));
-        if (kMoi) msn[k] = __ldg(mask_scale + __umulhi(ik, magic_pp));
-      }
-    }
-  };
-  fetch(i);
-  while (i < i_end) {
-    unsigned x[K], o[K];
-    float sc[K], ms[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      const unsigned ik = i + k * kRmqThreads;
-      x[k] = xn[k], sc[k] = scn[k], ms[k] = msn[k];
-      o[k] = ik + __umulhi(ik, magic_pp) * o_r + o_c;
-    }
-    i += K * kRmqThreads;
-    fetch(i);  // next round's descriptors and scales in flight during this round's look-ups
-    RmqCand best[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k)
-      best[k] = rmq_query_fast(plane_s, tabs_s + (x[k] & 0x3FFFFu), ((x[k] >> 18) & 15u) * w2, (x[k] >> 22) & 31u);
-#pragma unroll
-    for (int k = 0; k < K; ++k) {
-      bool act = (int)x[k] < 0;  // x >= 0: slow bin (left to the list) or past the end
-      if (kUngrouped && act) act = __ldg(ws.batch_idx + (o[k] - o_c) / (unsigned)cpp) == it.n;
-      if (act) {
-        const float v = kMoi ? __fmul_rn(best[k].v, ms[k]) : best[k].v;  // (f * mask_scale) * (objectness + 1)
-        if (kMoi && zero_floor && !(best[k].v > 0.f)) {
-          output[o[k]] = Elem<T>::from_f(0.f);
-          argmax[o[k]] = Arg<A>::enc(-1);
-        } else {
-          output[o[k]] = Elem<T>::from_f(__fmul_rn(v, sc[k]));
-          argmax[o[k]] = (A)best[k].i;  // a fast bin always has a cell
-        }
-      }
-    }
-  }
-}
-
-// The few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%) of RoIs [r_lo, r_hi) for the plane
-// whose tables are resident.  The prep kernel lists them, so no warp of the main loop diverges into the long
-// path; the list is short and every CTA filters it for the RoI range it has just served.
-template <typename T, typename A, bool kMoi>
-__device__ __forceinline__ void rmq_slow_pass(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
-                                              int n, int c, int r_lo, int r_hi, bool ungrouped, int channels, int hw,
-                                              int W, int PH, int PW, const MoiAux& moi, T* __restrict__ output,
-                                              A* __restrict__ argmax) {
-  const int PP = PH * PW;
-  if (kMoi) return;  // the visit-list kernel answers every bin without a fast descriptor
-  const int ns = __ldg(ws.slow_count);
-  for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
-    const int id = __ldg(ws.slow_list + j);
-    const int rr = id / PP, b = id - rr * PP;
-    if (rr < r_lo || rr >= r_hi) continue;
-    if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
-    const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
-    const int ph = b / PW, pw = b - ph * PW;
-    const RmqCand best = rmq_query_slow(plane, tabs, hw, W, __ldg(ws.hbins + (size_t)rr * PH + ph),
-                                        __ldg(ws.wbins + (size_t)rr * PW + pw));
-    output[so] = Elem<T>::from_f(__fmul_rn(best.v, __ldg(ws.rscale + rr)));
-    argmax[so] = Arg<A>::enc((int)best.i);
-  }
-}
-
-// dynamic smem: plane A (hw fp32) | 10 tables (hw uint16 each) | plane B (hw fp32, only when two_planes)
-template <typename T, typename A, bool kMoi = false>
-__global__ void __launch_bounds__(kRmqThreads, 1)
-roi_pool_fwd_rmq_kernel(const T* __restrict__ input, int channels, int H, int W, int PH, int PW,
-                        int chunks, int num_items, int two_planes, PoolWorkspace ws, MoiAux moi,
-                        T* __restrict__ output, A* __restrict__ argmax) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  if (kMoi && !moi_rmq_gate(moi.slow_total, moi.total_bins, moi.gate_pct)) return;  // uniform: the list kernel runs
-  const int hw = H * W;
-  float* plane = (float*)smem_raw;
-  unsigned short* tabs = (unsigned short*)(plane + hw);
-  float* spare = (float*)(tabs + (size_t)kRmqTables * hw);  // valid only when two_planes
-  const int PP = PH * PW, cpp = channels * PP;
-  const unsigned w2 = 2u * (unsigned)W;
-  const bool ungrouped = *ws.ungrouped != 0;
-  const unsigned magic_pp = (unsigned)((0x100000000ull + PP - 1) / PP);
-  const bool async = PlaneAsync<T>::ok && two_planes;
-
-  // Item schedule of this CTA.  Planes are dealt round-robin -- CTA k serves planes k, k + G, k + 2G, ... with all
-  // their RoI chunks -- so that at any moment neighbouring CTAs write neighbouring channels of the same RoIs: the
-  // 196-byte runs of channel c and c + 1 share a 32-byte sector, and its two halves now reach L2 within
-  // microseconds of each other instead of a plane's whole processing time apart (a half-written sector that is
-  // evicted costs a DRAM read-modify-write).  The planes left over after the full rounds are cut into chunks and
-  // spread over all CTAs as one contiguous range each.
-  const int G = gridDim.x, planes = num_items / chunks;
-  const int full = (planes / G) * chunks;               // items of the full rounds, per CTA
-  const int tail_items = (planes % G) * chunks;         // items of the last, partial round (all CTAs together)
-  const int tail_base = (planes / G) * G * chunks;      // id of its first item
-  const int t_per = tail_items / G, t_rem = tail_items % G;
-  const int t0 = blockIdx.x * t_per + min((int)blockIdx.x, t_rem);
-  const int my_items = full + t_per + ((int)blockIdx.x < t_rem ? 1 : 0);
-  // (plane, chunk) of this CTA's idx-th item, stepped without divisions
-  int nc = full > 0 ? (int)blockIdx.x : (tail_base + t0) / chunks;
-  int chunk = full > 0 ? 0 : (tail_base + t0) % chunks;
-  auto advance = [&](int idx_next, int& pl, int& ch) {  // (pl, ch) of item idx_next - 1 -> item idx_next
-    if (idx_next == full) {  // first item of the tail range
-      pl = (tail_base + t0) / chunks;
-      ch = (tail_base + t0) % chunks;
-    } else if (++ch == chunks) {
-      ch = 0;
-      pl += idx_next < full ? G : 1;
-    }
-  };
-  int cur_plane = -1, in_flight = -1;  // plane whose tables are resident / plane being fetched into `spare`
-  int r_lo = 0, r_hi = 0;              // RoIs served with the resident tables
-
-  for (int p = threadIdx.x; p < hw; p += kRmqThreads) tabs[p] = (unsigned short)p;  // identity level (0,0), slot 0
-
-  for (int idx = 0; idx < my_items; ++idx) {
-    if (idx > 0) advance(idx, nc, chunk);
-    const RmqItem it = rmq_item(nc, chunk, chunks, channels, ws);
-    if (nc != cur_plane) {
-      if (cur_plane >= 0)
-        rmq_slow_pass<T, A, kMoi>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
-                                  channels, hw, W, PH, PW, moi, output, argmax);
-      if (async && in_flight == nc) {
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        __syncthreads();  // everyone is done with the old plane and tables; the fetched plane is complete
-        float* t = plane;
-        plane = spare;
-        spare = t;
-      } else {
-        __syncthreads();
-        const T* src = input + (size_t)nc * hw;
-        for (int p = threadIdx.x; p < hw; p += kRmqThreads) plane[p] = Elem<T>::to_f(src[p]);
-        __syncthreads();
-      }
-      cur_plane = nc;
-      r_lo = it.r0, r_hi = it.r0;
-      rmq_build_tables(plane, tabs, hw, W);
-      // the next plane this CTA will serve, if any: fetch it behind the queries of this one
-      if (async) {
-        int j = idx + 1, pl = nc, ch = chunk;
-        while (j < my_items) {
-          advance(j, pl, ch);
-          if (pl != nc) break;
-          ++j;
-        }
-        if (j < my_items) {
-          in_flight = pl;
-          plane_prefetch_async(input + (size_t)in_flight * hw, spare, hw);
-        }
-      }
-    }
-    if (it.nr > 0) r_hi = it.r0 + it.nr;  // chunks of a plane are consecutive RoI ranges
-    if (ungrouped)
-      rmq_main_loop<T, A, true, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, moi.zero_floor, output, argmax);
-    else
-      rmq_main_loop<T, A, false, kMoi>(plane, tabs, ws, it, PP, cpp, w2, magic_pp, moi.mask_scale, moi.zero_floor, output, argmax);
-  }
-  if (cur_plane >= 0)
-    rmq_slow_pass<T, A, kMoi>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
-                              channels, hw, W, PH, PW, moi, output, argmax);
-  asm volatile("cp.async.wait_all;" ::: "memory");
 }
 
 }  // namespace jtsm

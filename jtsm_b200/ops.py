@@ -44,9 +44,17 @@ def _workspace(nbytes, device):
 
 
 def _rois_f32(rois):
-    # The reference casts rois to the feature dtype (roi_align.py:108); coordinates are
-    # kept in fp32 here so bin edges do not depend on the feature precision.
-    return rois.detach().to(torch.float32).contiguous()
+    """RoI dtype rule (one rule for every pooling op, stated in include/jtsm_b200.h): the kernels read box
+    coordinates as fp32 and an op uses the VALUES the caller passes, widened losslessly (bf16 / fp16 -> fp32 is exact).
+    The reference's `ROIAlign` MODULE rounds the coordinates through the feature dtype first
+    (`rois.to(dtype=input.dtype)`, detectron2/layers/roi_align.py:108) before its op sees them; layers/roi_align.py does
+    the same cast, so module == reference module and op == reference op on the same tensors."""
+    return _aligned16(rois.detach().to(torch.float32).contiguous())
+
+
+def _aligned16(t):
+    """Kernels read boxes / RoI rows with 128-bit loads: a contiguous view at an odd storage offset is cloned."""
+    return t.clone() if t.numel() and t.data_ptr() % 16 else t
 
 
 # --------------------------------------------------------------------------- RoIPool
@@ -133,7 +141,7 @@ def segment_offsets(counts, device):
 
 
 def _f32c(t):
-    return t.detach().to(torch.float32).contiguous()
+    return _aligned16(t.detach().to(torch.float32).contiguous())
 
 
 # --------------------------------------------------------------------------- WSDDN MIL head
@@ -167,8 +175,10 @@ def wsddn_forward(cls_logits, det_logits, num_preds_per_image, labels_onehot=Non
                 cls=C, det=D, n=n)
 
 
-def wsddn_backward(fwd, grad_scores=None, grad_loss=None, use_loss=True):
-    """-> (grad_cls, grad_det) for the state returned by wsddn_forward."""
+def wsddn_backward(fwd, grad_scores=None, grad_loss=None, use_loss=True, grad_img=None):
+    """-> (grad_cls, grad_det) for the state returned by wsddn_forward.  Upstream gradient per element:
+    grad_scores[r,k] + gi[n(r),k] * grad_loss, with gi = `grad_img` when given (d / d unclamped image sum, e.g. from
+    autograd), else the BCE gradient the forward saved (use_loss)."""
     C, D = fwd["cls"], fwd["det"]
     r, k = C.shape
     dC, dD = torch.empty_like(C), torch.empty_like(D)
@@ -178,7 +188,7 @@ def wsddn_backward(fwd, grad_scores=None, grad_loss=None, use_loss=True):
         grad_scores = _f32c(grad_scores)
     if grad_loss is not None:
         grad_loss = _f32c(grad_loss).reshape(1)
-    gi = fwd["grad_img"] if use_loss else None
+    gi = _f32c(grad_img) if grad_img is not None else (fwd.get("grad_img") if use_loss else None)
     with torch.cuda.device(C.device):
         check(lib().jtsm_wsddn_backward(_ptr(C), _ptr(D), _ptr(fwd["scores"]), _ptr(fwd["col_stats"]), _ptr(fwd["seg"]),
                                         fwd["n"], r, k, _ptr(grad_scores), _ptr(gi), _ptr(grad_loss), _ptr(dC), _ptr(dD),
