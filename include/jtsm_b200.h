@@ -49,6 +49,7 @@ enum {
   JTSM_ERR_INVALID_ARGUMENT = 1,
   JTSM_ERR_UNSUPPORTED = 2,
   JTSM_ERR_WORKSPACE_TOO_SMALL = 3,
+  JTSM_ERR_STATIC_LIMIT = 4, /* size beyond the fixed maximum of an allocation-free (*_static) entry point */
   JTSM_ERR_CUDA_BASE = 1000 /* + cudaError_t */
 };
 
@@ -266,6 +267,22 @@ JTSM_API int jtsm_refine_ce(const float* logits, int num_rois, int num_cols,
                             const int* valid_count, const float* grad_loss, float loss_scale,
                             float* probs, float* grad_logits, float* loss, int* acc_counters,
                             void* workspace, size_t workspace_bytes, void* stream);
+/* Allocation-free variant of jtsm_refine_ce.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same arguments and results as jtsm_refine_ce without the workspace: the
+ * kernel's scratch (grid-sum ticket + per-CTA loss partials) is a file-scope `static __device__` array of 8 KB
+ * that every GPU loading the library holds until exit.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * Limit: num_rois <= JTSM_REFINE_CE_STATIC_MAX_ROIS (also returned by jtsm_refine_ce_static_max_rois());
+ * larger -> JTSM_ERR_STATIC_LIMIT ("size exceeds the static scratch limit").  All calls on one device share the
+ * array and it keeps the last call's contents (the call clears what must start at zero): stream-ordered calls are
+ * safe, calls that OVERLAP on the GPU (different streams) race -- serialise them. */
+#define JTSM_REFINE_CE_STATIC_MAX_ROIS 262144
+JTSM_API int jtsm_refine_ce_static_max_rois(void);
+JTSM_API int jtsm_refine_ce_static(const float* logits, int num_rois, int num_cols,
+                                   const long long* gt_classes, const float* loss_weights,
+                                   const int* valid_count, const float* grad_loss, float loss_scale,
+                                   float* probs, float* grad_logits, float* loss, int* acc_counters,
+                                   void* stream);
 /* out = (accumulate ? out : 0) + scale * softmax(logits, dim=1)   (predict_probs_K, fast_rcnn_oicr.py:764-783) */
 JTSM_API int jtsm_softmax_rows(const float* logits, int num_rois, int num_cols, float scale,
                                int accumulate, float* out, void* stream);

@@ -75,6 +75,7 @@ extern "C" const char* jtsm_error_string(int code) {
     case JTSM_ERR_INVALID_ARGUMENT: return "invalid argument";
     case JTSM_ERR_UNSUPPORTED: return "unsupported configuration";
     case JTSM_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+    case JTSM_ERR_STATIC_LIMIT: return "size exceeds the static scratch limit of this allocation-free entry point";
     default: break;
   }
   if (code >= JTSM_ERR_CUDA_BASE) return cudaGetErrorString((cudaError_t)(code - JTSM_ERR_CUDA_BASE));

@@ -690,3 +690,65 @@ extern "C" int jtsm_pairwise_iou(const float* boxes1, int n1, const float* boxes
   count_launch();
   return cuda_status();
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of jtsm_refine_ce (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA-graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  The kernel's scratch -- the grid-sum ticket and the per-CTA loss partials -- lives in a file-scope
+// device array instead of a caller-provided workspace.  Every GPU that loads the library holds the 8 KB until exit.
+// All calls on a device share the array: calls that overlap on the GPU (different streams) race; stream-ordered
+// calls are safe (the ticket is cleared at the start of every call, the partials are overwritten before they are read).
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr size_t kStaticScratchBytes = 8192;  // 16 (ticket) + kMaxSumCtas * 4 (partials) = 4752, rounded up
+static_assert(16 + (size_t)kMaxSumCtas * 4 <= kStaticScratchBytes, "static scratch too small for the grid-sum");
+static __device__ __align__(256) unsigned char g_refine_ce_scratch[kStaticScratchBytes];
+
+// In host code `g_refine_ce_scratch` is a host-side stand-in, not a device address: the device address is looked up
+// once per device (with that device current) and cached by device ordinal.
+int static_scratch_ptr(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::atomic<void*> cached[kMaxDev];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return JTSM_ERR_CUDA_BASE + (int)e;
+  if (dev < 0 || dev >= kMaxDev) return JTSM_ERR_UNSUPPORTED;
+  void* p = cached[dev].load(std::memory_order_acquire);
+  if (!p) {
+    e = cudaGetSymbolAddress(&p, g_refine_ce_scratch);
+    if (e != cudaSuccess || !p) return JTSM_ERR_CUDA_BASE + (int)(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+    cached[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return JTSM_OK;
+}
+}  // namespace
+
+extern "C" int jtsm_refine_ce_static_max_rois(void) { return JTSM_REFINE_CE_STATIC_MAX_ROIS; }
+
+extern "C" int jtsm_refine_ce_static(const float* logits, int num_rois, int num_cols, const long long* gt_classes,
+                                     const float* loss_weights, const int* valid_count, const float* grad_loss,
+                                     float loss_scale, float* probs, float* grad_logits, float* loss,
+                                     int* acc_counters, void* stream) {
+  if (num_rois < 0 || num_cols <= 0 || num_cols > 256) return JTSM_ERR_INVALID_ARGUMENT;
+  if (num_rois > JTSM_REFINE_CE_STATIC_MAX_ROIS) return JTSM_ERR_STATIC_LIMIT;  // beyond the stated maximum
+  if (!loss || !valid_count) return JTSM_ERR_INVALID_ARGUMENT;
+  if (num_rois > 0 && (!logits || !gt_classes || !loss_weights)) return JTSM_ERR_INVALID_ARGUMENT;
+  void* scratch = nullptr;
+  const int rc = static_scratch_ptr(&scratch);
+  if (rc != JTSM_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned int* ticket = (unsigned int*)scratch;
+  float* partials = (float*)((char*)scratch + 16);
+  cudaMemsetAsync(ticket, 0, 4, st);  // the array keeps the last call's contents: the ticket must start at zero
+  if (acc_counters) cudaMemsetAsync(acc_counters, 0, 4 * sizeof(int), st);
+  int grid = (num_rois + 7) / 8;
+  grid = grid < 1 ? 1 : (grid > kMaxSumCtas ? kMaxSumCtas : grid);
+  JTSM_DISPATCH_KT(num_cols, KT, {
+    refine_ce_kernel<KT><<<grid, 256, 0, st>>>(logits, num_cols, gt_classes, loss_weights, valid_count, grad_loss,
+                                                num_rois, loss_scale, probs, grad_logits, loss, acc_counters, partials,
+                                                ticket);
+  });
+  count_launch();
+  return cuda_status();
+}
