@@ -9,7 +9,7 @@
 // torchvision's GPU path builds an n x n/64 bitmask, copies it to the host and scans it on the
 // CPU.  Here: two stable radix sorts give (a) the global descending-score order and (b) the
 // per-class segments in that order; one CTA per class then runs greedy NMS over its segment in
-// 64-box blocks (intra-block resolve by one thread on a 64x64 bitmask, kept boxes of the block
+// 64-box blocks (intra-block resolve by one warp on a 64x64 bitmask, kept boxes of the block
 // suppress the tail in parallel); a flagged select emits the keep list.  No host sync.
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
@@ -27,21 +27,27 @@ __device__ __forceinline__ unsigned int desc_key(float s) {
   return ~u;
 }
 
-__global__ void nms_keys_kernel(const float* __restrict__ scores, int n, unsigned int* __restrict__ keys,
-                                int* __restrict__ vals) {
+constexpr unsigned int kPadKey = 0xFFFFFFFFu;  // padding entries (index >= *num_valid): last in score order, own class
+
+__global__ void nms_keys_kernel(const float* __restrict__ scores, int n, const int* __restrict__ num_valid,
+                                unsigned int* __restrict__ keys, int* __restrict__ vals) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
-    keys[i] = desc_key(scores[i]);
+    const int nv = num_valid ? min(*num_valid, n) : n;
+    keys[i] = i < nv ? desc_key(scores[i]) : kPadKey;
     vals[i] = i;
   }
 }
 
 // cls1[pos] = class of the pos-th best box; pos1[pos] = pos
 __global__ void nms_gather_class_kernel(const long long* __restrict__ idxs, const int* __restrict__ order1,
-                                        int n, unsigned int* __restrict__ cls1, int* __restrict__ pos1) {
+                                        int n, const int* __restrict__ num_valid, unsigned int* __restrict__ cls1,
+                                        int* __restrict__ pos1) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) {
-    cls1[i] = idxs ? (unsigned int)idxs[order1[i]] : 0u;
+    const int nv = num_valid ? min(*num_valid, n) : n;
+    const int src = order1[i];
+    cls1[i] = src >= nv ? kPadKey : (idxs ? (unsigned int)idxs[src] : 0u);
     pos1[i] = i;
   }
 }
@@ -50,11 +56,22 @@ __global__ void nms_gather_class_kernel(const long long* __restrict__ idxs, cons
 __global__ void nms_segments_kernel(const float* __restrict__ boxes, const int* __restrict__ order1,
                                     const int* __restrict__ order2, const unsigned int* __restrict__ cls2,
                                     int n, float4* __restrict__ sboxes, int* __restrict__ seg_start,
-                                    int* __restrict__ num_seg) {
+                                    int* __restrict__ seg_end, int* __restrict__ num_seg) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= n) return;
+  const unsigned int c = cls2[q];
+  if (c == kPadKey) return;  // padding: no box, no segment
   sboxes[q] = *(const float4*)(boxes + (size_t)order1[order2[q]] * 4);
-  if (q == 0 || cls2[q] != cls2[q - 1]) seg_start[atomicAdd(num_seg, 1)] = q;
+  if (q == 0 || c != cls2[q - 1]) {
+    int lo = q + 1, hi = n;  // first position after q whose class differs (classes are sorted)
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (cls2[mid] == c) lo = mid + 1; else hi = mid;
+    }
+    const int slot = atomicAdd(num_seg, 1);
+    seg_start[slot] = q;
+    seg_end[slot] = lo;
+  }
 }
 
 // torchvision nms IoU test (CPU kernel op order): inter / (area_i + area_j - inter) > thr
@@ -67,50 +84,47 @@ __device__ __forceinline__ bool suppresses(const float4 a, float area_a, const f
   return ovr > thr;
 }
 
-// CTAs stride over class segments.  seg_start is unordered (atomic append) -> each segment's end is
-// the smallest start greater than its own (or n).  Removed bits live in shared memory.
+// CTAs stride over class segments [seg_start, seg_end) (any order).  Removed bits live in shared memory.
+// Per 64-box block: (A) the block's boxes are staged in shared memory and the 64 x 64 suppression bits computed by
+// all threads; (B) warp 0 resolves the block -- the 64 mask rows are read up front (independent of the running `dead`
+// word, so the loads pipeline), the dependent chain is one AND / OR per box, every lane carries the same state; the
+// kept boxes are then compacted in parallel (rank = popcount of the kept bits below); (C) the kept boxes suppress
+// the tail in parallel.  The first version resolved with one thread that loaded every kept box from global memory
+// inside the sequential loop (~64 dependent L2 round trips per block).
 __global__ void __launch_bounds__(kNmsThreads)
 nms_segment_kernel(const float4* __restrict__ sboxes, const int* __restrict__ seg_start,
-                   const int* __restrict__ num_seg, const int* __restrict__ order2, int n, float thr,
+                   const int* __restrict__ seg_end, const int* __restrict__ num_seg,
+                   const int* __restrict__ order2, int n, float thr,
                    unsigned char* __restrict__ keep_flag /* by global score rank */) {
-  extern __shared__ unsigned int s_removed[];  // (n + 31) / 32 words
+  extern __shared__ unsigned int s_removed[];  // (n + 31) / 32 words (+ 2: a block's pair of words is always readable)
   __shared__ unsigned long long s_mask[64];
+  __shared__ float4 s_box[64];
   __shared__ float4 s_kbox[64];
   __shared__ float s_karea[64];
-  __shared__ int s_nk;
-  __shared__ int s_bounds[2];
+  __shared__ unsigned long long s_kept;
   const int ns = *num_seg;
   for (int seg = blockIdx.x; seg < ns; seg += gridDim.x) {
     __syncthreads();
-    if (threadIdx.x == 0) {
-      const int s = seg_start[seg];
-      int e = n;
-      for (int i = 0; i < ns; ++i) {
-        const int t = seg_start[i];
-        if (t > s && t < e) e = t;
-      }
-      s_bounds[0] = s;
-      s_bounds[1] = e;
-    }
-    __syncthreads();
-    const int s = s_bounds[0], m = s_bounds[1] - s_bounds[0];
+    const int s = seg_start[seg], m = seg_end[seg] - s;
     const float4* B = sboxes + s;
-    for (int i = threadIdx.x; i < (m + 31) / 32; i += kNmsThreads) s_removed[i] = 0u;
+    for (int i = threadIdx.x; i < (m + 31) / 32 + 2; i += kNmsThreads) s_removed[i] = 0u;
     __syncthreads();
     const int nblk = (m + 63) / 64;
     for (int blk = 0; blk < nblk; ++blk) {
       const int base = blk * 64;
       const int cnt = min(64, m - base);
+      if (threadIdx.x < cnt) s_box[threadIdx.x] = B[base + threadIdx.x];
+      __syncthreads();
       // A: 64x64 suppression bits inside the block (thread = (row i, 8-column group))
       {
         const int i = threadIdx.x >> 3, part = threadIdx.x & 7;
         unsigned long long bits = 0ull;
         if (i < cnt) {
-          const float4 a = B[base + i];
+          const float4 a = s_box[i];
           const float area_a = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
           for (int jj = 0; jj < 8; ++jj) {
             const int j = part * 8 + jj;
-            if (j > i && j < cnt && suppresses(a, area_a, B[base + j], thr)) bits |= 1ull << j;
+            if (j > i && j < cnt && suppresses(a, area_a, s_box[j], thr)) bits |= 1ull << j;
           }
         }
         // combine the 8 partial masks of row i (8 consecutive lanes); executed by every lane
@@ -120,29 +134,34 @@ nms_segment_kernel(const float4* __restrict__ sboxes, const int* __restrict__ se
         if (part == 0 && i < 64) s_mask[i] = bits;
       }
       __syncthreads();
-      // B: sequential resolve by one thread
-      if (threadIdx.x == 0) {
-        unsigned long long dead = 0ull;
-        for (int i = 0; i < cnt; ++i) {
-          const int p = base + i;
-          if ((s_removed[p >> 5] >> (p & 31)) & 1u) dead |= 1ull << i;
+      // B: resolve by warp 0 (all lanes run the same chain)
+      if (threadIdx.x < 32) {
+        unsigned long long dead = (unsigned long long)s_removed[base >> 5] |
+                                  ((unsigned long long)s_removed[(base >> 5) + 1] << 32);
+        if (cnt < 64) dead |= ~0ull << cnt;
+        unsigned long long kept = 0ull;
+#pragma unroll 16
+        for (int i = 0; i < 64; ++i) {
+          const unsigned long long row = s_mask[i];  // rows >= cnt are zero
+          const bool alive = !((dead >> i) & 1ull);
+          kept |= alive ? (1ull << i) : 0ull;
+          dead |= alive ? row : 0ull;
         }
-        int nk = 0;
-        for (int i = 0; i < cnt; ++i) {
-          if (!((dead >> i) & 1ull)) {
-            dead |= s_mask[i];
-            const float4 a = B[base + i];
-            s_kbox[nk] = a;
-            s_karea[nk] = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
-            ++nk;
+        // the kept boxes, compacted in block order; their keep flags
+        for (int i = threadIdx.x; i < cnt; i += 32) {
+          if ((kept >> i) & 1ull) {
+            const int pos = __popcll(kept & ((1ull << i) - 1ull));
+            const float4 a = s_box[i];
+            s_kbox[pos] = a;
+            s_karea[pos] = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
             keep_flag[order2[s + base + i]] = 1;
           }
         }
-        s_nk = nk;
+        if (threadIdx.x == 0) s_kept = kept;
       }
       __syncthreads();
       // C: kept boxes of this block suppress the tail
-      const int nk = s_nk;
+      const int nk = __popcll(s_kept);
       for (int j = base + 64 + threadIdx.x; j < m; j += kNmsThreads) {
         if ((s_removed[j >> 5] >> (j & 31)) & 1u) continue;
         const float4 b = B[j];
@@ -165,7 +184,7 @@ __global__ void nms_finish_kernel(const int* __restrict__ sel, const int* __rest
 
 struct NmsWs {
   unsigned int *keys_a, *keys_b, *cls_a, *cls_b;
-  int *vals_a, *order1, *pos_a, *order2, *seg_start, *num_seg, *sel, *num_sel;
+  int *vals_a, *order1, *pos_a, *order2, *seg_start, *seg_end, *num_seg, *sel, *num_sel;
   float4* sboxes;
   unsigned char* keep_flag;
   void* cub_temp;
@@ -193,6 +212,7 @@ inline size_t nms_layout(int n, void* base, NmsWs* w) {
   t.pos_a = (int*)take(n4);
   t.order2 = (int*)take(n4);
   t.seg_start = (int*)take(n4);
+  t.seg_end = (int*)take(n4);
   t.sel = (int*)take(n4);
   t.sboxes = (float4*)take((size_t)n * 16);
   // zero-initialised block: keep flags, counters
@@ -214,43 +234,37 @@ extern "C" size_t jtsm_nms_workspace_bytes(int num_boxes) {
   return nms_layout(num_boxes, nullptr, nullptr);
 }
 
-extern "C" int jtsm_batched_nms(const float* boxes, const float* scores, const long long* idxs,
-                                int num_boxes, float iou_threshold, long long* keep,
-                                long long* num_keep, void* workspace, size_t workspace_bytes,
-                                void* stream) {
-  if (num_boxes < 0 || !num_keep) return JTSM_ERR_INVALID_ARGUMENT;
-  cudaStream_t st = (cudaStream_t)stream;
-  const int n = num_boxes;
-  if (n == 0) {
-    cudaMemsetAsync(num_keep, 0, sizeof(long long), st);
-    return cuda_status();
-  }
-  if (!boxes || !scores || !keep || !workspace) return JTSM_ERR_INVALID_ARGUMENT;
+namespace jtsm {
+// The whole NMS pipeline.  num_valid (DEVICE int, optional): only boxes [0, *num_valid) take part -- for callers whose
+// candidate count is produced on the device (fast_rcnn_inference: threshold + compaction); n is then the capacity.
+int nms_run(const float* boxes, const float* scores, const long long* idxs, int n, const int* num_valid,
+            float iou_threshold, long long* keep, long long* num_keep, void* workspace, size_t workspace_bytes,
+            cudaStream_t st) {
   if (workspace_bytes < jtsm_nms_workspace_bytes(n)) return JTSM_ERR_WORKSPACE_TOO_SMALL;
   NmsWs w;
   nms_layout(n, workspace, &w);
   const int tb = 256, gb = (n + tb - 1) / tb;
   // zero the contiguous scratch block [keep_flag .. num_sel]
   cudaMemsetAsync(w.keep_flag, 0, (size_t)((char*)w.cub_temp - (char*)w.keep_flag), st);
-  nms_keys_kernel<<<gb, tb, 0, st>>>(scores, n, w.keys_a, w.vals_a);
+  nms_keys_kernel<<<gb, tb, 0, st>>>(scores, n, num_valid, w.keys_a, w.vals_a);
   size_t need = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, need, w.keys_a, w.keys_b, w.vals_a, w.order1, n, 0, 32, st);
   if (need > w.cub_bytes) return JTSM_ERR_WORKSPACE_TOO_SMALL;
   cub::DeviceRadixSort::SortPairs(w.cub_temp, need, w.keys_a, w.keys_b, w.vals_a, w.order1, n, 0, 32, st);
-  nms_gather_class_kernel<<<gb, tb, 0, st>>>(idxs, w.order1, n, w.cls_a, w.pos_a);
+  nms_gather_class_kernel<<<gb, tb, 0, st>>>(idxs, w.order1, n, num_valid, w.cls_a, w.pos_a);
   need = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, need, w.cls_a, w.cls_b, w.pos_a, w.order2, n, 0, 32, st);
   if (need > w.cub_bytes) return JTSM_ERR_WORKSPACE_TOO_SMALL;
   cub::DeviceRadixSort::SortPairs(w.cub_temp, need, w.cls_a, w.cls_b, w.pos_a, w.order2, n, 0, 32, st);
-  nms_segments_kernel<<<gb, tb, 0, st>>>(boxes, w.order1, w.order2, w.cls_b, n, w.sboxes, w.seg_start,
+  nms_segments_kernel<<<gb, tb, 0, st>>>(boxes, w.order1, w.order2, w.cls_b, n, w.sboxes, w.seg_start, w.seg_end,
                                          w.num_seg);
   // CTAs stride over segments; the segment count is only known on the device.
   const int max_seg = n < 2 * num_sms() ? n : 2 * num_sms();
-  const size_t smem = ((size_t)n / 32 + 2) * 4;
+  const size_t smem = ((size_t)n / 32 + 4) * 4;
   if (smem > 160 * 1024) return JTSM_ERR_UNSUPPORTED;
   if (smem > 40 * 1024)
     cudaFuncSetAttribute(nms_segment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  nms_segment_kernel<<<max_seg, kNmsThreads, smem, st>>>(w.sboxes, w.seg_start, w.num_seg, w.order2, n,
+  nms_segment_kernel<<<max_seg, kNmsThreads, smem, st>>>(w.sboxes, w.seg_start, w.seg_end, w.num_seg, w.order2, n,
                                                          iou_threshold, w.keep_flag);
   need = 0;
   cub::DeviceSelect::Flagged(nullptr, need, w.order1, w.keep_flag, w.sel, w.num_sel, n, st);
@@ -259,4 +273,19 @@ extern "C" int jtsm_batched_nms(const float* boxes, const float* scores, const l
   nms_finish_kernel<<<gb, tb, 0, st>>>(w.sel, w.num_sel, keep, n, num_keep);
   count_launch(6);
   return cuda_status();
+}
+}  // namespace jtsm
+
+extern "C" int jtsm_batched_nms(const float* boxes, const float* scores, const long long* idxs,
+                                int num_boxes, float iou_threshold, long long* keep,
+                                long long* num_keep, void* workspace, size_t workspace_bytes,
+                                void* stream) {
+  if (num_boxes < 0 || !num_keep) return JTSM_ERR_INVALID_ARGUMENT;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (num_boxes == 0) {
+    cudaMemsetAsync(num_keep, 0, sizeof(long long), st);
+    return cuda_status();
+  }
+  if (!boxes || !scores || !keep || !workspace) return JTSM_ERR_INVALID_ARGUMENT;
+  return nms_run(boxes, scores, idxs, num_boxes, nullptr, iou_threshold, keep, num_keep, workspace, workspace_bytes, st);
 }

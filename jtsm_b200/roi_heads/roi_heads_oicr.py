@@ -162,6 +162,10 @@ class OICRROIHeadsB200(nn.Module):
     def _forward_box(self, features, proposals):
         box_features, _ = self._pool(features, proposals)
         box_features = self.box_head(box_features)
+        return self._forward_predictors(box_features, proposals)
+
+    def _forward_predictors(self, box_features, proposals):
+        """Everything of `_forward_box` after the box head (roi_heads_oicr.py:404-468) on given fc7 activations."""
         counts = [len(p) for p in proposals]
         if not self.training:
             if self.refine_K == 0:
