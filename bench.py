@@ -13,8 +13,11 @@ fc6/fc7 GEMMs are excluded (they stay in torch).
   value : RoIs/s, whole job, inputs resident in HBM, CUDA-event timed, L2 flushed
           (256 MiB write) between timed steps.
   e2e   : same step driven from pinned HOST buffers through the public ops layer
-          (-> C ABI), H2D of feature map / rois / logits and D2H of losses + grad_feature
-          inside the timed region.
+          (-> C ABI); inside the timed region every step uploads its inputs (feature map in the
+          step's dtype, rois, objectness, head logits, labels: one pinned arena) and downloads
+          what the host consumes (losses, pseudo-labels, counters and a CHECKSUM of grad_feature:
+          the gradient itself stays on the device, where the backbone's backward reads it).  The
+          timed loop rotates over distinct host batches.
   roofline : dominant kernel (RoIPool forward): algorithmic bytes / its CUDA-event time.
   cpu_baseline : the CPU oracle port (oracle/jtsm_oracle.c, host threads) on a bounded
           sample of the same workload.  --impl reference times the reference's own CPU
@@ -34,6 +37,11 @@ if ROOT not in sys.path:
 
 METRIC = "rois_per_sec_fwd_bwd_pool_mil_refine"
 UNIT = "RoIs/s"
+# what the reference arm runs: the pooling op is the reference's own dependency (torchvision CPU roi_pool, or the
+# reference's MOIPool kernels built as host code); the head math is oracle/ref_heads.py, a restatement pinned
+# bit-equal to the reference's Python (tests/test_ref_parity.py) -- a port, and labelled as one
+REF_KIND = "reference(pool)+port(heads)"
+SINGLE_PROCESS = "; ONE CPU process on rank 0 whatever --gpus says (at N > 1 the driver's ratio divides N GPUs by it)"
 
 
 def parse():
@@ -131,6 +139,21 @@ def make_workload(name, rank, dtype):
     return w
 
 
+def config_dict(wl):
+    """The workload description both arms print verbatim (the driver compares them)."""
+    cfg = wl["cfg"]
+    d = {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"], "pooled": cfg["P"],
+         "classes": cfg["K"], "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")),
+         "pooler": cfg.get("pooler", "ROIPool")}
+    if "augs" in wl:  # inference chain (c4)
+        d.update(mode="inference", augmentations=cfg["A"], feature_channels=cfg["C"], stride=cfg["stride"],
+                 min_sizes=list(cfg["min_sizes"]), flip=bool(cfg["flip"]), score_thresh=cfg["score_thresh"],
+                 nms_thresh=cfg["nms_thresh"], detections_per_image=cfg["topk"])
+    else:
+        d.update(mode="train_step", feature=[cfg["N"], cfg["C"], cfg["H"], cfg["W"]])
+    return d
+
+
 def algorithmic_bytes(cfg, esz):
     """compulsory traffic only."""
     n, c, h, w_, r, p, k, kr = cfg["N"], cfg["C"], cfg["H"], cfg["W"], cfg["N"] * cfg["R"], cfg["P"], cfg["K"], cfg["Kr"]
@@ -173,6 +196,8 @@ def run_b200(a):
     esz = 2 if a.dtype == "bf16" else 4
     step = hotpath.HotPathStep(cfg, dev, dtype=torch.bfloat16 if a.dtype == "bf16" else torch.float32)
     host = step.pin_host_inputs(wl)
+    # a second, different batch of the same shapes: the e2e loop alternates between the two pinned arenas
+    host_b = step.pin_host_inputs(make_workload(a.config, rank + 1000, a.dtype))
     resident = step.upload(host)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
@@ -238,7 +263,8 @@ def run_b200(a):
         c1.record()
         torch.cuda.synchronize()
         h2d_gbps = 10 * step.h2d_bytes(host) / (c0.elapsed_time(c1) * 1e-3) / 1e9
-        step.run_stream([host] * 3)
+        batches = [host if i % 2 == 0 else host_b for i in range(a.steps)]
+        step.run_stream(batches[:3])
         barrier()
         # the streamed step's graph alone (derive inputs + step + result packing), inputs resident, back to back
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -255,14 +281,14 @@ def run_b200(a):
         seen = []
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        step.run_stream([host] * a.steps, consume=lambda i, out: seen.append(float(out[0][0])))
+        step.run_stream(batches, consume=lambda i, out: seen.append(float(out[0][0])))
         e1.record()
         barrier()
         assert len(seen) == a.steps
         e2e_ms = e0.elapsed_time(e1)
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         f0.record()
-        step.run_stream([host] * a.steps, before_step=flush.zero_)
+        step.run_stream(batches, before_step=flush.zero_)
         f1.record()
         barrier()
         e2e_flush_ms = f0.elapsed_time(f1)
@@ -283,6 +309,12 @@ def run_b200(a):
         e2e_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev2)
         e2e_mode = "sequential: H2D, step, blocking D2H"
 
+    # what bounds a streamed step: its upload over the host link, or its kernels
+    e2e_bound = None
+    if h2d_gbps and io_graph_ms:
+        up_ms = step.h2d_bytes(host) / (h2d_gbps * 1e9) * 1e3
+        e2e_bound = "h2d (%.3f ms upload vs %.3f ms of kernels per step)" % (up_ms, io_graph_ms) if up_ms > io_graph_ms \
+            else "kernels (%.3f ms per step vs %.3f ms upload)" % (io_graph_ms, up_ms)
     clocks = sampler.stop() if rank == 0 else None
     tm = torch.tensor([dev_ms, e2e_ms, e2e_flush_ms or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -298,14 +330,18 @@ def run_b200(a):
             "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": dev_ms / a.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32" if a.dtype == "fp32" else "bf16",
             "data": "synthetic (seeded MCG-like proposals, relu(randn) conv5 map, random head logits)",
-            "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
-                       "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
-                       "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": cfg.get("pooler", "ROIPool"),
-                       "l2": "flushed (256 MiB write) between timed steps (value, roofline); e2e: see e2e.l2", "stages": step.stages(), "schedule": step.schedule(),
+            "config": config_dict(wl),
+            "detail": {"l2": "flushed (256 MiB write) between timed steps (value, roofline); e2e: see e2e.l2",
+                       "stages": step.stages(), "schedule": step.schedule(),
                        "launch": "cuda_graph_replay" if use_graph else "eager"},
             "e2e": {"value": world * R * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": step.h2d_bytes(host), "d2h_bytes_per_step": step.d2h_bytes(),
                     "mode": e2e_mode,
+                    "uploaded": "feature map (step dtype), rois, objectness, MIL + refinement logits, image labels "
+                                "(in the real system the feature map is produced on the device by the backbone)",
+                    "downloaded": "losses, pseudo-labels, fg/bg + accuracy counters, checksum of grad_feature "
+                                  "(the gradient w.r.t. the feature map stays on the device)",
+                    "bound": e2e_bound,
                     "l2": "fresh H2D inputs every step; alternating buffer sets, > 500 MB streamed per step "
                           "(126 MB L2) before a buffer is reused; no explicit flush" if use_graph else
                           "flushed (256 MiB write) before every step",
@@ -362,14 +398,192 @@ def run_reference(a):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * sum(ts) / len(ts), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["name"], "images_per_gpu": cfg["N"], "rois_per_image": cfg["R"],
-                   "feature": [cfg["N"], cfg["C"], cfg["H"], cfg["W"]], "pooled": cfg["P"], "classes": cfg["K"],
-                   "refine_branches": cfg["Kr"], "box_reg": bool(cfg.get("reg")), "pooler": cfg.get("pooler", "ROIPool")},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": desc},
+        "config": config_dict(wl),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": REF_KIND, "sample": desc + SINGLE_PROCESS},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(json.dumps(out))
+
+
+# ----------------------------------------------------------------------------------------------
+# c4: the multi-scale + flip INFERENCE chain (BASELINE.json configs[3])
+# ----------------------------------------------------------------------------------------------
+def nms_pairs(det_classes_counts):
+    """Box pairs of the per-class suppression matrices (what torchvision's bitmask kernel evaluates): sum m (m - 1) / 2."""
+    return sum(m * (m - 1) // 2 for m in det_classes_counts)
+
+
+def run_b200_infer(a):
+    import torch
+    import torch.distributed as dist
+
+    from jtsm_b200 import _lib, inferpath, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (impl=b200) needs a CUDA device; there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    wl = synth.infer_case(a.config, sweep_index=rank)
+    cfg = wl["cfg"]
+    rois_per_step = cfg["A"] * cfg["R"]  # RoIs pooled + scored per image
+    step = inferpath.InferenceStep(cfg, dev, dtype=torch.bfloat16 if a.dtype == "bf16" else torch.float32)
+    host = step.host_inputs(wl)
+    d = step.upload(host)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    step.capture(d)
+    for _ in range(max(a.warmup, 3)):
+        step.graph.replay()
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    sampler.mark()
+    t0 = time.perf_counter()
+    for i in range(a.steps):
+        flush.zero_()
+        ev[i][0].record()
+        step.graph.replay()
+        ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t0
+    dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
+    # the NMS kernel alone (its own graph: the detection call on the merged tensors), CUDA events, L2 flushed
+    from jtsm_b200 import inference
+    mb, ms = step.last["mean_boxes"], step.last["mean_scores"]
+    g2 = torch.cuda.CUDAGraph()
+    s2 = torch.cuda.Stream()
+    s2.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s2):
+        inference.fast_rcnn_inference_device(mb, ms, step.orig_hw, cfg["score_thresh"], cfg["nms_thresh"], cfg["topk"])
+    torch.cuda.current_stream().wait_stream(s2)
+    torch.cuda.synchronize()
+    with torch.cuda.graph(g2):
+        inference.fast_rcnn_inference_device(mb, ms, step.orig_hw, cfg["score_thresh"], cfg["nms_thresh"], cfg["topk"])
+    kev = []
+    for i in range(a.steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g2.replay()
+        e1.record()
+        kev.append((e0, e1))
+    barrier()
+    det_ms = sum(e0.elapsed_time(e1) for e0, e1 in kev) / len(kev)
+    # candidates per class (score > thresh) -> pair count of the suppression problem
+    sc = ms[:, :-1]
+    counts = [int(v) for v in (sc > cfg["score_thresh"]).sum(dim=0).tolist()]
+
+    # e2e: every step uploads ALL its inputs from pinned host memory (the conv5 maps of the 10 augmentations included,
+    # which the real system produces on the device) and downloads the packed detections
+    out_host = torch.empty(step.graph_packed.shape, dtype=step.graph_packed.dtype).pin_memory()
+    hosts = [host, step.host_inputs(synth.infer_case(a.config, sweep_index=rank + 1000))]
+    for i in range(2):
+        step.upload(hosts[i % 2], into=d)
+        step.graph.replay()
+        out_host.copy_(step.graph_packed, non_blocking=True)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        step.upload(hosts[i % 2], into=d)
+        step.graph.replay()
+        out_host.copy_(step.graph_packed, non_blocking=True)
+    e1.record()
+    barrier()
+    e2e_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    tm = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = (float(v) for v in tm.tolist())
+    if rank == 0:
+        pairs = nms_pairs(counts)
+        flops = 16.0 * pairs  # SURVEY 8(d): ~16 FP32 ops per box pair
+        sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+        peak_tflops = sm_count * 128 * 2 * 1.965e9 / 1e12  # FP32 SIMT peak at the maximum SM clock
+        ach = flops / (det_ms * 1e-3) / 1e12
+        out = {
+            "metric": METRIC, "value": world * rois_per_step * a.steps / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": dev_ms / a.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if a.dtype == "fp32" else "bf16",
+            "data": "synthetic (seeded MCG-like proposals mapped into 10 augmented images, relu(randn) conv5 maps, random head logits)",
+            "config": config_dict(wl),
+            "detail": {"images_per_sec": world * a.steps / (dev_ms * 1e-3), "l2": "flushed (256 MiB write) between timed steps",
+                       "stages": step.stages(), "launch": "cuda_graph_replay",
+                       "value_counts": "RoIs pooled and scored = augmentations x proposals per image"},
+            "e2e": {"value": world * rois_per_step * a.steps / (e2e_ms * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": step.h2d_bytes(host),
+                    "d2h_bytes_per_step": out_host.numel() * out_host.element_size(),
+                    "mode": "sequential per image: H2D of all inputs, graph replay, D2H of the packed detections",
+                    "uploaded": "conv5 maps of the 10 augmentations (produced on the device in the real system), RoIs, "
+                                "objectness, refinement logits / deltas", "downloaded": "top-100 detections (boxes, scores, classes, proposal ids, count)",
+                    "bound": "h2d"},
+            "gpu_launches": int(step.launches_per_step * a.steps),
+            "roofline": {"bound": "alu", "kernel": "nms_segment_kernel (inside jtsm_fast_rcnn_inference: 9 launches)",
+                         "achieved": ach, "peak": peak_tflops, "unit": "TFLOP/s", "frac": ach / peak_tflops,
+                         "peak_source": "FP32 SIMT: %d SMs x 128 lanes x 2 x 1.965 GHz" % sm_count, "traffic": None,
+                         "algorithmic_pairs": pairs, "flops_per_pair": 16, "candidates_per_class": counts,
+                         "avg_launch_ms": det_ms,
+                         "note": "algorithmic work = the full per-class suppression matrices (what a bitmask NMS evaluates); "
+                                 "greedy NMS has a sequential chain of ceil(m / 64) dependent block steps per class and "
+                                 "20 classes occupy 20 of the SMs, so the fraction of the chip-wide ALU peak is small by "
+                                 "construction; avg_launch_ms covers the whole detection call"},
+            "clocks": clocks, "wall_s_timed_region": t_wall,
+        }
+        if not a.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline_infer(wl, a)
+        emit(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline_infer(wl, a):
+    from oracle import cpu_infer
+
+    cores = os.cpu_count() or 1
+    sample = a.cpu_sample_rois or cpu_infer.auto_sample_rois(wl)
+    t, n_rois, desc, parts = cpu_infer.time_step(wl, sample, cores)
+    return {"value": n_rois / t, "unit": UNIT, "cores": cores, "kind": REF_KIND, "sample": desc, "seconds_per_image_scaled": t,
+            "measured_seconds": parts}
+
+
+def run_reference_infer(a):
+    from jtsm_b200 import synth
+    from oracle import cpu_infer
+
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = synth.infer_case(a.config, sweep_index=0)
+    cores = os.cpu_count() or 1
+    sample = a.cpu_sample_rois or cpu_infer.auto_sample_rois(wl, budget_s=4.0)
+    ts, desc, n_rois = [], "", 0
+    for i in range(max(1, min(a.warmup, 1)) + a.steps):
+        t, n_rois, desc, _ = cpu_infer.time_step(wl, sample, cores)
+        if i >= max(1, min(a.warmup, 1)):
+            ts.append(t)
+    v = n_rois * len(ts) / sum(ts)
+    emit(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 * sum(ts) / len(ts), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(wl),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": REF_KIND, "sample": desc + SINGLE_PROCESS},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
 
 _JSON_OUT = None
@@ -400,10 +614,13 @@ def main():
     sys.stdout.flush()
     _JSON_OUT = os.dup(1)
     os.dup2(2, 1)  # stray prints of libraries -> stderr
+    from jtsm_b200 import synth
+
+    infer = a.config in synth.INFER_CONFIGS
     if a.impl == "reference":
-        run_reference(a)
+        (run_reference_infer if infer else run_reference)(a)
     else:
-        run_b200(a)
+        (run_b200_infer if infer else run_b200)(a)
 
 
 if __name__ == "__main__":

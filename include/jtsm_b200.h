@@ -320,6 +320,27 @@ JTSM_API int jtsm_batched_nms(const float* boxes, const float* scores, const lon
                               void* stream);
 
 /* ------------------------------------------------------------------------
+ * fast_rcnn_inference_single_image on the device
+ * (projects/WSL/wsl/modeling/roi_heads/fast_rcnn_oicr.py:95-163 == fast_rcnn_wsddn.py:94-162; the stock twin
+ * detectron2/modeling/roi_heads/fast_rcnn.py is what GeneralizedRCNNWithTTAAVG calls at test_time_augmentation_avg.py:393):
+ * rows with a non-finite box or score are dropped, the background column (last) is ignored, boxes are clipped to
+ * (image_h, image_w), candidates are the (row, class) pairs with score > score_thresh in row-major (`nonzero`) order,
+ * per-class NMS (IoU > nms_thresh suppresses), the topk best (topk < 0: all) are returned in descending score.
+ * boxes  [num_rois, boxes_per_row, 4] (boxes_per_row = 1 or num_classes), scores [num_rois, num_classes + 1].
+ * Outputs, `capacity` rows each (capacity >= topk, or >= num_rois * num_classes when topk < 0): det_boxes [cap, 4],
+ * det_scores [cap], det_classes int64 (pred_classes), det_rows int64 (filter_inds[:, 0]: index among the VALID rows,
+ * what the reference returns as the kept indices), det_pred_inds int64 (pred_inds: the original row);
+ * rows >= *num_det are zero / -1.  num_det int64 [1] DEVICE.  Never synchronises, CUDA-graph capturable.
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_fast_rcnn_inference_workspace_bytes(int num_rois, int num_classes);
+JTSM_API int jtsm_fast_rcnn_inference(const float* boxes, int boxes_per_row, const float* scores,
+                                      int num_rois, int num_classes, float image_h, float image_w,
+                                      float score_thresh, float nms_thresh, int topk, int capacity,
+                                      float* det_boxes, float* det_scores, long long* det_classes,
+                                      long long* det_rows, long long* det_pred_inds, long long* num_det,
+                                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
  * Test-time-augmentation average.
  * GeneralizedRCNNWithTTAAVG._get_augmented_boxes
  * (projects/WSL/wsl/modeling/test_time_augmentation_avg.py:364-390): the boxes of every augmented

@@ -25,34 +25,23 @@ def predict_boxes_K(deltas_K, proposal_boxes, weights=(10.0, 10.0, 5.0, 5.0)):
 
 def fast_rcnn_inference_single_image(boxes, scores, image_shape, score_thresh, nms_thresh, topk_per_image):
     """boxes [R, 4] or [R, 4K], scores [R, K+1] (background last), image_shape (h, w).
-    -> dict(pred_boxes, scores, pred_classes, pred_inds), kept RoI indices, all_scores, all_boxes."""
+    -> dict(pred_boxes, scores, pred_classes, pred_inds), kept RoI indices, all_scores, all_boxes -- the reference's
+    return values (fast_rcnn_oicr.py:95-163).  The whole function is ONE C-ABI call (jtsm_fast_rcnn_inference: finite
+    mask, background drop, clip, threshold, ordered compaction, per-class NMS, top-k; no host sync inside); the one
+    host read here is the detection count, because the reference's signature returns tensors of that length.
+    `fast_rcnn_inference_device` keeps everything padded on the device."""
     all_scores, all_boxes = scores.clone().unsqueeze(0), boxes.clone().unsqueeze(0)
-    r, k1 = scores.shape
-    pred_inds = torch.arange(r, device=scores.device, dtype=torch.long).unsqueeze(1).repeat(1, k1)
-    valid = torch.isfinite(boxes).all(dim=1) & torch.isfinite(scores).all(dim=1)
-    if not valid.all():
-        boxes, scores, pred_inds = boxes[valid], scores[valid], pred_inds[valid]
-    scores = scores[:, :-1]
-    nb = boxes.shape[1] // 4
-    h, w = image_shape
-    boxes = boxes.reshape(-1, 4).clone()
-    boxes[:, 0].clamp_(min=0, max=w)  # Boxes.clip, detectron2/structures/boxes.py:195-211
-    boxes[:, 1].clamp_(min=0, max=h)
-    boxes[:, 2].clamp_(min=0, max=w)
-    boxes[:, 3].clamp_(min=0, max=h)
-    boxes = boxes.view(-1, nb, 4)
-    pred_inds = pred_inds[:, :-1]
-    mask = scores > score_thresh
-    filter_inds = mask.nonzero()
-    boxes = boxes[filter_inds[:, 0], 0] if nb == 1 else boxes[mask]
-    scores = scores[mask]
-    pred_inds = pred_inds[mask]
-    keep = ops.batched_nms(boxes, scores, filter_inds[:, 1], nms_thresh)
-    if topk_per_image >= 0:
-        keep = keep[:topk_per_image]
-    boxes, scores, filter_inds, pred_inds = boxes[keep], scores[keep], filter_inds[keep], pred_inds[keep]
-    result = dict(pred_boxes=boxes, scores=scores, pred_classes=filter_inds[:, 1], pred_inds=pred_inds)
-    return result, filter_inds[:, 0], all_scores, all_boxes
+    d = ops.fast_rcnn_inference_raw(boxes, scores, image_shape, score_thresh, nms_thresh, topk_per_image)
+    n = int(d["num"].item())
+    result = dict(pred_boxes=d["pred_boxes"][:n], scores=d["scores"][:n], pred_classes=d["pred_classes"][:n],
+                  pred_inds=d["pred_inds"][:n])
+    return result, d["rows"][:n], all_scores, all_boxes
+
+
+def fast_rcnn_inference_device(boxes, scores, image_shape, score_thresh, nms_thresh, topk_per_image):
+    """Same computation, results left padded on the device (`num` int64 [1] says how many rows are detections):
+    no host synchronisation at all, CUDA-graph capturable (bench.py's c4 inference chain)."""
+    return ops.fast_rcnn_inference_raw(boxes, scores, image_shape, score_thresh, nms_thresh, topk_per_image)
 
 
 def fast_rcnn_inference(boxes, scores, image_shapes, score_thresh, nms_thresh, topk_per_image):

@@ -416,10 +416,46 @@ def batched_nms_raw(boxes, scores, idxs, iou_threshold):
 
 
 def batched_nms(boxes, scores, idxs, iou_threshold):
-    """detectron2.layers.batched_nms signature (nms.py:10-30): int64 keep indices, descending score."""
+    """detectron2.layers.batched_nms signature (nms.py:10-30): int64 keep indices, descending score.  The returned
+    tensor's LENGTH is data dependent, so this signature costs one host read of the count (the reference's returns
+    after a device -> host mask copy); device-resident callers use batched_nms_raw / fast_rcnn_inference_raw."""
     assert boxes.shape[-1] == 4
     keep, num = batched_nms_raw(boxes.float(), scores, idxs, iou_threshold)
     return keep[: int(num.item())]
+
+
+def fast_rcnn_inference_raw(boxes, scores, image_shape, score_thresh, nms_thresh, topk_per_image):
+    """fast_rcnn_inference_single_image (fast_rcnn_oicr.py:95-163) in one C-ABI call, no host sync.
+    boxes [R, 4] or [R, 4K], scores [R, K+1] -> dict of PADDED device tensors with `cap` rows (cap = topk, or R*K when
+    topk < 0): pred_boxes [cap,4], scores [cap], pred_classes / rows / pred_inds int64 [cap] (-1 padding), num int64 [1]."""
+    _require_cuda(boxes, scores)
+    B, S = _f32c(boxes), _f32c(scores)
+    r, k1 = S.shape
+    k = k1 - 1
+    nb = B.shape[1] // 4 if r else 1
+    dev = S.device
+    cap = int(topk_per_image) if topk_per_image >= 0 else r * k
+    out = dict(pred_boxes=torch.empty((cap, 4), dtype=torch.float32, device=dev),
+               scores=torch.empty(cap, dtype=torch.float32, device=dev),
+               pred_classes=torch.empty(cap, dtype=torch.int64, device=dev),
+               rows=torch.empty(cap, dtype=torch.int64, device=dev),
+               pred_inds=torch.empty(cap, dtype=torch.int64, device=dev),
+               num=torch.zeros(1, dtype=torch.int64, device=dev))
+    if r == 0 or k <= 0:
+        return out
+    L = lib()
+    wsb = L.jtsm_fast_rcnn_inference_workspace_bytes(r, k)
+    if wsb == 0:
+        raise RuntimeError("jtsm_b200.fast_rcnn_inference: R x K too large")
+    ws = _workspace(wsb, dev)
+    h, w = image_shape
+    with torch.cuda.device(dev):
+        check(L.jtsm_fast_rcnn_inference(_ptr(B), nb, _ptr(S), r, k, float(h), float(w), float(score_thresh),
+                                         float(nms_thresh), int(topk_per_image), cap, _ptr(out["pred_boxes"]),
+                                         _ptr(out["scores"]), _ptr(out["pred_classes"]), _ptr(out["rows"]),
+                                         _ptr(out["pred_inds"]), _ptr(out["num"]), _ptr(ws), wsb, _stream()),
+              "fast_rcnn_inference")
+    return out
 
 
 def nms(boxes, scores, iou_threshold):

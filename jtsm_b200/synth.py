@@ -12,7 +12,8 @@ CONFIGS = {
     "c1": dict(N=1, C=512, stride=16, img_h=600, img_w=800, R=2000, P=7, K=20, Kr=0, reg=False),
     "c2": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=2000, P=7, K=20, Kr=3, reg=False),
     "c3": dict(N=2, C=2048, stride=8, img_h=600, img_w=800, R=4000, P=7, K=80, Kr=4, reg=True),
-    "c4": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=4000, P=7, K=20, Kr=3, reg=False),
+    # config 2's training step with 4000 proposals (round 1 called this "c4"; BASELINE.json's c4 is INFERENCE: infer_case)
+    "c2_r4000": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=4000, P=7, K=20, Kr=3, reg=False),
     # c3 with JTSM's own pooler (POOLER_TYPE "MOIPool", jtsm_WSR_50_DC5_1x.yaml:17): superpixel-masked pooling with
     # the heads' mask_scale x (objectness + 1) epilogue (roi_heads_jtsm.py:607-633); ~1000 superpixels per image
     "c3m": dict(N=2, C=2048, stride=8, img_h=600, img_w=800, R=4000, P=7, K=80, Kr=4, reg=True, pooler="MOIPool",
@@ -21,8 +22,49 @@ CONFIGS = {
 
 
 def config_index(name):
-    """c2 -> 2, c3m -> 3 (seed / label rules follow the base configuration)."""
+    """c2 -> 2, c3m -> 3, c2_r4000 -> 4 (its round-1 seed) (seed / label rules follow the base configuration)."""
+    if name == "c2_r4000":
+        return 4
     return int("".join(ch for ch in name[1:] if ch.isdigit()))
+
+
+# BASELINE.json configs[3]: multi-scale (5 scales + flip) WSL inference, 4000 proposals, OICR scoring + per-class NMS.
+# TEST.AUG of the WSL VGG configs: MIN_SIZES (480, 576, 688, 864, 1200), MAX_SIZE 4000, FLIP True
+# (projects/WSL/configs/PascalVOC-Detection/oicr_V_16_DC5_1x.yaml); thresholds :22-23; top 100 detections.
+INFER_CONFIGS = {
+    "c4": dict(N=1, C=512, stride=8, img_h=600, img_w=800, R=4000, P=7, K=20, Kr=3, reg=False,
+               min_sizes=(480, 576, 688, 864, 1200), max_size=4000, flip=True, score_thresh=1e-5, nms_thresh=0.3, topk=100),
+}
+
+
+def infer_case(name, sweep_index=0, **over):
+    """Everything one c4 inference step consumes, generated on the host: per augmentation the conv5 map of the resized
+    (and flipped) image, the proposals mapped into that image (transform_proposals, test_time_augmentation_avg.py:27-70),
+    objectness, and the Kr refinement heads' logits (+ deltas with box regression) that fc6 / fc7 would produce."""
+    from . import tta_shapes
+
+    cfg = dict(INFER_CONFIGS[name])
+    cfg.update(over)
+    g = generator(seed_for(config_index(name), sweep_index))
+    hw = (cfg["img_h"], cfg["img_w"])
+    boxes = proposals(g, cfg["R"], *hw)
+    obj = torch.rand(cfg["R"], generator=g)
+    augs = []
+    for (nh, nw, flip) in tta_shapes.augmented_shapes(hw, cfg["min_sizes"], cfg["max_size"], cfg["flip"]):
+        fh, fw = int(math.ceil(nh / cfg["stride"])), int(math.ceil(nw / cfg["stride"]))
+        sx, sy = float(torch.tensor(nw * 1.0 / hw[1], dtype=torch.float32)), float(torch.tensor(nh * 1.0 / hw[0], dtype=torch.float32))
+        b = boxes * torch.tensor([sx, sy, sx, sy])
+        if flip:
+            b = torch.stack([nw - b[:, 2], b[:, 1], nw - b[:, 0], b[:, 3]], dim=1)
+        b[:, 0::2] = b[:, 0::2].clamp(0, nw)
+        b[:, 1::2] = b[:, 1::2].clamp(0, nh)
+        augs.append(dict(hw=(nh, nw), flip=flip, feat=feature_map(g, 1, cfg["C"], fh, fw), boxes=b,
+                         rois=rois_from_boxes([b]),
+                         ref_logits=[torch.randn(cfg["R"], cfg["K"] + 1, generator=g) * 2 for _ in range(cfg["Kr"])],
+                         ref_deltas=[(torch.randn(cfg["R"], 4 * cfg["K"], generator=g) * 0.05 if cfg["reg"] else
+                                      torch.zeros(cfg["R"], 4 * cfg["K"])) for _ in range(cfg["Kr"])]))
+    cfg.update(scale=1.0 / cfg["stride"], A=len(augs))
+    return dict(name=name, cfg=cfg, boxes=boxes, objectness=obj, augs=augs)
 
 
 def seed_for(config_index, sweep_index=0):
