@@ -56,4 +56,4 @@ def test_reference_arm_prints_on_rank0_only():
     assert r0.returncode == 0
     line = json.loads(r0.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
-    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "reference"
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["cpu_baseline"]["kind"] == "reference(pool)+port(heads)"
