@@ -92,7 +92,12 @@ def test_head_modules_train_step_matches_reference_modules(cuda, name):
             key = "grad/%s.%s" % (mod_name, pn)
             if key in gold.files:
                 assert pv.grad is not None, key
-                _close(pv.grad.cpu().numpy(), gold[key], key)
+                if key.endswith("det.bias"):
+                    # analytically ZERO (softmax over the proposals is invariant to a per-class bias): both sides hold
+                    # rounding noise of ~1e-8, five orders below the other gradients
+                    assert float(np.abs(gold[key]).max()) < 1e-6 and float(pv.grad.abs().max()) < 1e-6, key
+                else:
+                    _close(pv.grad.cpu().numpy(), gold[key], key)
                 checked += 1
             else:
                 assert pv.grad is None or float(pv.grad.abs().max()) == 0.0, key  # bbox_pred without regression
