@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--config", default="c2")
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the DDP training-step leg (train_images_per_sec)")
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-sample-rois", type=int, default=0, help="0 = auto (about 10-30 s)")
     return ap.parse_args()
@@ -316,6 +317,9 @@ def run_b200(a):
         e2e_bound = "h2d (%.3f ms upload vs %.3f ms of kernels per step)" % (up_ms, io_graph_ms) if up_ms > io_graph_ms \
             else "kernels (%.3f ms per step vs %.3f ms upload)" % (io_graph_ms, up_ms)
     clocks = sampler.stop() if rank == 0 else None
+    train = None
+    if not a.no_train and cfg.get("pooler", "ROIPool") == "ROIPool":
+        train = train_leg(a, wl, dev, world, rank, barrier)
     tm = torch.tensor([dev_ms, e2e_ms, e2e_flush_ms or 0.0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
@@ -356,11 +360,76 @@ def run_b200(a):
             "clocks": clocks,
             "wall_s_timed_region": t_wall,
         }
+        if train is not None:
+            out.update(train)
         if not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(wl, a, kind="port")
         emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def train_leg(a, wl, dev, world, rank, barrier):
+    """The data-parallel TRAINING step: RoIPool -> fc6 / fc7 -> MIL + Kr refinement heads (~120 M fc
+    parameters) under DistributedDataParallel, loss.backward() through the head autograd Functions, SGD step; conv5
+    map resident on the device, per-rank synthetic images.  -> extra keys of the JSON line (identical on every rank
+    after the max-reduce; only rank 0 prints)."""
+    import torch
+    import torch.distributed as dist
+
+    from jtsm_b200 import trainstep
+
+    cfg = wl["cfg"]
+    ts = trainstep.TrainStep(cfg, dev, world=world)
+    batch = ts.make_batch(wl)
+    steps = max(3, min(a.steps, 10))
+
+    def timed(sync):
+        for _ in range(3):
+            ts.step(batch, sync=sync)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            ts.step(batch, sync=sync)
+        e1.record()
+        barrier()
+        return e0.elapsed_time(e1) / steps
+
+    ms = timed(True)
+    ms_local, ar_alone = None, None
+    if world > 1:
+        flat = torch.empty(ts.num_params(), dtype=torch.float32, device=dev)
+        for _ in range(2):
+            dist.all_reduce(flat)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            dist.all_reduce(flat)
+        e1.record()
+        barrier()
+        ar_alone = e0.elapsed_time(e1) / steps
+        ms_local = timed(False)  # same step without the gradient all-reduce (replicas diverge: timing only, run last)
+    tm = torch.tensor([ms, ms_local or 0.0, ar_alone or 0.0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    ms, ms_local, ar_alone = (float(v) for v in tm.tolist())
+    loss = float(ts.step(batch)) if world == 1 else None
+    return {
+        "train_images_per_sec": world * cfg["N"] * 1e3 / ms,
+        "allreduce_ms": (ms - ms_local) if world > 1 else 0.0,
+        "train_step": {
+            "ms_per_step": ms, "ms_per_step_without_allreduce": ms_local if world > 1 else None,
+            "allreduce_alone_ms": ar_alone if world > 1 else None, "allreduce_bytes": 4 * ts.num_params(),
+            "allreduce_ms_means": "exposed: step time under DDP minus the same step inside no_sync()",
+            "params": ts.num_params(), "images_per_gpu": cfg["N"], "steps": steps,
+            "what": "RoIPool x objectness -> fc6/fc7 (torch GEMMs, TF32 tensor cores) -> WSDDN MIL + BCE -> Kr x "
+                    "(pseudo-gt, label assignment, weighted CE[, box reg]) -> backward (autograd Functions, DDP "
+                    "gradient all-reduce over NCCL) -> SGD momentum step; conv5 map resident on the device",
+            "loss_after": loss,
+        },
+    }
 
 
 # ----------------------------------------------------------------------------------------------

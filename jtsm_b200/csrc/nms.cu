@@ -14,11 +14,16 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace jtsm {
 
+namespace cg = cooperative_groups;
+
 constexpr int kNmsThreads = 512;
+constexpr int kNmsCluster = 8;  // CTAs per class segment: the tail suppression is split over them by 64-box block
 
 __device__ __forceinline__ unsigned int desc_key(float s) {
   // ascending radix order of this key == descending score order
@@ -80,18 +85,27 @@ __device__ __forceinline__ bool suppresses(const float4 a, float area_a, const f
   const float h = fmaxf(0.f, __fsub_rn(fminf(a.w, b.w), fmaxf(a.y, b.y)));
   const float inter = __fmul_rn(w, h);
   const float area_b = __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
-  const float ovr = __fdiv_rn(inter, __fsub_rn(__fadd_rn(area_a, area_b), inter));
-  return ovr > thr;
+  const float uni = __fsub_rn(__fadd_rn(area_a, area_b), inter);
+  // inter / uni > thr  <=>  inter > thr * uni for uni > 0; the product and the quotient are each within one rounding
+  // of their real values, so a relative margin of 1e-5 decides all but the closest calls without the division
+  // (the exact quotient decides those, and every degenerate case: uni <= 0, non-finite, thr <= 0)
+  const float t = __fmul_rn(thr, uni);
+  if (uni > 1e-20f && uni < 1e30f && t > 0.f) {
+    if (inter > __fmul_rn(t, 1.00001f)) return true;
+    if (inter < __fmul_rn(t, 0.99999f)) return false;
+  }
+  return __fdiv_rn(inter, uni) > thr;
 }
 
-// CTAs stride over class segments [seg_start, seg_end) (any order).  Removed bits live in shared memory.
-// Per 64-box block: (A) the block's boxes are staged in shared memory and the 64 x 64 suppression bits computed by
-// all threads; (B) warp 0 resolves the block -- the 64 mask rows are read up front (independent of the running `dead`
-// word, so the loads pipeline), the dependent chain is one AND / OR per box, every lane carries the same state; the
-// kept boxes are then compacted in parallel (rank = popcount of the kept bits below); (C) the kept boxes suppress
-// the tail in parallel.  The first version resolved with one thread that loaded every kept box from global memory
-// inside the sequential loop (~64 dependent L2 round trips per block).
-__global__ void __launch_bounds__(kNmsThreads)
+// CLUSTERS of kNmsCluster CTAs stride over class segments [seg_start, seg_end) (any order).
+// Per 64-box block of a segment, every CTA of the cluster redundantly (A) stages the block's boxes in shared memory and
+// computes the 64 x 64 suppression bits, (B) resolves the block with warp 0 -- the 64 mask rows are read up front
+// (independent of the running `dead` word, so the loads pipeline), the dependent chain is one AND / OR per box -- and
+// compacts the kept boxes; then (C) the kept boxes suppress the tail, split over the cluster: tail block t belongs to
+// CTA t % kNmsCluster, which owns its removed bits.  The removed bits of the block being resolved are read from their
+// owner through distributed shared memory; one cluster barrier per block orders (C) before the next (B).
+// (Round 1: one CTA per class, a single thread resolved the block with a global-memory load per kept box.)
+__global__ void __cluster_dims__(kNmsCluster, 1, 1) __launch_bounds__(kNmsThreads)
 nms_segment_kernel(const float4* __restrict__ sboxes, const int* __restrict__ seg_start,
                    const int* __restrict__ seg_end, const int* __restrict__ num_seg,
                    const int* __restrict__ order2, int n, float thr,
@@ -102,13 +116,15 @@ nms_segment_kernel(const float4* __restrict__ sboxes, const int* __restrict__ se
   __shared__ float4 s_kbox[64];
   __shared__ float s_karea[64];
   __shared__ unsigned long long s_kept;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int cr = (int)cluster.block_rank();
+  const int cid = blockIdx.x / kNmsCluster, ncl = gridDim.x / kNmsCluster;
   const int ns = *num_seg;
-  for (int seg = blockIdx.x; seg < ns; seg += gridDim.x) {
-    __syncthreads();
+  for (int seg = cid; seg < ns; seg += ncl) {
     const int s = seg_start[seg], m = seg_end[seg] - s;
     const float4* B = sboxes + s;
     for (int i = threadIdx.x; i < (m + 31) / 32 + 2; i += kNmsThreads) s_removed[i] = 0u;
-    __syncthreads();
+    cluster.sync();  // every CTA's bits are cleared before anyone reads them (and nobody still reads the last segment's)
     const int nblk = (m + 63) / 64;
     for (int blk = 0; blk < nblk; ++blk) {
       const int base = blk * 64;
@@ -134,10 +150,10 @@ nms_segment_kernel(const float4* __restrict__ sboxes, const int* __restrict__ se
         if (part == 0 && i < 64) s_mask[i] = bits;
       }
       __syncthreads();
-      // B: resolve by warp 0 (all lanes run the same chain)
+      // B: resolve by warp 0 (all lanes run the same chain); the block's removed bits live in CTA blk % kNmsCluster
       if (threadIdx.x < 32) {
-        unsigned long long dead = (unsigned long long)s_removed[base >> 5] |
-                                  ((unsigned long long)s_removed[(base >> 5) + 1] << 32);
+        const unsigned int* owner = cluster.map_shared_rank(s_removed, blk % kNmsCluster);
+        unsigned long long dead = (unsigned long long)owner[base >> 5] | ((unsigned long long)owner[(base >> 5) + 1] << 32);
         if (cnt < 64) dead |= ~0ull << cnt;
         unsigned long long kept = 0ull;
 #pragma unroll 16
@@ -147,29 +163,31 @@ nms_segment_kernel(const float4* __restrict__ sboxes, const int* __restrict__ se
           kept |= alive ? (1ull << i) : 0ull;
           dead |= alive ? row : 0ull;
         }
-        // the kept boxes, compacted in block order; their keep flags
+        // the kept boxes, compacted in block order; their keep flags (written by one CTA of the cluster)
         for (int i = threadIdx.x; i < cnt; i += 32) {
           if ((kept >> i) & 1ull) {
             const int pos = __popcll(kept & ((1ull << i) - 1ull));
             const float4 a = s_box[i];
             s_kbox[pos] = a;
             s_karea[pos] = __fmul_rn(__fsub_rn(a.z, a.x), __fsub_rn(a.w, a.y));
-            keep_flag[order2[s + base + i]] = 1;
+            if (cr == 0) keep_flag[order2[s + base + i]] = 1;
           }
         }
         if (threadIdx.x == 0) s_kept = kept;
       }
       __syncthreads();
-      // C: kept boxes of this block suppress the tail
+      // C: kept boxes of this block suppress this CTA's share of the tail (blocks t > blk with t % cluster == rank)
       const int nk = __popcll(s_kept);
-      for (int j = base + 64 + threadIdx.x; j < m; j += kNmsThreads) {
-        if ((s_removed[j >> 5] >> (j & 31)) & 1u) continue;
+      int t0 = blk + 1 + ((cr - (blk + 1)) % kNmsCluster + kNmsCluster) % kNmsCluster;  // first owned block after blk
+      for (int t = t0 + (threadIdx.x >> 6) * kNmsCluster; t < nblk; t += (kNmsThreads >> 6) * kNmsCluster) {
+        const int j = t * 64 + (threadIdx.x & 63);
+        if (j >= m || ((s_removed[j >> 5] >> (j & 31)) & 1u)) continue;
         const float4 b = B[j];
         bool kill = false;
         for (int k = 0; k < nk && !kill; ++k) kill = suppresses(s_kbox[k], s_karea[k], b, thr);
         if (kill) atomicOr(&s_removed[j >> 5], 1u << (j & 31));
       }
-      __syncthreads();
+      cluster.sync();  // (C) of every CTA is complete before the next block is resolved
     }
   }
 }
@@ -258,8 +276,10 @@ int nms_run(const float* boxes, const float* scores, const long long* idxs, int 
   cub::DeviceRadixSort::SortPairs(w.cub_temp, need, w.cls_a, w.cls_b, w.pos_a, w.order2, n, 0, 32, st);
   nms_segments_kernel<<<gb, tb, 0, st>>>(boxes, w.order1, w.order2, w.cls_b, n, w.sboxes, w.seg_start, w.seg_end,
                                          w.num_seg);
-  // CTAs stride over segments; the segment count is only known on the device.
-  const int max_seg = n < 2 * num_sms() ? n : 2 * num_sms();
+  // clusters stride over segments; the segment count is only known on the device
+  int clusters = 2 * num_sms() / kNmsCluster;
+  if (clusters > n) clusters = n;
+  const int max_seg = (clusters < 1 ? 1 : clusters) * kNmsCluster;
   const size_t smem = ((size_t)n / 32 + 4) * 4;
   if (smem > 160 * 1024) return JTSM_ERR_UNSUPPORTED;
   if (smem > 40 * 1024)

@@ -53,8 +53,19 @@ struct PoolWorkspace {
   uint32_t* bdesc;   // [R * PH * PW]  one word per output bin
   float* rscale;     // [R]            row scale (1 when the caller passes none)
   int* slow_count;   // [1]            number of bins without a fast descriptor
-  int* slow_list;    // [R * PH * PW]  their ids (r * PH*PW + bin), in no particular order
+  int* slow_list;    // [R * PH * PW]  their ids (r * PH*PW + bin), in no particular order; bit 30 = does not fit a band
+  unsigned char* bband;  // [R * PH * PW]  row band of the bin (planes larger than shared memory, RmqBands)
 };
+
+// Row bands of a plane that is too large for shared memory (plane + 10 tables = 24 B per cell): band b covers rows
+// [b * S, b * S + Hb) (the last one ends at H); consecutive bands overlap by Hb - S >= the tallest bin a RoI inside
+// the map can have (ceil(H / PH) + 1), so every such bin lies inside the band floor(hstart / S).  nb == 1: the whole
+// plane (S = Hb = H).  Descriptors, table entries and slow-path ranges are band relative.
+struct RmqBands {
+  int nb, S, Hb;
+};
+__host__ __device__ inline int band_of(int hs, const RmqBands& bd) { return min(max(hs, 0) / bd.S, bd.nb - 1); }
+__host__ __device__ inline int band_rows(int b, int H, const RmqBands& bd) { return min(bd.Hb, H - b * bd.S); }
 
 // Per-bin descriptor of the range-max-table kernel.  Table (kh, kw) sits in slot kh + 2*kw of the
 // table block, so the 4 look-ups of a bin are base, base + db, base + dh, base + dh + db (bytes):
@@ -88,6 +99,7 @@ inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int po
   b += align_up((size_t)batch * 4 * 2 + 16, 256);
   b += 2 * align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
   b += align_up((size_t)num_rois * 4, 256);
+  b += align_up((size_t)num_rois * pooled_h * pooled_w, 256);  // bband
   return b + 256;
 }
 
@@ -104,7 +116,8 @@ inline PoolWorkspace carve_pool_workspace(void* ws, int batch, int num_rois, int
   p += align_up((size_t)batch * 4 * 2 + 16, 256);
   w.bdesc = (uint32_t*)p; p += align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
   w.rscale = (float*)p; p += align_up((size_t)num_rois * 4, 256);
-  w.slow_list = (int*)p;
+  w.slow_list = (int*)p; p += align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
+  w.bband = (unsigned char*)p;
   return w;
 }
 

@@ -29,7 +29,8 @@ namespace jtsm {
 constexpr int kPrepRois = 32, kPrepThreads = 256;
 __global__ void __launch_bounds__(kPrepThreads)
 roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, int height, int width, float scale,
-                     int PH, int PW, const float* __restrict__ row_scale, int want_desc, PoolWorkspace ws) {
+                     int PH, int PW, const float* __restrict__ row_scale, int want_desc, RmqBands bands,
+                     PoolWorkspace ws) {
   const int r_base = blockIdx.x * kPrepRois;
   const int r = r_base + threadIdx.x;
   if (threadIdx.x < kPrepRois && r < num_rois) {
@@ -51,14 +52,21 @@ roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, in
   }
   if (!want_desc) return;  // uniform
   __syncthreads();         // the CTA's bin tables are visible to all its threads
-  const int hw = height * width, PP = PH * PW;
+  // descriptors are relative to the bin's row band (one band = the whole plane when it fits shared memory)
+  const int hw_t = bands.Hb * width, PP = PH * PW;
   const int n_local = min(kPrepRois, num_rois - r_base);
   for (int j = threadIdx.x; j < n_local * PP; j += kPrepThreads) {
     const int rl = j / PP, bin = j - rl * PP, ph = bin / PW, pw = bin - ph * PW;
     const int rr = r_base + rl;
-    const uint32_t d = rmq_bin_desc(ws.hbins[(size_t)rr * PH + ph], ws.wbins[(size_t)rr * PW + pw], width, hw);
+    const uint32_t hb = ws.hbins[(size_t)rr * PH + ph];
+    const int b = band_of(range_lo(hb), bands), row0 = b * bands.S;
+    const bool fits = range_hi(hb) <= row0 + band_rows(b, height, bands) || range_hi(hb) <= range_lo(hb);
+    const uint32_t hb_rel = hb - ((uint32_t)row0 | ((uint32_t)row0 << 16));
+    const uint32_t d = fits ? rmq_bin_desc(hb_rel, ws.wbins[(size_t)rr * PW + pw], width, hw_t) : 0u;
     ws.bdesc[(size_t)rr * PP + bin] = d;
-    if (d == 0u) ws.slow_list[atomicAdd(ws.slow_count, 1)] = rr * PP + bin;  // ~2% of the bins
+    ws.bband[(size_t)rr * PP + bin] = (unsigned char)b;
+    if (d == 0u)  // ~2% of the bins; bit 30: taller than a band (RoI reaching far outside the map) -> global-memory scan
+      ws.slow_list[atomicAdd(ws.slow_count, 1)] = (rr * PP + bin) | (fits ? 0 : 0x40000000);
   }
 }
 
@@ -317,9 +325,26 @@ constexpr size_t kMaxPlaneSmem = 200 * 1024;
 
 // The range-max-table kernel applies when plane + tables fit in shared memory (hw <= 9685, which also
 // keeps every descriptor field inside its bits), the batch index fits 11 bits and output offsets 32 bits.
+// Row bands for a plane (RmqBands, roi_bins.cuh): one band when plane + tables fit shared memory, else bands of the
+// largest height whose plane + tables + staging buffer fit, overlapping by the tallest bin of a RoI inside the map.
+// nb = 0: not feasible (very wide maps, where a band would be shorter than ~1.5 bins) -> direct-scan kernels.
+RmqBands pick_bands(int height, int width, int PH) {
+  const long long hw = (long long)height * width;
+  if (hw <= 0 || width > 4096) return {0, 0, 0};
+  if (hw < (1 << 20) && rk_smem_core((int)hw) <= 227 * 1024) return {1, height, height};
+  int Hb = (int)((227 * 1024 - kRkHeader - 64) / (28 * (long long)width));  // 4 (plane) + 20 (tables) + 4 (staging) B / cell
+  while (Hb > 0 && rk_smem_core(Hb * width) + rk_stage_bytes(Hb * width, 4) > 227 * 1024) --Hb;
+  const int O = (height + PH - 1) / PH + 1;
+  const int S = Hb - O;
+  if (Hb < 3 || S < 1 || 3 * S < Hb) return {0, 0, 0};
+  const int nb = (height - O + S - 1) / S;
+  if (nb < 1 || nb > 255) return {0, 0, 0};
+  return {nb, S, Hb};
+}
+
 bool rmq_geometry_ok(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
   const long long hw = (long long)height * width;
-  return hw < 65535 && rmq_smem_bytes((int)hw) <= 227 * 1024 && rk_smem_core((int)hw) <= 227 * 1024 &&
+  return pick_bands(height, width, PH).nb > 0 &&
          (long long)num_rois * channels * PH * PW < 0x7FFFFFFFLL &&
          (long long)num_rois * PH * PW * PH * PW < 0xFFFFFFFFLL &&  // exact magic division of a bin id by PH*PW
          (long long)num_rois * 64 < 0x7FFFFFFFLL &&                // chunk bounds in 32 bits (chunks <= 64)
@@ -347,8 +372,11 @@ int pick_splits(int planes, int num_rois, int ctas_per_sm) {
 template <typename T, typename A, bool kMoi>
 int launch_rmq(const void* input, int batch, int channels, int height, int width, int num_rois, int PH, int PW,
                const PoolWorkspace& ws, const MoiAux& moi, void* output, void* argmax, cudaStream_t st) {
-  const int planes = batch * channels;
-  const int hw = height * width;
+  const RmqBands bands = pick_bands(height, width, PH);
+  if (bands.nb < 1 || (kMoi && bands.nb != 1)) return JTSM_ERR_UNSUPPORTED;
+  const int real_planes = batch * channels;
+  const int planes = real_planes * bands.nb;  // virtual planes: (band, plane)
+  const int hw = bands.Hb * width;            // cells of a band
   {
     // table format: index tables (8 look-ups per bin, LSU bound) by default; keyed entries (5 look-ups, ALU bound and
     // slower on B200: profiles/r2_roi_pool_fwd_keyed.md) on request.  Planes arrive by bulk copy (TMA 1-D) into a raw
@@ -381,15 +409,15 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
     if (chunks > 64) chunks = 64;
     const int items = planes * chunks;
     const int grid = items < max_grid ? items : max_grid;
-    const unsigned long long in_bytes = (unsigned long long)planes * hw * sizeof(T);
+    const unsigned long long in_bytes = (unsigned long long)real_planes * height * width * sizeof(T);
     if (keyed)
       roi_pool_fwd_rmq_kernel<T, A, kMoi, true><<<grid, kRmqThreads, smem, st>>>(
-          (const T*)input, in_bytes, channels, height, width, PH, PW, chunks, items, staged, ws, moi, (T*)output,
-          (A*)argmax);
+          (const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks, items, staged, bands, ws, moi,
+          (T*)output, (A*)argmax);
     else
       roi_pool_fwd_rmq_kernel<T, A, kMoi, false><<<grid, kRmqThreads, smem, st>>>(
-          (const T*)input, in_bytes, channels, height, width, PH, PW, chunks, items, staged, ws, moi, (T*)output,
-          (A*)argmax);
+          (const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks, items, staged, bands, ws, moi,
+          (T*)output, (A*)argmax);
     count_launch();
     return cuda_status();
   }
@@ -429,8 +457,10 @@ int run_prep(const float* rois, int num_rois, int batch, int channels, int heigh
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
   cudaMemsetAsync(ws.ungrouped, 0, 2 * sizeof(int), st);  // ungrouped flag + slow-bin counter
   const int want_desc = force_desc || rmq_eligible(batch, channels, height, width, num_rois, PH, PW);
+  RmqBands bands = pick_bands(height, width, PH);
+  if (bands.nb < 1) bands = {1, height, height};  // descriptors unused then (direct-scan kernels)
   roi_pool_prep_kernel<<<(num_rois + kPrepRois - 1) / kPrepRois, kPrepThreads, 0, st>>>(
-      rois, num_rois, batch, height, width, scale, PH, PW, row_scale, want_desc, ws);
+      rois, num_rois, batch, height, width, scale, PH, PW, row_scale, want_desc, bands, ws);
   count_launch();
   return cuda_status();
 }
@@ -440,7 +470,8 @@ int run_prep(const float* rois, int num_rois, int batch, int channels, int heigh
 // ---- entry points for MOIPool's range-max mode (wsl_pool.cu) ----
 namespace jtsm {
 bool moi_rmq_eligible(int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
-  return rmq_geometry_ok(batch, channels, height, width, num_rois, PH, PW);
+  // the masked pools keep whole planes in shared memory (their visit-list kernels are not banded)
+  return pick_bands(height, width, PH).nb == 1 && rmq_geometry_ok(batch, channels, height, width, num_rois, PH, PW);
 }
 int moi_rmq_prep(const float* rois, int num_rois, int batch, int channels, int height, int width, float scale, int PH,
                  int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st) {

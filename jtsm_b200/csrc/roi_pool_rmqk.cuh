@@ -223,6 +223,22 @@ struct RmqSchedule {
   }
 };
 
+// One (band, plane) of the schedule: "virtual plane" vp = band * planes + plane (band-major, so that neighbouring CTAs
+// serve neighbouring channels of the same band and their output runs share sectors while they are written).
+struct RmqVPlane {
+  int nc, band, row0, cells;  // (image, channel) plane, band, its first row, its cell count
+  size_t elem_off;            // offset of the band's first cell in the input tensor (elements)
+};
+__device__ __forceinline__ RmqVPlane rmq_vplane(int vp, int planes, int H, int W, const RmqBands& bd) {
+  RmqVPlane v;
+  v.band = vp / planes;
+  v.nc = vp - v.band * planes;
+  v.row0 = v.band * bd.S;
+  v.cells = band_rows(v.band, H, bd) * W;
+  v.elem_off = (size_t)v.nc * H * W + (size_t)v.row0 * W;
+  return v;
+}
+
 // Main loop of one (plane, RoI-chunk) item: one fast bin per thread and chain, kRmqBinsPerThread independent chains.
 // Everything is indexed with 32-bit offsets from the kernel's own pointer arguments (the launcher checks the sizes):
 // bin id i -> RoI r = i / PP (magic multiply) -> output element i + r * (C - 1) * PP + c * PP.  Descriptor and row
@@ -232,7 +248,10 @@ template <typename T, typename A, bool kUngrouped, bool kMoi, bool kKeyed>
 __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
                                              const RmqItem& it, int PP, int cpp, unsigned W, unsigned hw,
                                              unsigned magic_pp, const float* __restrict__ mask_scale, int zero_floor,
-                                             T* __restrict__ output, A* __restrict__ argmax) {
+                                             int nb, int band, unsigned arg_off, T* __restrict__ output,
+                                             A* __restrict__ argmax) {
+  // nb > 1 (banded plane): only the bins of row band `band` are served (ws.bband), their table indices are band
+  // relative (arg_off = first cell of the band); warps without a bin of this band skip the look-ups altogether.
   const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
   const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned plane_s = smem_u32(plane), tabs_s = smem_u32(tabs);
@@ -247,6 +266,7 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
       xn[k] = 0u, scn[k] = 0.f, msn[k] = 0.f;
       if (ik < i_end) {
         xn[k] = __ldg(ws.bdesc + ik);
+        if (nb > 1 && (int)__ldg(ws.bband + ik) != band) xn[k] = 0u;  // another band's bin
         scn[k] = __ldg(ws.rscale + __umulhi(ik, magic_pp));
         if (kMoi) msn[k] = __ldg(mask_scale + __umulhi(ik, magic_pp));
       }
@@ -264,6 +284,12 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
     }
     i += K * kRmqThreads;
     fetch(i);
+    if (nb > 1) {  // uniform per warp: nothing of this band in the round
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < K; ++k) any |= (int)x[k] < 0;
+      if (!__any_sync(__activemask(), any)) continue;
+    }
     RmqCand best[K];
 #pragma unroll
     for (int k = 0; k < K; ++k)
@@ -280,7 +306,7 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
         const bool floor0 = kMoi && zero_floor;
         const bool none = floor0 ? !(best[k].v > 0.f) : !(best[k].v > -FLT_MAX);
         output[o[k]] = Elem<T>::from_f(floor0 && none ? 0.f : __fmul_rn(v, sc[k]));
-        argmax[o[k]] = none ? Arg<A>::enc(-1) : (A)best[k].i;
+        argmax[o[k]] = none ? Arg<A>::enc(-1) : (A)(best[k].i + arg_off);
       }
     }
   }
@@ -291,21 +317,43 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
 // path; the list is short and every CTA filters it for the RoI range it has just served.
 template <typename T, typename A, bool kMoi, bool kKeyed>
 __device__ __forceinline__ void rk_slow_pass(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
-                                             int n, int c, int r_lo, int r_hi, bool ungrouped, int channels, int hw,
-                                             int W, int PH, int PW, T* __restrict__ output, A* __restrict__ argmax) {
+                                             const T* __restrict__ input, const RmqVPlane& vpl, int r_lo, int r_hi,
+                                             bool ungrouped, int channels, int hw, int H, int W, int PH, int PW,
+                                             const RmqBands& bands, T* __restrict__ output, A* __restrict__ argmax) {
   const int PP = PH * PW;
   if (kMoi) return;  // the visit-list kernel answers every bin without a fast descriptor
+  const int n = vpl.nc / channels, c = vpl.nc - n * channels;
   const int ns = __ldg(ws.slow_count);
   for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
-    const int id = __ldg(ws.slow_list + j);
+    const int e = __ldg(ws.slow_list + j);
+    const int id = e & 0x3FFFFFFF;
     const int rr = id / PP, b = id - rr * PP;
     if (rr < r_lo || rr >= r_hi) continue;
     if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
     const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
     const int ph = b / PW, pw = b - ph * PW;
     const uint32_t hb = __ldg(ws.hbins + (size_t)rr * PH + ph), wb = __ldg(ws.wbins + (size_t)rr * PW + pw);
-    RmqCand best = kKeyed ? rk_query_slow(plane, tabs, hw, W, hb, wb) : rmq_query_slow(plane, tabs, hw, W, hb, wb);
-    if (best.i != 0xFFFFFFFFu && !(best.v > -FLT_MAX)) best.i = 0xFFFFFFFFu;  // non-empty, nothing beats -FLT_MAX
+    RmqCand best;
+    if (e & 0x40000000) {
+      // taller than a band (a RoI reaching far outside the map): scanned from global memory, once, by band 0's CTA
+      if (vpl.band != 0) continue;
+      const T* src = input + (size_t)vpl.nc * H * W;
+      best = {-FLT_MAX, 0xFFFFFFFFu};
+      for (int h = range_lo(hb); h < range_hi(hb); ++h)
+        for (int w = range_lo(wb); w < range_hi(wb); ++w) {
+          const float v = Elem<T>::to_f(src[h * W + w]);
+          if (v > best.v) best = {v, (unsigned)(h * W + w)};
+        }
+      if (range_hi(wb) <= range_lo(wb)) best.v = 0.f;  // empty in w (h is non-empty here)
+    } else {
+      if (band_of(range_lo(hb), bands) != vpl.band) continue;
+      const uint32_t hb_rel = hb - ((uint32_t)vpl.row0 | ((uint32_t)vpl.row0 << 16));
+      best = kKeyed ? rk_query_slow(plane, tabs, hw, W, hb_rel, wb) : rmq_query_slow(plane, tabs, hw, W, hb_rel, wb);
+      if (best.i != 0xFFFFFFFFu) {
+        if (!(best.v > -FLT_MAX)) best.i = 0xFFFFFFFFu;  // non-empty, nothing beats -FLT_MAX
+        else best.i += (unsigned)(vpl.row0 * W);
+      }
+    }
     output[so] = Elem<T>::from_f(__fmul_rn(best.v, __ldg(ws.rscale + rr)));
     argmax[so] = Arg<A>::enc((int)best.i);
   }
@@ -320,12 +368,12 @@ __host__ __device__ inline size_t rk_stage_bytes(int hw, int esz) { return (((si
 
 template <typename T, typename A, bool kMoi, bool kKeyed>
 __global__ void __launch_bounds__(kRmqThreads, 1)
-roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_bytes, int channels, int H, int W,
-                         int PH, int PW, int chunks, int num_items, int staged, PoolWorkspace ws, MoiAux moi,
-                         T* __restrict__ output, A* __restrict__ argmax) {
+roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_bytes, int planes, int channels, int H,
+                         int W, int PH, int PW, int chunks, int num_items, int staged, RmqBands bands,
+                         PoolWorkspace ws, MoiAux moi, T* __restrict__ output, A* __restrict__ argmax) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   if (kMoi && !moi_rmq_gate(moi.slow_total, moi.total_bins, moi.gate_pct)) return;  // uniform: the list kernel runs
-  const int hw = H * W;
+  const int hw = bands.Hb * W;  // cells of a full band = table stride (the whole plane when nb == 1)
   unsigned long long* bar = (unsigned long long*)smem_raw;
   float* stats = (float*)(smem_raw + 16);      // [0] lo, [1] scale
   float* red = (float*)(smem_raw + 32);        // [32 warps][2] partial min / max
@@ -338,20 +386,20 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
   // byte offsets are taken from the 16-byte aligned address below `input` (32-bit: the launcher bounds the tensor size)
   const unsigned a0 = (unsigned)((uintptr_t)input & 15u), in_end = a0 + (unsigned)input_bytes;
   const unsigned char* in_al = (const unsigned char*)input - a0;
-  const unsigned plane_bytes = (unsigned)hw * (unsigned)sizeof(T);
 
   RmqSchedule sch;
   sch.init(num_items, chunks);
-  int nc, chunk;
-  sch.first(nc, chunk);
+  int vp, chunk;
+  sch.first(vp, chunk);
 
-  // The 16-byte aligned window around plane `pl`; false when it would leave the tensor (first / last plane of a
-  // tensor whose ends are not 16-byte aligned): that plane is then read with plain loads.  Uniform per CTA.
+  // The 16-byte aligned window around the cells of virtual plane `pl`; false when it would leave the tensor (first /
+  // last plane of a tensor whose ends are not 16-byte aligned): read with plain loads then.  Uniform per CTA.
   auto window = [&](int pl, unsigned& src_off, unsigned& off, unsigned& bytes) {
-    const unsigned start = a0 + (unsigned)pl * plane_bytes;
+    const RmqVPlane v = rmq_vplane(pl, planes, H, W, bands);
+    const unsigned start = a0 + (unsigned)(v.elem_off * sizeof(T));
     src_off = start & ~15u;
     off = start - src_off;
-    bytes = (off + plane_bytes + 15u) & ~15u;
+    bytes = (off + (unsigned)v.cells * (unsigned)sizeof(T) + 15u) & ~15u;
     return src_off >= a0 && src_off + bytes <= in_end;  // only bytes of the tensor itself are ever fetched
   };
   auto issue = [&](int pl) {
@@ -373,45 +421,48 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
     __syncthreads();
   }
   unsigned parity = 0;
-  int in_flight = -1;  // plane whose bytes are on their way into (or already in) the staging buffer
-  if (staged && sch.my_items > 0 && issue(nc)) in_flight = nc;
+  int in_flight = -1;  // virtual plane whose bytes are on their way into (or already in) the staging buffer
+  if (staged && sch.my_items > 0 && issue(vp)) in_flight = vp;
 
-  int cur_plane = -1;
+  int cur_vp = -1;
+  RmqVPlane cur{};
   int r_lo = 0, r_hi = 0;
   if (!kKeyed)  // index tables: the identity level (0,0), slot 0, never changes
     for (int p = threadIdx.x; p < hw; p += kRmqThreads) tabs[p] = (unsigned short)p;
 
   for (int idx = 0; idx < sch.my_items; ++idx) {
-    if (idx > 0) sch.advance(idx, nc, chunk);
-    const RmqItem it = rmq_item(nc, chunk, chunks, channels, ws);
-    if (nc != cur_plane) {
-      if (cur_plane >= 0)
-        rk_slow_pass<T, A, kMoi, kKeyed>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi,
-                                         ungrouped, channels, hw, W, PH, PW, output, argmax);
+    if (idx > 0) sch.advance(idx, vp, chunk);
+    const RmqVPlane v = rmq_vplane(vp, planes, H, W, bands);
+    const RmqItem it = rmq_item(v.nc, chunk, chunks, channels, ws);
+    if (vp != cur_vp) {
+      if (cur_vp >= 0)
+        rk_slow_pass<T, A, kMoi, kKeyed>(plane, tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW,
+                                         bands, output, argmax);
       __syncthreads();  // everyone is done with the old plane and tables
       // ---- unpack: staged bytes (or global memory) -> fp32 plane, sanitised; min / max of the plane
       float lo = FLT_MAX, hi = -FLT_MAX;
-      if (in_flight == nc) {
+      if (in_flight == vp) {
         mbar_wait(bar, parity);
         parity ^= 1u;
         unsigned src_off, off, bytes;
-        window(nc, src_off, off, bytes);
+        window(vp, src_off, off, bytes);
         const T* sp = (const T*)(stage + off);
-        for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
-          float v = Elem<T>::to_f(sp[p]);
-          v = v > -FLT_MAX ? v : -FLT_MAX;
-          plane[p] = v;
-          lo = fminf(lo, v), hi = fmaxf(hi, v);
+        for (int p = threadIdx.x; p < v.cells; p += kRmqThreads) {
+          float x = Elem<T>::to_f(sp[p]);
+          x = x > -FLT_MAX ? x : -FLT_MAX;
+          plane[p] = x;
+          lo = fminf(lo, x), hi = fmaxf(hi, x);
         }
       } else {
-        const T* src = input + (size_t)nc * hw;
-        for (int p = threadIdx.x; p < hw; p += kRmqThreads) {
-          float v = Elem<T>::to_f(src[p]);
-          v = v > -FLT_MAX ? v : -FLT_MAX;
-          plane[p] = v;
-          lo = fminf(lo, v), hi = fmaxf(hi, v);
+        const T* src = input + v.elem_off;
+        for (int p = threadIdx.x; p < v.cells; p += kRmqThreads) {
+          float x = Elem<T>::to_f(src[p]);
+          x = x > -FLT_MAX ? x : -FLT_MAX;
+          plane[p] = x;
+          lo = fminf(lo, x), hi = fmaxf(hi, x);
         }
       }
+      for (int p = v.cells + threadIdx.x; p < hw; p += kRmqThreads) plane[p] = -FLT_MAX;  // a shorter last band
       if (kKeyed) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -437,11 +488,12 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
       // the next plane this CTA will serve streams in behind the build and the queries of this one
       in_flight = -1;
       if (staged) {
-        const int nx = sch.next_plane(idx, nc, chunk);
+        const int nx = sch.next_plane(idx, vp, chunk);
         if (nx >= 0 && issue(nx)) in_flight = nx;
       }
       __syncthreads();
-      cur_plane = nc;
+      cur_vp = vp;
+      cur = v;
       r_lo = it.r0, r_hi = it.r0;
       if (kKeyed)
         rk_build_tables(plane, tabs, hw, W, stats[0], stats[1]);
@@ -451,14 +503,16 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
     if (it.nr > 0) r_hi = it.r0 + it.nr;
     if (ungrouped)
       rk_main_loop<T, A, true, kMoi, kKeyed>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
-                                             moi.mask_scale, moi.zero_floor, output, argmax);
+                                             moi.mask_scale, moi.zero_floor, bands.nb, v.band, (unsigned)(v.row0 * W),
+                                             output, argmax);
     else
       rk_main_loop<T, A, false, kMoi, kKeyed>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
-                                              moi.mask_scale, moi.zero_floor, output, argmax);
+                                              moi.mask_scale, moi.zero_floor, bands.nb, v.band, (unsigned)(v.row0 * W),
+                                              output, argmax);
   }
-  if (cur_plane >= 0)
-    rk_slow_pass<T, A, kMoi, kKeyed>(plane, tabs, ws, cur_plane / channels, cur_plane % channels, r_lo, r_hi, ungrouped,
-                                     channels, hw, W, PH, PW, output, argmax);
+  if (cur_vp >= 0)
+    rk_slow_pass<T, A, kMoi, kKeyed>(plane, tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW, bands,
+                                     output, argmax);
 }
 
 }  // namespace jtsm

@@ -256,3 +256,47 @@ def test_roi_pool_keyed_tables_equal_index_tables(cuda):
             for name in ("keyed+tma", "keyed", "index", "index-no-tma"):
                 assert torch.equal(res[name][0], res["scan"][0]), (name, dt, shape)
                 assert torch.equal(res[name][1], res["scan"][1]), (name, dt, shape)
+
+
+@pytest.mark.parametrize("h,w,scale,pooled,dtype", [
+    (150, 200, 1 / 8.0, (7, 7), torch.float32),    # c4's largest augmentation: 8 row bands
+    (108, 144, 1 / 8.0, (7, 7), torch.bfloat16),   # 4 bands, 16-bit planes through the staging buffer
+    (86, 115, 1 / 8.0, (14, 14), torch.float32),   # odd width (unaligned band starts), 14 x 14 bins
+    (200, 60, 1 / 8.0, (3, 5), torch.float16),     # tall narrow map, few tall bins
+])
+def test_roi_pool_banded_planes_vs_oracle(cuda, oracle, h, w, scale, pooled, dtype):
+    """Planes too large for shared memory are served in overlapping row bands by the same range-max kernel; boxes that
+    reach far outside the map (bins taller than a band) take the global-memory scan.  Values / argmax bit-exact."""
+    from jtsm_b200 import _lib, ops
+
+    img_h, img_w = int(h / scale), int(w / scale)
+    g = synth.generator(1000 + h + w)
+    x = (synth.feature_map(g, 2, 5, h, w) - 0.2).to(dtype)
+    boxes = [synth.proposals(g, 400, img_h, img_w) for _ in range(2)]
+    extreme = torch.tensor([[0, 0, img_w - 1, img_h - 1], [-3.0 * img_w, -2.0 * img_h, 2.0 * img_w, 4.0 * img_h],
+                            [10, -5.0 * img_h, 60, 6.0 * img_h], [-500, 20, img_w + 900, 40], [5, 5, 5, 5],
+                            [img_w + 50, img_h + 50, img_w + 90, img_h + 90]], dtype=torch.float32)
+    boxes[1][:6] = extreme
+    rois = synth.rois_from_boxes(boxes)
+    ref, rarg = oracle.roi_pool_forward(x.float().numpy(), rois.numpy(), scale, pooled)
+    res = {}
+    try:
+        for name, (keys, tma, algo) in {"bands": (0, 1, 0), "bands-no-tma": (0, 0, 0), "bands-keyed": (1, 1, 0),
+                                        "scan": (0, 1, 1)}.items():
+            _lib.set_tuning("roi_pool_fwd_keys", keys)
+            _lib.set_tuning("roi_pool_fwd_tma", tma)
+            _lib.set_tuning("roi_pool_fwd_algo", algo)
+            res[name] = ops.roi_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled)
+    finally:
+        _lib.set_tuning("roi_pool_fwd_keys", 0)
+        _lib.set_tuning("roi_pool_fwd_tma", 1)
+        _lib.set_tuning("roi_pool_fwd_algo", 0)
+    for name, (out, arg) in res.items():
+        assert np.array_equal(out.float().cpu().numpy(), ref), name
+        assert np.array_equal(arg.cpu().numpy(), rarg), name
+    # u16 argmax + row scale + backward through the banded forward's argmax
+    sc = torch.rand(rois.shape[0], generator=g) + 0.5
+    out, arg = ops.roi_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled, row_scale=sc.to(cuda), argmax_dtype=torch.int16)
+    assert np.array_equal(_decode(arg), rarg)
+    if dtype == torch.float32:
+        assert np.array_equal(out.cpu().numpy(), ref * sc.numpy()[:, None, None, None])
