@@ -380,7 +380,7 @@ def train_leg(a, wl, dev, world, rank, barrier):
     from jtsm_b200 import trainstep
 
     cfg = wl["cfg"]
-    ts = trainstep.TrainStep(cfg, dev, world=world)
+    ts = trainstep.TrainStep(cfg, dev, world=world, tf32=True)
     batch = ts.make_batch(wl)
     steps = max(3, min(a.steps, 10))
 

@@ -320,6 +320,24 @@ JTSM_API int jtsm_batched_nms(const float* boxes, const float* scores, const lon
                               void* stream);
 
 /* ------------------------------------------------------------------------
+ * RoIPool -> fc6 fused on the tensor cores (inference: no argmax is produced).  Replaces the chain
+ *   box_pooler -> * (objectness_logits + 1) -> flatten -> fc6 (+ ReLU)
+ * of projects/WSL/wsl/modeling/roi_heads/roi_heads_oicr.py:391-403 and box_head.py:59-68,90 without materialising the
+ * pooled [R, C, P, P] tensor: the pooled values are produced as bf16 A-operand tiles in shared memory and consumed by
+ * tcgen05.mma (fp32 accumulation in TMEM); the weight tiles arrive by TMA.
+ * feat      [batch, height, width, channels] bf16, CHANNELS-LAST (a staged copy of the NCHW map), channels % 64 == 0
+ * weight    [out_features, P*P*channels] bf16, BIN-MAJOR columns: weight[n, bin*channels + c] = fc6.weight[n, c*P*P + bin]
+ *           (a one-time re-layout of the checkpoint), out_features % 512 == 0
+ * out       [num_rois, out_features] fp32 = relu?(bias + pooled_bf16 x weight^T), pooled_bf16 = bf16(max * row_scale)
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_pool_fc6_workspace_bytes(int batch, int num_rois, int pooled_h, int pooled_w);
+JTSM_API int jtsm_pool_fc6_forward(const void* feat_nhwc_bf16, const float* rois, int batch, int channels,
+                                   int height, int width, int num_rois, float spatial_scale, int pooled_h,
+                                   int pooled_w, const float* row_scale, const void* weight_binmajor_bf16,
+                                   const float* bias, int out_features, int relu, float* out,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
  * fast_rcnn_inference_single_image on the device
  * (projects/WSL/wsl/modeling/roi_heads/fast_rcnn_oicr.py:95-163 == fast_rcnn_wsddn.py:94-162; the stock twin
  * detectron2/modeling/roi_heads/fast_rcnn.py is what GeneralizedRCNNWithTTAAVG calls at test_time_augmentation_avg.py:393):

@@ -385,11 +385,13 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
     const size_t stage = rk_stage_bytes(hw, (int)sizeof(T));
     const int staged = rk_smem_core(hw) + stage <= 227 * 1024 && tuning("roi_pool_fwd_tma", 1);
     const size_t smem = rk_smem_core(hw) + (staged ? stage : 0);
+    // kernel instantiation: table format x banded (the masked pools are single band only)
+    auto kern = roi_pool_fwd_rmq_kernel<T, A, kMoi, false, false>;
+    if (keyed && bands.nb > 1) kern = roi_pool_fwd_rmq_kernel<T, A, kMoi, true, !kMoi>;
+    else if (keyed) kern = roi_pool_fwd_rmq_kernel<T, A, kMoi, true, false>;
+    else if (bands.nb > 1) kern = roi_pool_fwd_rmq_kernel<T, A, kMoi, false, !kMoi>;
     // per call: the attribute is per device, and one process may drive several GPUs
-    if (keyed)
-      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A, kMoi, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    else
-      cudaFuncSetAttribute(roi_pool_fwd_rmq_kernel<T, A, kMoi, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     const int per_sm = (int)((227 * 1024) / (smem + 1024)) >= 2 ? 2 : 1;  // 1024-thread CTAs
     const int max_grid = num_sms() * per_sm;
     // RoI chunks per plane: the planes of the last, partial round (planes % grid) are cut into chunks and dealt to
@@ -410,14 +412,8 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
     const int items = planes * chunks;
     const int grid = items < max_grid ? items : max_grid;
     const unsigned long long in_bytes = (unsigned long long)real_planes * height * width * sizeof(T);
-    if (keyed)
-      roi_pool_fwd_rmq_kernel<T, A, kMoi, true><<<grid, kRmqThreads, smem, st>>>(
-          (const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks, items, staged, bands, ws, moi,
-          (T*)output, (A*)argmax);
-    else
-      roi_pool_fwd_rmq_kernel<T, A, kMoi, false><<<grid, kRmqThreads, smem, st>>>(
-          (const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks, items, staged, bands, ws, moi,
-          (T*)output, (A*)argmax);
+    kern<<<grid, kRmqThreads, smem, st>>>((const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks,
+                                          items, staged, bands, ws, moi, (T*)output, (A*)argmax);
     count_launch();
     return cuda_status();
   }

@@ -244,14 +244,15 @@ __device__ __forceinline__ RmqVPlane rmq_vplane(int vp, int planes, int H, int W
 // bin id i -> RoI r = i / PP (magic multiply) -> output element i + r * (C - 1) * PP + c * PP.  Descriptor and row
 // scale are loaded one round ahead.  x = 0 marks a slow bin (left to the list) or an inactive thread: the branch-free
 // look-ups then run on offset 0, which is harmless.  kKeyed: table format (keyed entries / absolute indices).
-template <typename T, typename A, bool kUngrouped, bool kMoi, bool kKeyed>
+template <typename T, typename A, bool kUngrouped, bool kMoi, bool kKeyed, bool kBanded>
 __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
                                              const RmqItem& it, int PP, int cpp, unsigned W, unsigned hw,
                                              unsigned magic_pp, const float* __restrict__ mask_scale, int zero_floor,
                                              int nb, int band, unsigned arg_off, T* __restrict__ output,
                                              A* __restrict__ argmax) {
-  // nb > 1 (banded plane): only the bins of row band `band` are served (ws.bband), their table indices are band
-  // relative (arg_off = first cell of the band); warps without a bin of this band skip the look-ups altogether.
+  // kBanded (plane cut into row bands): only the bins of row band `band` are served (ws.bband), their table indices
+  // are band relative (arg_off = first cell of the band); warps without a bin of this band skip the look-ups.  The
+  // single-band instantiation compiles to the code without any of it.
   const unsigned i_end = (unsigned)((it.r0 + it.nr) * PP);
   const unsigned o_c = (unsigned)(it.c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned plane_s = smem_u32(plane), tabs_s = smem_u32(tabs);
@@ -266,7 +267,7 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
       xn[k] = 0u, scn[k] = 0.f, msn[k] = 0.f;
       if (ik < i_end) {
         xn[k] = __ldg(ws.bdesc + ik);
-        if (nb > 1 && (int)__ldg(ws.bband + ik) != band) xn[k] = 0u;  // another band's bin
+        if (kBanded && (int)__ldg(ws.bband + ik) != band) xn[k] = 0u;  // another band's bin
         scn[k] = __ldg(ws.rscale + __umulhi(ik, magic_pp));
         if (kMoi) msn[k] = __ldg(mask_scale + __umulhi(ik, magic_pp));
       }
@@ -284,7 +285,7 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
     }
     i += K * kRmqThreads;
     fetch(i);
-    if (nb > 1) {  // uniform per warp: nothing of this band in the round
+    if (kBanded) {  // uniform per warp: nothing of this band in the round
       bool any = false;
 #pragma unroll
       for (int k = 0; k < K; ++k) any |= (int)x[k] < 0;
@@ -306,7 +307,7 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
         const bool floor0 = kMoi && zero_floor;
         const bool none = floor0 ? !(best[k].v > 0.f) : !(best[k].v > -FLT_MAX);
         output[o[k]] = Elem<T>::from_f(floor0 && none ? 0.f : __fmul_rn(v, sc[k]));
-        argmax[o[k]] = none ? Arg<A>::enc(-1) : (A)(best[k].i + arg_off);
+        argmax[o[k]] = none ? Arg<A>::enc(-1) : (A)(kBanded ? best[k].i + arg_off : best[k].i);
       }
     }
   }
@@ -366,7 +367,7 @@ __host__ __device__ inline size_t rk_smem_core(int hw) {
 }
 __host__ __device__ inline size_t rk_stage_bytes(int hw, int esz) { return (((size_t)hw * esz + 15) & ~(size_t)15) + 32; }
 
-template <typename T, typename A, bool kMoi, bool kKeyed>
+template <typename T, typename A, bool kMoi, bool kKeyed, bool kBanded>
 __global__ void __launch_bounds__(kRmqThreads, 1)
 roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_bytes, int planes, int channels, int H,
                          int W, int PH, int PW, int chunks, int num_items, int staged, RmqBands bands,
@@ -462,7 +463,8 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
           lo = fminf(lo, x), hi = fmaxf(hi, x);
         }
       }
-      for (int p = v.cells + threadIdx.x; p < hw; p += kRmqThreads) plane[p] = -FLT_MAX;  // a shorter last band
+      if (kBanded)
+        for (int p = v.cells + threadIdx.x; p < hw; p += kRmqThreads) plane[p] = -FLT_MAX;  // a shorter last band
       if (kKeyed) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -502,11 +504,11 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
     }
     if (it.nr > 0) r_hi = it.r0 + it.nr;
     if (ungrouped)
-      rk_main_loop<T, A, true, kMoi, kKeyed>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
+      rk_main_loop<T, A, true, kMoi, kKeyed, kBanded>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
                                              moi.mask_scale, moi.zero_floor, bands.nb, v.band, (unsigned)(v.row0 * W),
                                              output, argmax);
     else
-      rk_main_loop<T, A, false, kMoi, kKeyed>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
+      rk_main_loop<T, A, false, kMoi, kKeyed, kBanded>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
                                               moi.mask_scale, moi.zero_floor, bands.nb, v.band, (unsigned)(v.row0 * W),
                                               output, argmax);
   }

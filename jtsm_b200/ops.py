@@ -738,3 +738,43 @@ def pcl_loss_backward(pcl_probs, labels, cls_loss_weights, gt_assignment, pc_lab
         check(lib().jtsm_pcl_loss_backward(_ptr(P), *[_ptr(x) for x in v], r, c, v[3].numel(), _ptr(grad), _stream()),
               "pcl_loss_backward")
     return grad
+
+
+# --------------------------------------------------------------------------- pool -> fc6 on the tensor cores
+def fc6_weight_binmajor(weight, channels, pooled):
+    """fc6.weight [N, C*P*P] (column = c*P*P + bin, what flatten([R, C, P, P]) feeds) -> bf16 [N, P*P*C] with
+    column = bin*C + c: 64 consecutive columns are 64 consecutive channels of one bin.  One-time re-layout."""
+    ph, pw = _pair(pooled)
+    n = weight.shape[0]
+    return weight.detach().view(n, channels, ph * pw).permute(0, 2, 1).reshape(n, ph * pw * channels) \
+        .to(torch.bfloat16).contiguous()
+
+
+def pool_fc6_forward(feat_nhwc, rois, spatial_scale, output_size, weight_binmajor, bias, row_scale=None, relu=True):
+    """relu(fc6(flatten(roi_pool(x, rois) * row_scale))) without the pooled tensor: feat_nhwc [N, H, W, C] bf16
+    (channels last), weight_binmajor from fc6_weight_binmajor -> [R, out_features] fp32."""
+    _require_cuda(feat_nhwc, rois, weight_binmajor, bias, row_scale)
+    if feat_nhwc.dtype != torch.bfloat16 or weight_binmajor.dtype != torch.bfloat16:
+        raise RuntimeError("jtsm_b200.pool_fc6_forward: bf16 feature map (NHWC) and bf16 bin-major weight expected")
+    ph, pw = _pair(output_size)
+    n, h, w, c = feat_nhwc.shape
+    r = rois.size(0)
+    feat = feat_nhwc.contiguous()
+    W = weight_binmajor.contiguous()
+    nout = W.shape[0]
+    if W.shape[1] != ph * pw * c:
+        raise RuntimeError("jtsm_b200.pool_fc6_forward: weight has %d columns, expected %d" % (W.shape[1], ph * pw * c))
+    rois = _rois_f32(rois)
+    out = torch.empty((r, nout), dtype=torch.float32, device=feat.device)
+    if r == 0:
+        return out
+    rs = _f32c(row_scale) if row_scale is not None else None
+    b = _f32c(bias)
+    L = lib()
+    wsb = L.jtsm_pool_fc6_workspace_bytes(n, r, ph, pw)
+    ws = _workspace(wsb, feat.device)
+    with torch.cuda.device(feat.device):
+        check(L.jtsm_pool_fc6_forward(_ptr(feat), _ptr(rois), n, c, h, w, r, float(spatial_scale), ph, pw, _ptr(rs), _ptr(W),
+                                      _ptr(b), nout, int(bool(relu)), _ptr(out), _ptr(ws), wsb, _stream()),
+              "pool_fc6_forward")
+    return out

@@ -41,9 +41,9 @@ def build_heads(cfg, fc_dims=(4096, 4096)):
 
 
 class TrainStep:
-    def __init__(self, cfg, device, world=1, fc_dims=(4096, 4096), lr=1e-3, tf32=True):
+    def __init__(self, cfg, device, world=1, fc_dims=(4096, 4096), lr=1e-3, tf32=False):
         self.cfg, self.dev, self.world = cfg, device, world
-        if tf32:  # the fc GEMMs are torch's; TF32 tensor cores keep fp32 storage / fp32 accumulate
+        if tf32:  # the fc GEMMs are torch's; TF32 tensor cores keep fp32 storage / fp32 accumulate (process-wide switch)
             torch.backends.cuda.matmul.allow_tf32 = True
         torch.manual_seed(1234)  # identical initial replicas on every rank
         self.heads = build_heads(cfg, fc_dims).to(device)

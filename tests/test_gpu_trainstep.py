@@ -46,11 +46,11 @@ def test_roi_heads_fused_objectness_equals_reference_order_of_operations(cuda):
 @pytest.mark.parametrize("name,over", [("c2", {}), ("c3", dict(C=12, R=200, K=80))])
 def test_train_step_runs_and_learns(cuda, name, over):
     """A few SGD iterations on one fixed batch: finite losses, every trainable parameter receives a gradient, the MIL
-    loss goes down (c3: two images per step, box regression on)."""
+    loss falls by more than 10 % (c3: two images per step, box regression on)."""
     from jtsm_b200 import trainstep
 
     wl = _small(name, **over)
-    ts = trainstep.TrainStep(wl["cfg"], cuda, fc_dims=(96, 64), lr=5e-2)
+    ts = trainstep.TrainStep(wl["cfg"], cuda, fc_dims=(96, 64), lr=1e-2)
     batch = ts.make_batch(wl)
     hist = []
     for i in range(12):
@@ -61,7 +61,7 @@ def test_train_step_runs_and_learns(cuda, name, over):
             missing = [n for n, p in ts.heads.named_parameters() if p.requires_grad and p.grad is None]
             assert not missing, missing
             assert batch["feat"].grad is not None and float(batch["feat"].grad.abs().max()) > 0
-    assert hist[-1] < hist[0], hist
+    assert min(hist) < 0.9 * hist[0], hist
     expect = {"loss_cls"} | {"loss_cls_r%d" % k for k in range(wl["cfg"]["Kr"])}
     if wl["cfg"]["reg"]:
         expect |= {"loss_box_reg_r%d" % k for k in range(wl["cfg"]["Kr"])}
