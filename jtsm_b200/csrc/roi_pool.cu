@@ -332,8 +332,10 @@ RmqBands pick_bands(int height, int width, int PH) {
   const long long hw = (long long)height * width;
   if (hw <= 0 || width > 4096) return {0, 0, 0};
   if (hw < (1 << 20) && rk_smem_core((int)hw) <= 227 * 1024) return {1, height, height};
-  int Hb = (int)((227 * 1024 - kRkHeader - 64) / (28 * (long long)width));  // 4 (plane) + 20 (tables) + 4 (staging) B / cell
-  while (Hb > 0 && rk_smem_core(Hb * width) + rk_stage_bytes(Hb * width, 4) > 227 * 1024) --Hb;
+  // bands as tall as plane + tables allow (24 B per cell): no staging buffer in banded mode -- fewer bands (fewer table
+  // builds and descriptor sweeps per plane) are worth more than the bulk-copy fetch (150 x 200: 6 bands instead of 8)
+  int Hb = (int)((227 * 1024 - kRkHeader - 64) / (24 * (long long)width));
+  while (Hb > 0 && rk_smem_core(Hb * width) > 227 * 1024) --Hb;
   const int O = (height + PH - 1) / PH + 1;
   const int S = Hb - O;
   if (Hb < 3 || S < 1 || 3 * S < Hb) return {0, 0, 0};
