@@ -256,6 +256,19 @@ JTSM_API int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_clas
                                int num_thresholds, long long* matched_idx, float* matched_iou,
                                long long* gt_classes, float* gt_weights, float* gt_scores, float* gt_boxes,
                                float* loss_weights, int* counters, void* stream);
+/* jtsm_refine_match with the number of seeds per image read from DEVICE memory, so that seed sets whose size is data
+ * dependent (thresholded get_pgt_top_k, roi_heads_oicr.py:754-760; the NMS survivors of get_pgt_mist, :573-581) need no
+ * host read and the branch can sit inside a CUDA graph: image n owns the padded slot [seed_offsets[n],
+ * seed_offsets[n+1]) of pgt_*, of which the first min(seed_counts[n], slot size) entries are seeds.
+ * seed_counts int32 [num_images] DEVICE (NULL: every slot is full == jtsm_refine_match); max_seeds_per_image bounds the
+ * SLOT size. */
+JTSM_API int jtsm_refine_match_counted(const float* pgt_boxes, const long long* pgt_classes, const float* pgt_scores,
+                                       const float* pgt_weights, const int* seed_offsets, const int* seed_counts,
+                                       int max_seeds_per_image, const float* proposals, const int* seg_offsets,
+                                       int num_images, int num_rois, int num_classes, float iou_t0, float iou_t1,
+                                       int label0, int label1, int label2, int num_thresholds, long long* matched_idx,
+                                       float* matched_iou, long long* gt_classes, float* gt_weights, float* gt_scores,
+                                       float* gt_boxes, float* loss_weights, int* counters, void* stream);
 JTSM_API size_t jtsm_refine_workspace_bytes(void);
 /* Weighted softmax cross-entropy, forward + backward + probabilities in one launch
  * (OICROutputs.softmax_cross_entropy_loss + _log_accuracy, fast_rcnn_oicr.py:252-298; predict_probs :744-762):

@@ -69,13 +69,15 @@ refine_assign_kernel(const float* __restrict__ prev_scores, int score_stride,
                      float* __restrict__ gt_weights, float* __restrict__ gt_scores,
                      float* __restrict__ gt_boxes, float* __restrict__ loss_weights,
                      int* __restrict__ counters /* [N*3] fg,bg,ignore ; then [1] valid; zeroed by the caller */,
-                     int num_images) {
+                     int num_images, const int* __restrict__ seed_counts /* optional: device-side seeds per image */) {
   extern __shared__ float4 seeds[];  // [G] boxes, then float area[G], weight[G], score[G], int cls[G], cand_v[G], cand_i[G]
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank(), nrank = (int)cluster.num_blocks();
   const int n = blockIdx.x / nrank;
   const int r0 = seg[n], r1 = seg[n + 1];
-  const int g0 = cls_off[n], G = cls_off[n + 1] - g0;
+  const int g0 = cls_off[n];
+  // caller-supplied seeds may come padded: slot [cls_off[n], cls_off[n+1]) with seed_counts[n] of them in use
+  const int G = seed_counts ? min(max(seed_counts[n], 0), cls_off[n + 1] - g0) : cls_off[n + 1] - g0;
   float* s_area = (float*)(seeds + G);
   float* s_weight = s_area + G;
   float* s_score = s_weight + G;
@@ -560,18 +562,19 @@ extern "C" int jtsm_refine_assign(
   launch_assign(num_images, smem, st, prev_scores, score_stride, prev_boxes, boxes_per_row, proposals, seg_offsets,
                 num_classes, img_cls_offsets, img_cls_ids, img_scores, mp, pgt_boxes, pgt_classes, pgt_scores,
                 pgt_weights, matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes, loss_weights,
-                counters, num_images);
+                counters, num_images, (const int*)nullptr);
   count_launch();
   return cuda_status();
 }
 
-extern "C" int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_classes, const float* pgt_scores,
-                                 const float* pgt_weights, const int* seed_offsets, int max_seeds_per_image,
-                                 const float* proposals, const int* seg_offsets, int num_images, int num_rois,
-                                 int num_classes, float iou_t0, float iou_t1, int label0, int label1, int label2,
-                                 int num_thresholds, long long* matched_idx, float* matched_iou,
-                                 long long* gt_classes, float* gt_weights, float* gt_scores, float* gt_boxes,
-                                 float* loss_weights, int* counters, void* stream) {
+extern "C" int jtsm_refine_match_counted(const float* pgt_boxes, const long long* pgt_classes,
+                                         const float* pgt_scores, const float* pgt_weights, const int* seed_offsets,
+                                         const int* seed_counts, int max_seeds_per_image, const float* proposals,
+                                         const int* seg_offsets, int num_images, int num_rois, int num_classes,
+                                         float iou_t0, float iou_t1, int label0, int label1, int label2,
+                                         int num_thresholds, long long* matched_idx, float* matched_iou,
+                                         long long* gt_classes, float* gt_weights, float* gt_scores, float* gt_boxes,
+                                         float* loss_weights, int* counters, void* stream) {
   if (num_images < 0 || num_rois < 0 || num_classes <= 0 || num_thresholds < 1 || num_thresholds > 2 ||
       max_seeds_per_image < 0)
     return JTSM_ERR_INVALID_ARGUMENT;
@@ -593,9 +596,22 @@ extern "C" int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_cl
                 num_classes, seed_offsets, (const long long*)nullptr, (const float*)nullptr, mp,
                 const_cast<float*>(pgt_boxes), const_cast<long long*>(pgt_classes), const_cast<float*>(pgt_scores),
                 const_cast<float*>(pgt_weights), matched_idx, matched_iou, gt_classes, gt_weights, gt_scores, gt_boxes,
-                loss_weights, counters, num_images);
+                loss_weights, counters, num_images, seed_counts);
   count_launch();
   return cuda_status();
+}
+
+extern "C" int jtsm_refine_match(const float* pgt_boxes, const long long* pgt_classes, const float* pgt_scores,
+                                 const float* pgt_weights, const int* seed_offsets, int max_seeds_per_image,
+                                 const float* proposals, const int* seg_offsets, int num_images, int num_rois,
+                                 int num_classes, float iou_t0, float iou_t1, int label0, int label1, int label2,
+                                 int num_thresholds, long long* matched_idx, float* matched_iou,
+                                 long long* gt_classes, float* gt_weights, float* gt_scores, float* gt_boxes,
+                                 float* loss_weights, int* counters, void* stream) {
+  return jtsm_refine_match_counted(pgt_boxes, pgt_classes, pgt_scores, pgt_weights, seed_offsets, nullptr,
+                                   max_seeds_per_image, proposals, seg_offsets, num_images, num_rois, num_classes, iou_t0,
+                                   iou_t1, label0, label1, label2, num_thresholds, matched_idx, matched_iou, gt_classes,
+                                   gt_weights, gt_scores, gt_boxes, loss_weights, counters, stream);
 }
 
 extern "C" int jtsm_refine_ce(const float* logits, int num_rois, int num_cols,

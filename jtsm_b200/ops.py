@@ -275,10 +275,12 @@ def refine_assign(prev_scores, prev_boxes, proposals, num_preds_per_image, gt_cl
 
 
 def refine_match(pgt_boxes, pgt_classes, pgt_scores, pgt_weights, seeds_per_image, proposals, num_preds_per_image,
-                 num_classes, iou_thresholds=(0.5,), iou_labels=(0, 1), want_iou=False):
+                 num_classes, iou_thresholds=(0.5,), iou_labels=(0, 1), want_iou=False, seed_counts=None):
     """label_and_sample_proposals for caller-supplied pseudo-gt seeds (roi_heads.py:263-370): seeds of all images
     concatenated ([G,4], [G] int64, [G], [G]) with `seeds_per_image` counts (host ints).  Same outputs as
-    refine_assign (without the pgt_* it did not build)."""
+    refine_assign (without the pgt_* it did not build).
+    seed_counts (int32 DEVICE tensor [N], optional): `seeds_per_image` are then SLOT sizes and image n uses the first
+    seed_counts[n] entries of its slot -- data-dependent seed sets without a host read."""
     _require_cuda(pgt_boxes, proposals)
     P = _f32c(proposals)
     dev = P.device
@@ -297,9 +299,13 @@ def refine_match(pgt_boxes, pgt_classes, pgt_scores, pgt_weights, seeds_per_imag
     out = dict(gt_boxes=fl[:4 * r].view(r, 4), gt_weights=fl[4 * r:5 * r], gt_scores=fl[5 * r:6 * r],
                loss_weights=fl[6 * r:7 * r], matched_iou=fl[8 * r:9 * r] if want_iou else None,
                matched_idx=il[:r], gt_classes=il[r:], counters=torch.empty(n * 3 + 1, dtype=torch.int32, device=dev))
+    if seed_counts is not None:
+        seed_counts = seed_counts.to(device=dev, dtype=torch.int32).contiguous()
+        assert seed_counts.numel() == n
     with torch.cuda.device(dev):
-        check(lib().jtsm_refine_match(
-            _ptr(gb), _ptr(gc), _ptr(gs), _ptr(gw), _ptr(soff), max([0] + [int(v) for v in seeds_per_image]), _ptr(P),
+        check(lib().jtsm_refine_match_counted(
+            _ptr(gb), _ptr(gc), _ptr(gs), _ptr(gw), _ptr(soff), _ptr(seed_counts),
+            max([0] + [int(v) for v in seeds_per_image]), _ptr(P),
             _ptr(seg), n, r, num_classes, float(thr[0]), float(thr[1]) if len(thr) > 1 else 0.0, int(lab[0]), int(lab[1]),
             int(lab[2]) if len(lab) > 2 else 0, len(thr), _ptr(out["matched_idx"]), _ptr(out["matched_iou"]),
             _ptr(out["gt_classes"]), _ptr(out["gt_weights"]), _ptr(out["gt_scores"]), _ptr(out["gt_boxes"]),

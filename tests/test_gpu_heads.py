@@ -258,14 +258,91 @@ def test_mist_seeds_and_matching_bit_exact(cuda, counts, k, top_pro):
     allp = torch.cat(boxes)
     want = ref_heads.get_pgt_mist(boxes, list(scores.split(list(counts))), labels, img, k, top_pro)
     got = heads.refine_labels_mist(scores.to(cuda), allp.to(cuda), allp.to(cuda), list(counts), labels, img.to(cuda), k,
-                                   top_pro, want_iou=True)
+                                   top_pro, want_iou=True, compact=True)
     assert got["seeds_per_image"] == [int(w[0].numel()) for w in want]
+    assert got["seed_counts"].dtype == torch.int32 and got["seed_counts"].tolist() == got["seeds_per_image"]
     assert torch.equal(got["pgt_scores"].cpu(), torch.cat([w[0] for w in want]))
     assert torch.equal(got["pgt_boxes"].cpu(), torch.cat([w[1] for w in want]))
     assert torch.equal(got["pgt_classes"].cpu(), torch.cat([w[2] for w in want]))
     labs = [ref_heads.label_proposals(w, b, k) for w, b in zip(want, boxes)]
     for key in ("gt_classes", "gt_weights", "gt_scores", "gt_boxes", "matched_idx", "matched_iou"):
         assert torch.equal(got[key].cpu(), torch.cat([l[key] for l in labs])), key
+
+
+@pytest.mark.parametrize("top_k,thres", [(3, 0.0), (0.1, 0.9), (5, 0.97), (0.02, 0.5)])
+def test_top_k_and_thresholded_seeds_without_host_read_bit_exact(cuda, top_k, thres):
+    """get_pgt_top_k for top_k > 1 / fractional top_k / thres (roi_heads_oicr.py:675-811) + label assignment with the
+    seed counts kept on the device (padded slots -> jtsm_refine_match_counted) vs the restatement, bit for bit."""
+    from jtsm_b200 import heads
+    from oracle import ref_heads
+
+    counts, k = (900, 1, 400), 11
+    g = synth.generator(43)
+    boxes = [synth.proposals(g, c, 600, 800) for c in counts]
+    labels = synth.image_labels(g, len(counts), k)
+    scores = torch.rand(sum(counts), k + 1, generator=g)
+    img = torch.rand(len(counts), k, generator=g)
+    allp = torch.cat(boxes)
+    want = ref_heads.get_pgt_top_k(boxes, list(scores.split(list(counts))), labels, img, k, top_k=top_k, thres=thres)
+    got = heads.refine_labels_top_k(scores.to(cuda), allp.to(cuda), allp.to(cuda), list(counts),
+                                    [l.to(cuda) for l in labels], img.to(cuda), k, top_k=top_k, thres=thres,
+                                    want_iou=True)
+    cnt = got["seed_counts"].tolist()
+    assert cnt == [int(w[0].numel()) for w in want]
+    if thres > 0.9:
+        assert any(c < s for c, s in zip(cnt, got["seed_slots"]))  # the threshold really removed seeds
+    off = 0
+    for c, slot, w in zip(cnt, got["seed_slots"], want):
+        assert torch.equal(got["pgt_scores"][off:off + c].cpu(), w[0])
+        assert torch.equal(got["pgt_boxes"][off:off + c].cpu(), w[1])
+        assert torch.equal(got["pgt_classes"][off:off + c].cpu(), w[2])
+        assert torch.equal(got["pgt_weights"][off:off + c].cpu(), w[3])
+        off += slot
+    labs = [ref_heads.label_proposals(w, b, k) for w, b in zip(want, boxes)]
+    for key in ("gt_classes", "gt_weights", "gt_scores", "gt_boxes", "matched_idx", "matched_iou"):
+        assert torch.equal(got[key].cpu(), torch.cat([l[key] for l in labs])), key
+    # the trimmed (host-read) form of the same seeds gives the same labels through jtsm_refine_match
+    sc, bx, cl, wt, per = heads.get_pgt_top_k(scores.to(cuda), allp.to(cuda), list(counts), labels, img.to(cuda), k,
+                                              top_k=top_k, thres=thres)
+    assert per == cnt
+    from jtsm_b200 import ops
+    trimmed = ops.refine_match(bx, cl, sc, wt, per, allp.to(cuda), list(counts), k, want_iou=True)
+    for key in ("gt_classes", "gt_weights", "gt_scores", "gt_boxes", "matched_idx", "matched_iou", "counters"):
+        assert torch.equal(trimmed[key], got[key]), key
+
+
+def test_mist_branch_replays_from_a_cuda_graph(cuda):
+    """The WSL.REFINE_MIST branch (top fraction, per-image NMS, matching) holds no host read: captured into a CUDA
+    graph, replayed on new scores, it gives the labels of the eager call."""
+    from jtsm_b200 import heads
+
+    counts, k = (1500, 800), 20
+    g = synth.generator(47)
+    boxes = torch.cat([synth.proposals(g, c, 600, 800) for c in counts]).to(cuda)
+    labels = [l.to(cuda) for l in synth.image_labels(g, len(counts), k)]
+    img = torch.rand(len(counts), k, generator=g).to(cuda)
+    s_static = torch.rand(sum(counts), k + 1, generator=g).to(cuda)
+    run = lambda: heads.refine_labels_mist(s_static, boxes, boxes, list(counts), labels, img, k, 0.15)
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        run()
+        run()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = run()
+    for seed in (1, 2):
+        fresh = torch.rand(sum(counts), k + 1, generator=torch.Generator().manual_seed(seed)).to(cuda)
+        s_static.copy_(fresh)
+        graph.replay()
+        torch.cuda.synchronize()
+        snap = {key: out[key].clone() for key in ("gt_classes", "gt_weights", "gt_boxes", "seed_counts", "counters")}
+        eager = heads.refine_labels_mist(fresh, boxes, boxes, list(counts), labels, img, k, 0.15)
+        for key, v in snap.items():
+            assert torch.equal(v, eager[key]), key
+        assert int(snap["seed_counts"].min()) > 0
 
 
 def test_head_step_with_mist_targets_vs_oracle(cuda):
@@ -277,7 +354,7 @@ def test_head_step_with_mist_targets_vs_oracle(cuda):
                               for _ in wl["ref_logits"]],
                   proposal_boxes=wl["boxes"], labels=wl["labels"], num_classes=cfg["K"])
     ref = ref_heads.head_step(**inputs, reg=True, refine_mist=True)
-    out = run_cuda(inputs, dict(reg=True, refine_mist=True), cuda)
+    out = run_cuda(inputs, dict(reg=True, refine_mist=True, compact_seeds=True), cuda)
     assert set(ref["losses"]) == set(out["losses"])
     for k in ref["losses"]:
         close(out["losses"][k], ref["losses"][k], k)
