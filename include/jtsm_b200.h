@@ -451,6 +451,50 @@ JTSM_API int jtsm_pcl_loss_backward(const float* probs, const float* labels,
                                     const float* im_labels, int num_rois, int channels,
                                     int num_positive, float* grad_probs, void* stream);
 
+/* ------------------------------------------------------------------------
+ * ROIMerge (the CMIL head's clique merge): wsl/layers/roi_merge.py:10-49 over
+ * projects/WSL/wsl/layers/csrc/ROIMerge/ROIMerge_cpu.cpp:33-232 (forward), :234-287 (backward).  The reference op is
+ * CPU only (ROIMerge.h:48-53), its caller copies scores + the R x R IoU matrix to the host every iteration
+ * (fast_rcnn_wsddn.py:621-667).  All pointers DEVICE.
+ *   scores [R] objectness (sum of the MIL scores), iou [R, R] pairwise IoU of the proposals, C / D [R, K] fp32.
+ *   lambda: the merge threshold of this iteration (getlambda(), ROIMerge_cpu.cpp:11-17 -- a host scalar);
+ *   top_k <= 256 (reference 200), window <= 64 (reference 40).
+ * outputs: I int32 [R] cluster id of every RoI; IC int32 [R] members per id (0 past num_id);
+ *   MC / MD [R, K]: rows < num_id = mean of the members' rows (the reference's running sum, bit for bit), rows past
+ *   num_id zero (the reference returns [num_id, K]: slice with stats[0]);
+ *   stats int32 [4] = num_id, num_top_id, max_clique, min_clique (ROIMerge_cpu.cpp:183-196).
+ * Equal scores are ranked lowest index first (the reference's std::sort leaves ties unspecified).
+ * backward: GC[n] = GMC[I[n]] / IC[I[n]] (same for D).
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_roi_merge_workspace_bytes(int num_rois);
+JTSM_API int jtsm_roi_merge_forward(const float* scores, const float* iou, const float* C, const float* D,
+                                    int num_rois, int num_classes, float lambda, int top_k, int window, float* MC,
+                                    float* MD, int* I, int* IC, int* stats, void* workspace, size_t workspace_bytes,
+                                    void* stream);
+JTSM_API int jtsm_roi_merge_backward(const float* GMC, const float* GMD, const int* I, const int* IC, int num_rois,
+                                     int num_classes, float* GC, float* GD, void* stream);
+
+/* ------------------------------------------------------------------------
+ * ROILabel (CMIL / UWSOD refinement labels): wsl/layers/roi_label.py:10-60 over
+ * projects/WSL/wsl/layers/csrc/ROILabel/ROILabel_cpu.cpp:16-194 (CPU only, ROILabel.h:29-34; callers
+ * roi_heads_cmil.py:419-431, roi_heads_uwsod.py).  All pointers DEVICE.
+ *   S [R, score_stride] scores (column c = class c; extra columns ignored), U [R, R] pairwise IoU,
+ *   L [K] image labels (== 1 switches a class on), CW [K] per-class weights or NULL (then the seed's score),
+ *   perm int32 [R]: the order in which the RoIs claim the capped foreground / background slots, or NULL = index order.
+ *   The reference draws it with std::random_shuffle seeded by time(0) (ROILabel_cpu.cpp:108-117); here it is an input
+ *   so that the op is a function of its arguments (the module draws it with torch.randperm on the device).
+ *   fg: IoU >= fg_thresh while at most num_pos were accepted before (num_pos + 1 in total, as the reference's
+ *   `num_pos <= num_pos_`); else bg: bg_thresh_lo <= IoU < bg_thresh_hi while at most num_neg; else weight 0.
+ * outputs: RL int32 [R] (class of the matched seed, K for background), RW [R];
+ *   stats float [4] = accepted fg, accepted bg, sum of fg weights, sum of bg weights of this call (the reference's
+ *   display accumulators P[10..13]).  At most 256 seeds (classes on x top_k) are used.
+ * ------------------------------------------------------------------------ */
+JTSM_API size_t jtsm_roi_label_workspace_bytes(int num_rois);
+JTSM_API int jtsm_roi_label_forward(const float* S, int score_stride, const float* U, const float* L, const float* CW,
+                                    const int* perm, int num_rois, int num_classes, float fg_thresh,
+                                    float bg_thresh_hi, float bg_thresh_lo, int num_pos, int num_neg, int top_k, int* RL,
+                                    float* RW, float* stats, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -784,3 +784,85 @@ def pool_fc6_forward(feat_nhwc, rois, spatial_scale, output_size, weight_binmajo
                                       _ptr(b), nout, int(bool(relu)), _ptr(out), _ptr(ws), wsb, _stream()),
               "pool_fc6_forward")
     return out
+
+
+# --------------------------------------------------------------------------- ROIMerge / ROILabel
+def roi_merge_lambda(cur_iter, size_epoch, max_epoch):
+    """The merge threshold of an iteration: getlambda(cur_iter / size_epoch, max_epoch), ROIMerge_cpu.cpp:11-17, :102."""
+    import math
+
+    import numpy as np
+
+    f = np.float32
+    low = f(0.01)
+    it = f(f(cur_iter) / f(size_epoch))
+    a = math.log(float(f(it + low))) - math.log(float(low))
+    b = math.log(float(f(f(max_epoch) + low))) - math.log(float(low))
+    return float(f(a / b))
+
+
+def roi_merge_forward(S, J, C, D, lam, top_k=200, window=40):
+    """ROIMerge_forward (wsl/layers/roi_merge.py:13, ROIMerge_cpu.cpp:33-232) on the device, no host read.
+    S [R] or [R,1], J [R,R], C / D [R,K] -> dict(MC, MD [R,K] padded with zero rows, I, IC int32 [R],
+    stats int32 [4] = num_id, num_top_id, max_clique, min_clique)."""
+    _require_cuda(S, J, C, D)
+    Cc, Dc, Jc = _f32c(C), _f32c(D), _f32c(J)
+    Sc = _f32c(S).reshape(-1)
+    r, k = Cc.shape
+    assert Sc.numel() == r and Jc.shape == (r, r) and Dc.shape == (r, k)
+    dev = Cc.device
+    out = dict(MC=torch.empty((r, k), dtype=torch.float32, device=dev), MD=torch.empty((r, k), dtype=torch.float32, device=dev),
+               I=torch.empty(r, dtype=torch.int32, device=dev), IC=torch.empty(r, dtype=torch.int32, device=dev),
+               stats=torch.empty(4, dtype=torch.int32, device=dev))
+    L = lib()
+    wsb = L.jtsm_roi_merge_workspace_bytes(r)
+    ws = _workspace(wsb, dev)
+    with torch.cuda.device(dev):
+        check(L.jtsm_roi_merge_forward(_ptr(Sc), _ptr(Jc), _ptr(Cc), _ptr(Dc), r, k, float(lam), int(top_k), int(window),
+                                       _ptr(out["MC"]), _ptr(out["MD"]), _ptr(out["I"]), _ptr(out["IC"]),
+                                       _ptr(out["stats"]), _ptr(ws), wsb, _stream()), "roi_merge_forward")
+    return out
+
+
+def roi_merge_backward(GMC, GMD, I, IC, num_rois=None):
+    """ROIMerge_backward (ROIMerge_cpu.cpp:234-287): GC[n] = GMC[I[n]] / IC[I[n]]."""
+    _require_cuda(GMC, GMD, I, IC)
+    gmc, gmd = _f32c(GMC), _f32c(GMD)
+    r = I.numel() if num_rois is None else int(num_rois)
+    k = gmc.shape[1]
+    dev = gmc.device
+    gc = torch.empty((r, k), dtype=torch.float32, device=dev)
+    gd = torch.empty((r, k), dtype=torch.float32, device=dev)
+    Ii, ICi = I.to(torch.int32).contiguous(), IC.to(torch.int32).contiguous()
+    with torch.cuda.device(dev):
+        check(lib().jtsm_roi_merge_backward(_ptr(gmc), _ptr(gmd), _ptr(Ii), _ptr(ICi), r, k, _ptr(gc), _ptr(gd), _stream()),
+              "roi_merge_backward")
+    return gc, gd
+
+
+def roi_label_forward(S, U, L, CW, perm, fg_thresh, bg_thresh_hi, bg_thresh_lo, num_pos, num_neg, top_k=1):
+    """ROILabel_forward (wsl/layers/roi_label.py:12, ROILabel_cpu.cpp:16-194) on the device with the visiting order as
+    an input (int32 [R] permutation, None = index order).  S [R,Ks], U [R,R], L [K] or [1,K], CW [K] / [1,K] / None.
+    -> (RL int32 [R], RW float32 [R], stats float32 [4] = fg rois, bg rois, fg weight, bg weight)."""
+    _require_cuda(S, U, L)
+    Sc, Uc = _f32c(S), _f32c(U)
+    Lc = _f32c(L).reshape(-1)
+    r, ks = Sc.shape
+    k = Lc.numel()
+    assert Uc.shape == (r, r)
+    dev = Sc.device
+    cw = _f32c(CW).reshape(-1) if CW is not None else None
+    assert cw is None or cw.numel() >= k
+    pm = perm.to(device=dev, dtype=torch.int32).contiguous() if perm is not None else None
+    assert pm is None or pm.numel() == r
+    rl = torch.empty(r, dtype=torch.int32, device=dev)
+    rw = torch.empty(r, dtype=torch.float32, device=dev)
+    stats = torch.empty(4, dtype=torch.float32, device=dev)
+    Lb = lib()
+    wsb = Lb.jtsm_roi_label_workspace_bytes(r)
+    ws = _workspace(wsb, dev)
+    with torch.cuda.device(dev):
+        check(Lb.jtsm_roi_label_forward(_ptr(Sc), ks, _ptr(Uc), _ptr(Lc), _ptr(cw), _ptr(pm), r, k, float(fg_thresh),
+                                        float(bg_thresh_hi), float(bg_thresh_lo), int(num_pos), int(num_neg), int(top_k),
+                                        _ptr(rl), _ptr(rw), _ptr(stats), _ptr(ws), wsb, _stream()), "roi_label_forward")
+    return rl, rw, stats

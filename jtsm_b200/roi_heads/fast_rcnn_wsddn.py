@@ -11,8 +11,10 @@ return values, the math behind them on the sm_100a kernels:
   inference          fast_rcnn_inference on the above
 
 `proposals` is a list of per-image containers with `len()`, `.proposal_boxes.tensor` and `.image_size` (detectron2
-`Instances` or jtsm_b200.structures.Instances).  CMIL (`forward_cmil`, ROIMerge) and ContextLocNet (`context=True`)
-variants are outside the ported path and raise."""
+`Instances` or jtsm_b200.structures.Instances).  With `cmil=True` (WSL.CMIL) the training forward runs `forward_cmil`
+(:621-667): objectness = row sums of the scores, pairwise IoU of the proposals and the ROIMerge clique merge of the C / D
+rows, all on the device (the reference copies S, the R x R IoU matrix, C and D to the host for its CPU-only op), and
+returns the 4-tuple of the reference.  The ContextLocNet variant (`context=True`) is outside the ported path and raises."""
 from typing import Dict, Union
 
 import torch
@@ -20,7 +22,9 @@ from torch import nn
 from torch.nn import functional as F
 
 from ..box_regression import Box2BoxTransform
+from .. import ops
 from ..inference import fast_rcnn_inference
+from ..layers.roi_merge import ROIMerge
 from . import functions as Fn
 
 
@@ -45,8 +49,6 @@ class WSDDNOutputLayers(nn.Module):
                  loss_weight: Union[float, Dict[str, float]] = 1.0, mean_loss: bool = True, cmil: bool = False,
                  display: int = 1280, max_epoch: int = 40, size_epoch: int = 5000):
         super().__init__()
-        if cmil:
-            raise NotImplementedError("WSL.CMIL (forward_cmil + ROIMerge) is outside the ported hot path")
         self.num_classes = num_classes
         input_size = _input_size(input_shape)
         self.num_bbox_reg_classes = 1 if cls_agnostic_bbox_reg else num_classes
@@ -67,7 +69,10 @@ class WSDDNOutputLayers(nn.Module):
             loss_weight = {"loss_cls": loss_weight, "loss_box_reg": loss_weight}
         self.loss_weight = loss_weight
         self.mean_loss = mean_loss
-        self.cmil = False
+        self.cmil = cmil
+        if cmil:
+            self.display, self.max_epoch, self.size_epoch = display, max_epoch, size_epoch
+            self.roi_merge = ROIMerge(0, display, max_epoch, size_epoch)
 
     @classmethod
     def from_config(cls, cfg, input_shape):
@@ -82,7 +87,8 @@ class WSDDNOutputLayers(nn.Module):
                     test_topk_per_image=cfg.TEST.DETECTIONS_PER_IMAGE,
                     box_reg_loss_type=cfg.MODEL.ROI_BOX_HEAD.BBOX_REG_LOSS_TYPE,
                     loss_weight={"loss_box_reg": cfg.MODEL.ROI_BOX_HEAD.BBOX_REG_LOSS_WEIGHT},
-                    mean_loss=cfg.WSL.MEAN_LOSS, cmil=cfg.WSL.CMIL)
+                    mean_loss=cfg.WSL.MEAN_LOSS, cmil=cfg.WSL.CMIL, display=int(1280 / cfg.SOLVER.IMS_PER_BATCH),
+                    max_epoch=int(cfg.SOLVER.MAX_ITER / cfg.WSL.SIZE_EPOCH), size_epoch=cfg.WSL.SIZE_EPOCH)
 
     def forward(self, x, proposals=None, context=False, gt_classes_img_oh=None):
         """-> (scores [R, K], proposal_deltas [R, 4 * num_bbox_reg_classes] zeros).
@@ -94,14 +100,33 @@ class WSDDNOutputLayers(nn.Module):
             x = torch.flatten(x, start_dim=1)
         C = self.cls(x)
         D = self.det(x)
-        counts = _counts(proposals, C.shape[0])
+        merged = self.cmil and self.training
+        if merged:
+            C, D, Oscores, Oproposal_deltas = self.forward_cmil(C, D, proposals)
+        counts = [C.shape[0]] if merged else _counts(proposals, C.shape[0])
         scores, img_sum, img_scores, loss = Fn.wsddn(C, D, counts, gt_classes_img_oh, self.mean_loss)
         # the extra results of the launch ride on the scores tensor (the reference's return type is a plain 2-tuple)
         scores._jtsm_mil = dict(img_sum=img_sum, img_scores=img_scores, counts=counts,
                                 loss=loss if gt_classes_img_oh is not None else None, labels=gt_classes_img_oh)
         proposal_deltas = torch.zeros(scores.shape[0], self.num_bbox_reg_classes * self.box_dim, dtype=scores.dtype,
                                       device=scores.device, requires_grad=False)
+        if merged:
+            return scores, proposal_deltas, Oscores, Oproposal_deltas
         return scores, proposal_deltas
+
+    def forward_cmil(self, C, D, proposals):
+        """fast_rcnn_wsddn.py:621-667: -> (MC, MD, scores of the un-merged rows, zero deltas).  One image per call, as in
+        the reference (its ROIMerge asserts a square IoU matrix, ROIMerge_cpu.cpp:58)."""
+        assert proposals and len(proposals) == 1, "WSL.CMIL merges the proposals of ONE image (square IoU matrix)"
+        scores, _, _, _ = Fn.wsddn(C, D, [C.shape[0]], None, self.mean_loss)
+        proposal_deltas = torch.zeros(scores.shape[0], self.num_bbox_reg_classes * self.box_dim, dtype=scores.dtype,
+                                      device=scores.device, requires_grad=False)
+        with torch.no_grad():
+            obn = scores.detach().sum(dim=1, keepdim=True)
+            boxes = proposals[0].proposal_boxes.tensor
+            J = ops.pairwise_iou(boxes, boxes)
+        MC, MD = self.roi_merge(obn, J, C, D)
+        return MC, MD, scores, proposal_deltas
 
     # ------------------------------------------------------------------ training
     def _img_sum(self, scores, proposals):

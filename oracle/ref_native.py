@@ -205,3 +205,71 @@ def pcl_loss_backward(probs, labels, cls_loss_weights, gt_assignment, pc_labels,
     g = np.zeros((r, c), np.float32)
     pcl().ref_pcl_loss_backward(_p(probs), *[_p(x) for x in a], r, c, a[3].shape[0], _p(g))
     return g
+
+
+# ---------------------------------------------------------------- ROIMerge / ROILabel (CMIL / UWSOD heads)
+WSLCMIL = os.path.join(OUT, "libref_wslcmil.so")
+_cmil = None
+
+
+def build_wsl_cmil():
+    return _build_aten("libref_wslcmil.so", ("projects", "WSL", "wsl", "layers", "csrc", "ROIMerge", "ROIMerge_cpu.cpp"),
+                       WSLCMIL)
+
+
+def wsl_cmil_available():
+    return build_wsl_cmil() is not None
+
+
+def cmil():
+    global _cmil
+    if _cmil is None:
+        path = build_wsl_cmil()
+        if path is None:
+            raise RuntimeError("oracle/_ref/libref_wslcmil.so missing and /root/reference not present")
+        import torch  # noqa: F401
+
+        _cmil = ctypes.CDLL(path)
+        _cmil.ref_roi_merge_forward.restype = ctypes.c_int
+    return _cmil
+
+
+def roi_merge_forward(S, J, C, D, P):
+    """The reference's ROIMerge_forward_cpu.  P: int32[8] state (copied, returned updated).
+    -> (MC [num_id,K], MD, I int32 [R], IC int32 [R], P)."""
+    S, J, C, D = _f32(S).reshape(-1), _f32(J), _f32(C), _f32(D)
+    P = _i32(P).copy()
+    r, k = C.shape
+    mc, md = np.zeros((r, k), np.float32), np.zeros((r, k), np.float32)
+    i, ic = np.zeros(r, np.int32), np.zeros(r, np.int32)
+    num_id = cmil().ref_roi_merge_forward(_p(S), _p(J), _p(C), _p(D), _p(P), r, k, _p(mc), _p(md), _p(i), _p(ic))
+    return mc[:num_id].copy(), md[:num_id].copy(), i, ic, P
+
+
+def roi_merge_backward(C, D, GMC, GMD, I, IC):
+    C, D, GMC, GMD = _f32(C), _f32(D), _f32(GMC), _f32(GMD)
+    I, IC = _i32(I), _i32(IC)
+    r, k = C.shape
+    gc, gd = np.zeros((r, k), np.float32), np.zeros((r, k), np.float32)
+    cmil().ref_roi_merge_backward(_p(C), _p(D), _p(GMC), _p(GMD), _p(I), _p(IC), r, k, GMC.shape[0], _p(gc), _p(gd))
+    return gc, gd
+
+
+def roi_label_perm(num_roi):
+    """The visiting order the reference's ROILabel call draws in this build (fixed seed; see the driver)."""
+    perm = np.zeros(num_roi, np.int32)
+    cmil().ref_roi_label_perm(int(num_roi), _p(perm))
+    return perm
+
+
+def roi_label_forward(S, U, L, CW, P):
+    """The reference's ROILabel_forward_cpu.  P: float32[14] state (copied, returned updated).  CW may be None.
+    -> (RL int32 [R], RW float32 [R], P)."""
+    S, U, L = _f32(S), _f32(U), _f32(L).reshape(-1)
+    P = _f32(P).copy()
+    r, ks = S.shape
+    rl, rw = np.zeros(r, np.int32), np.zeros(r, np.float32)
+    cw = _f32(CW).reshape(-1) if CW is not None else None
+    cmil().ref_roi_label_forward(_p(S), _p(U), _p(L), _p(cw) if cw is not None else None, _p(P), r, ks, L.shape[0],
+                                 _p(rl), _p(rw))
+    return rl, rw, P
