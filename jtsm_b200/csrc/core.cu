@@ -18,7 +18,8 @@ struct Knob {
 Knob g_knobs[] = {
     {"roi_pool_splits", {0}},      // 0 = auto
     {"roi_pool_force_gmem", {0}},  // 1 = skip the smem-plane kernel
-    {"roi_pool_bwd_algo", {0}},    // 0 = auto (vec4 + register folding), 1 = one RED per element, 2 = vec4 + warp match folding
+    {"roi_pool_bwd_super_mb", {0}},   // 7 x 7 backward: MB of accumulation planes the warps in flight spread over (0 = auto)
+    {"roi_pool_bwd_algo", {0}},    // 0 = auto (7 x 7: all 49 bins of a (RoI, channel) per lane, else vec4 folding), 1 = one RED per element, 3 = vec4 folding
     {"roi_pool_fwd_algo", {0}},    // 0 = auto, 1 = direct smem scan, 2 = gmem scan, 3 = range-max tables
     {"roi_pool_fwd_keys", {0}},    // range-max tables: 0 = absolute indices, 8 look-ups per bin (default); 1 = (key10 | rel6) entries, 5 look-ups, ALU bound
     {"roi_pool_fwd_tma", {1}},     // 1 = planes arrive by cp.async.bulk (TMA 1-D) + mbarrier into a staging buffer; 0 = plain loads

@@ -519,6 +519,87 @@ extern "C" int jtsm_roi_pool_forward(const void* input, const float* rois, int d
   return rc;
 }
 
+// 7 x 7 bins, contiguous gradient, channels % 32 == 0: a lane owns ALL 49 bins of one (RoI, channel), so every pair of
+// neighbouring bins that picked the same cell (right, below, and the two diagonals below: 33 % of the elements at config
+// 2, against the 14 % the 4-wide kernel can see) folds in registers before the reduction; the warp's 32 channels are one
+// contiguous 32 x 49 run of the gradient, staged through shared memory with coalesced loads (lane stride 49 words:
+// conflict free).  The bound of the backward is the number of REDs, nothing else.
+constexpr int kFoldWarps = 8;
+template <typename T, typename A>
+__global__ void __launch_bounds__(kFoldWarps * 32, 2)
+roi_pool_bwd_fold7_kernel(const T* __restrict__ grad_output, const float* __restrict__ rois,
+                          const A* __restrict__ argmax, int batch, int channels, int hw, int num_rois, int super,
+                          const float* __restrict__ row_scale, float* __restrict__ grad_acc) {
+  extern __shared__ __align__(16) unsigned char fold_smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* sg = (float*)fold_smem + warp * (32 * 49 * 2);
+  int* sa = (int*)(sg + 32 * 49);
+  const int groups = channels >> 5;
+  const long long units = (long long)num_rois * groups;
+  for (long long u = (long long)blockIdx.x * kFoldWarps + warp; u < units; u += (long long)gridDim.x * kFoldWarps) {
+    // Order of the units: RoI-major inside a super-group of `super` channel groups whose accumulation planes fit L2
+    // together.  Spreading the warps in flight over many planes keeps concurrent REDs off the same cells (config 1:
+    // 181 us against 202 us channel-group-major); bounding the spread keeps the planes L2 resident when the whole
+    // gradient map is not (config 3, 123 MB: 6.7 ms RoI-major over all 2048 channels against 3.2 ms).
+    const long long per_super = (long long)num_rois * super;
+    const int sgi = (int)(u / per_super);
+    const long long rem = u - sgi * per_super;
+    const int gs = min(super, groups - sgi * super);
+    const int r = (int)(rem / gs), cg = sgi * super + (int)(rem % gs);
+    const int b = (int)__ldg(rois + (size_t)r * 5);
+    if (b < 0 || b >= batch) continue;  // warp uniform
+    const float rs = row_scale ? __ldg(row_scale + r) : 1.f;
+    const size_t base = ((size_t)r * channels + (size_t)cg * 32) * 49;
+    const T* g_r = grad_output + base;
+    const A* a_r = argmax + base;
+#pragma unroll 7
+    for (int k = 0; k < 49; ++k) {
+      sg[k * 32 + lane] = Elem<T>::to_f(g_r[k * 32 + lane]);
+      sa[k * 32 + lane] = Arg<A>::dec(a_r[k * 32 + lane]);
+    }
+    __syncwarp();
+    float g[49];
+    int a[49];
+#pragma unroll
+    for (int k = 0; k < 49; ++k) {
+      g[k] = __fmul_rn(sg[lane * 49 + k], rs);
+      a[k] = sa[lane * 49 + k];
+    }
+    __syncwarp();
+    float* acc = grad_acc + ((size_t)b * channels + (size_t)cg * 32 + lane) * hw;
+#pragma unroll
+    for (int k = 0; k < 49; ++k) {
+      const int ph = k / 7, pw = k % 7;
+      bool done = a[k] < 0;
+      if (pw < 6) {
+        const bool m = !done && a[k] == a[k + 1];
+        g[k + 1] = __fadd_rn(g[k + 1], m ? g[k] : 0.f);
+        done |= m;
+      }
+      if (ph < 6) {
+        if (pw > 0) {
+          const bool m = !done && a[k] == a[k + 6];
+          g[k + 6] = __fadd_rn(g[k + 6], m ? g[k] : 0.f);
+          done |= m;
+        }
+        {
+          const bool m = !done && a[k] == a[k + 7];
+          g[k + 7] = __fadd_rn(g[k + 7], m ? g[k] : 0.f);
+          done |= m;
+        }
+        if (pw < 6) {
+          const bool m = !done && a[k] == a[k + 8];
+          g[k + 8] = __fadd_rn(g[k + 8], m ? g[k] : 0.f);
+          done |= m;
+        }
+      }
+      if (!done) {
+        atomicAdd(acc + a[k], g[k]);
+      }
+    }
+  }
+}
+
 extern "C" size_t jtsm_roi_pool_backward_workspace_bytes(int dtype, int batch, int channels,
                                                          int height, int width) {
   if (dtype == JTSM_F32) return 256;
@@ -560,7 +641,31 @@ extern "C" int jtsm_roi_pool_backward(const void* grad_output, long long stride_
                         (long long)channels * height * width < (1ll << 31) &&
                         ((uintptr_t)grad_output % 16 == 0) && ((uintptr_t)argmax % 16 == 0) &&
                         tuning("roi_pool_bwd_algo", 0) != 1;
-    if (vec_ok) {
+    const int bwd_algo = tuning("roi_pool_bwd_algo", 0);
+    const bool fold_ok = contiguous && pooled_h == 7 && pooled_w == 7 && channels % 32 == 0 && bwd_algo != 1 &&
+                         bwd_algo != 3 && (long long)channels * height * width < (1ll << 31);
+    if (fold_ok) {
+      const size_t smem = (size_t)kFoldWarps * 32 * 49 * 2 * sizeof(float);
+      const long long units = (long long)num_rois * (channels / 32);
+      long long blocks = (units + kFoldWarps - 1) / kFoldWarps;
+      const long long cap = (long long)num_sms() * 2 * 8;
+      if (blocks > cap) blocks = cap;
+      // how many channel groups the warps in flight spread over (measured, profiles/r2j_roi_pool_bwd_fold.md): all of
+      // them while the whole fp32 gradient map is small (<= 16 MB: configs 1, 2), else ~4 MB of planes (config 3)
+      const long long group_bytes = (long long)batch * height * width * 4 * 32;
+      const int knob_mb = tuning("roi_pool_bwd_super_mb", 0);
+      long long budget = knob_mb > 0 ? ((long long)knob_mb << 20)
+                                     : ((long long)n_in * 4 <= (16ll << 20) ? (long long)n_in * 4 : (4ll << 20));
+      long long sup = budget / (group_bytes > 0 ? group_bytes : 1);
+      const int super = (int)(sup < 1 ? 1 : (sup > channels / 32 ? channels / 32 : sup));
+      JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
+                            cudaFuncSetAttribute(roi_pool_bwd_fold7_kernel<T, A>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                            roi_pool_bwd_fold7_kernel<T, A><<<(int)blocks, kFoldWarps * 32, smem, st>>>(
+                                (const T*)grad_output, rois, (const A*)argmax, batch, channels, height * width,
+                                num_rois, super, row_scale, acc);
+                          }));
+    } else if (vec_ok) {
       const unsigned magic_pp = (unsigned)((0x100000000ull + PP - 1) / PP);
       int ysplit = (int)((cpp + 1023) / 1024);
       const int want = (4 * num_sms() * 8 + num_rois - 1) / num_rois;  // enough CTAs when R is small
