@@ -451,6 +451,18 @@ JTSM_API int jtsm_pcl_loss_backward(const float* probs, const float* labels,
                                     const float* im_labels, int num_rois, int channels,
                                     int num_positive, float* grad_probs, void* stream);
 
+/* Proposal clusters of PCL (wsl/modeling/roi_heads/third_party/pcl.py:150-200 `_get_proposal_clusters`; numpy on the
+ * host in the reference): rois [R,4], centers [G,4] (16-byte aligned), center_labels / center_scores [G] (class column
+ * ids 1..K as floats, scores), cls_prob [R, num_cols].  Outputs fp32 as the reference hands them to pcl_loss:
+ * labels / cls_loss_weights / gt_assignment [R] (IoU first-maximum; < fg_thresh: label 0, assignment -1;
+ * < bg_thresh: weight 0), pc_labels / pc_probs / pc_count / img_cls_loss_weights [G].  G <= 1024.
+ * The cluster CENTRES (`_get_graph_centers`: sklearn KMeans + greedy graph cover) stay host code. */
+JTSM_API int jtsm_pcl_proposal_clusters(const float* rois, const float* centers, const float* center_labels,
+                                        const float* center_scores, const float* cls_prob, int num_rois,
+                                        int num_centers, int num_cols, float fg_thresh, float bg_thresh, float* labels,
+                                        float* cls_loss_weights, float* gt_assignment, float* pc_labels,
+                                        float* pc_probs, float* pc_count, float* img_cls_loss_weights, void* stream);
+
 /* ------------------------------------------------------------------------
  * ROIMerge (the CMIL head's clique merge): wsl/layers/roi_merge.py:10-49 over
  * projects/WSL/wsl/layers/csrc/ROIMerge/ROIMerge_cpu.cpp:33-232 (forward), :234-287 (backward).  The reference op is

@@ -866,3 +866,25 @@ def roi_label_forward(S, U, L, CW, perm, fg_thresh, bg_thresh_hi, bg_thresh_lo, 
                                         float(bg_thresh_hi), float(bg_thresh_lo), int(num_pos), int(num_neg), int(top_k),
                                         _ptr(rl), _ptr(rw), _ptr(stats), _ptr(ws), wsb, _stream()), "roi_label_forward")
     return rl, rw, stats
+
+
+def pcl_proposal_clusters(rois, centers, center_labels, center_scores, cls_prob, fg_thresh=0.5, bg_thresh=0.1):
+    """`_get_proposal_clusters` (third_party/pcl.py:150-200) on the device.  rois [R,4], centers [G,4], center_labels [G]
+    (class column ids), center_scores [G], cls_prob [R,C] -> dict of fp32 tensors: labels, cls_loss_weights,
+    gt_assignment [R]; pc_labels, pc_probs, pc_count, img_cls_loss_weights [G]."""
+    _require_cuda(rois, centers, cls_prob)
+    B, Cn, P = _f32c(rois), _f32c(centers), _f32c(cls_prob)
+    r, g = B.shape[0], Cn.shape[0]
+    dev = B.device
+    cl = center_labels.to(device=dev, dtype=torch.float32).contiguous().view(-1)
+    cs = center_scores.to(device=dev, dtype=torch.float32).contiguous().view(-1)
+    assert cl.numel() == g and cs.numel() == g and P.shape[0] == r and g > 0
+    per_roi = torch.empty((3, r), dtype=torch.float32, device=dev)
+    per_c = torch.empty((4, g), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().jtsm_pcl_proposal_clusters(_ptr(B), _ptr(Cn), _ptr(cl), _ptr(cs), _ptr(P), r, g, P.shape[1],
+                                               float(fg_thresh), float(bg_thresh), _ptr(per_roi[0]), _ptr(per_roi[1]),
+                                               _ptr(per_roi[2]), _ptr(per_c[0]), _ptr(per_c[1]), _ptr(per_c[2]),
+                                               _ptr(per_c[3]), _stream()), "pcl_proposal_clusters")
+    return dict(labels=per_roi[0], cls_loss_weights=per_roi[1], gt_assignment=per_roi[2], pc_labels=per_c[0],
+                pc_probs=per_c[1], pc_count=per_c[2], img_cls_loss_weights=per_c[3])
