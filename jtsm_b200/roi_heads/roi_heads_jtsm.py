@@ -1,0 +1,100 @@
+"""`WSDDNROIHeadsB200` and `JTSMROIHeadsB200`: the other two registered WSL heads on the sm_100a path.
+
+* WSDDNROIHeads (projects/WSL/wsl/modeling/roi_heads/roi_heads_wsddn.py:28-330): pooling x objectness -> box head ->
+  `WSDDNOutputLayers` -> BCE; no refinement branches.  = `OICRROIHeadsB200` with `refine_K = 0`, kept as its own class so
+  that `MODEL.ROI_HEADS.NAME` and `from_config` read like the reference's.
+* JTSMROIHeads, BOX branch (roi_heads_jtsm.py:197-752, BASELINE.json configs[2]): the OICR chain over JTSM's pooler --
+  MOIPool restricted by the proposals' superpixel sets (`oh_labels`) -- with the pooled features scaled by
+  `mask_scale = P^2 / (#non-empty bins + 1)` (roi_heads_jtsm.py:607-620, recomputed there from the returned arg-max with
+  four eager kernels) and by `objectness_logits + 1`; both factors are the epilogue of the one MOIPool launch here
+  (`jtsm_moi_pool_forward(..., row_scale, mask_scale)`) and of its backward.  `forward` takes the reference's extra
+  arguments (`gt_sem_seg`, `superpixels`) and keeps `cnt_superpixels` for `ops.pairwise_iou_sp`.
+  Not ported: the segmentation branch (`_forward_mask`, GrabCut pseudo-masks on the CPU, `get_pgt_sem_seg`) -- outside the
+  per-proposal hot path; requesting it raises."""
+from typing import Dict, List, Optional
+
+import torch
+
+from ..structures import Instances
+from .roi_heads_oicr import OICRROIHeadsB200, get_image_level_gt
+
+
+class WSDDNROIHeadsB200(OICRROIHeadsB200):
+    def __init__(self, *, num_classes, box_in_features, box_pooler, box_head, box_predictor, **kwargs):
+        kwargs.pop("refine_K", None)
+        kwargs.pop("box_refinery", None)
+        super().__init__(num_classes=num_classes, box_in_features=box_in_features, box_pooler=box_pooler,
+                         box_head=box_head, box_predictor=box_predictor, refine_K=0, refine_reg=[], box_refinery=[],
+                         **kwargs)
+
+    @classmethod
+    def from_config(cls, cfg, input_shape):
+        ret = OICRROIHeadsB200.from_config.__func__(cls, _NoRefine(cfg), input_shape)
+        for k in ("refine_K", "refine_mist", "refine_reg", "box_refinery"):
+            ret.pop(k, None)
+        return ret
+
+
+class _NoRefine:
+    """cfg view with WSL.REFINE_NUM = 0 (the WSDDN configs do not carry the refinement keys)."""
+
+    def __init__(self, cfg):
+        self._cfg = cfg
+
+    def __getattr__(self, name):
+        v = getattr(self._cfg, name)
+        if name == "WSL":
+            return _Over(v, REFINE_NUM=0, REFINE_MIST=False, REFINE_REG=[])
+        return v
+
+
+class _Over:
+    def __init__(self, node, **over):
+        self._node, self._over = node, over
+
+    def __getattr__(self, name):
+        if name in self._over:
+            return self._over[name]
+        return getattr(self._node, name)
+
+
+class JTSMROIHeadsB200(OICRROIHeadsB200):
+    def __init__(self, *, mask_on: bool = False, **kwargs):
+        if mask_on:
+            raise NotImplementedError("JTSM's segmentation branch (_forward_mask / GrabCut) is outside the ported hot path")
+        super().__init__(**kwargs)
+        assert self.box_pooler is None or self.box_pooler.pooler_type == "MOIPool", "JTSM pools with MOIPool"
+        self.superpixels = None
+        self.cnt_superpixels = None
+
+    def forward(self, images, features: Dict[str, torch.Tensor], proposals: List[Instances],
+                targets: Optional[List[Instances]] = None, gt_sem_seg=None, superpixels=None):
+        """roi_heads_jtsm.py:502-561 (box branch).  `superpixels`: [N, Hs, Ws] integer label images (tensor or an
+        ImageList-like with `.tensor`); every proposal container carries `oh_labels` [R_i, S]."""
+        assert superpixels is not None, "JTSM heads need the superpixel label images"
+        self.proposals = proposals
+        self.superpixels = superpixels
+        sp = superpixels.tensor if hasattr(superpixels, "tensor") else superpixels
+        self.cnt_superpixels = [torch.bincount(s.reshape(-1).long(), minlength=p.oh_labels.size(1)).view(1, 1, -1)
+                                for s, p in zip(sp, proposals)]
+        return super().forward(images, features, proposals, targets)
+
+    def _pool(self, features, proposals):
+        """MOIPool x mask_scale x (objectness_logits + 1) (roi_heads_jtsm.py:606-625), one launch."""
+        feats = [features[f] for f in self.box_in_features]
+        scale = torch.cat([x.objectness_logits + 1 for x in proposals], dim=0)
+        out = self.box_pooler(feats, [x.proposal_boxes for x in proposals],
+                              oh_labels_list=[x.oh_labels for x in proposals], superpixels=self.superpixels,
+                              row_scale=scale, mask_scale=True)
+        box_features = out[0] if isinstance(out, tuple) else out
+        return box_features, scale
+
+
+def register_all(registry):
+    """Register the three heads in a detectron2 `ROI_HEADS_REGISTRY`."""
+    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, JTSMROIHeadsB200):
+        registry.register(c)
+    return registry
+
+
+__all__ = ["WSDDNROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]

@@ -1,0 +1,132 @@
+"""The other two registered heads on the GPU: `WSDDNROIHeadsB200` (= the OICR heads without refinement branches,
+roi_heads_wsddn.py:28-330) and the box branch of `JTSMROIHeadsB200` (roi_heads_jtsm.py:590-752: MOIPool over superpixel
+sets, mask_scale x objectness fused into the pooling launch)."""
+import numpy as np
+import pytest
+import torch
+
+from jtsm_b200 import synth
+
+gpu = pytest.mark.gpu
+
+
+def _heads(kind, cuda, c=16, k=6, kr=2, d=24):
+    from jtsm_b200.box_regression import Box2BoxTransform
+    from jtsm_b200.poolers import ROIPooler
+    from jtsm_b200.roi_heads import (DiscriminativeAdaptionNeck, JTSMROIHeadsB200, OICROutputLayers, WSDDNOutputLayers,
+                                     WSDDNROIHeadsB200)
+
+    torch.manual_seed(3)
+    shape = type("ShapeSpec", (), dict(channels=c, height=7, width=7, stride=None))()
+    head = DiscriminativeAdaptionNeck(shape, fc_dims=(d, d))
+    b2b = Box2BoxTransform(weights=(10.0, 10.0, 5.0, 5.0))
+    pred = WSDDNOutputLayers(head.output_shape, box2box_transform=b2b, num_classes=k)
+    if kind == "wsddn":
+        pooler = ROIPooler(output_size=7, scales=(1 / 8.0,), sampling_ratio=0, pooler_type="ROIPool")
+        return WSDDNROIHeadsB200(num_classes=k, box_in_features=["conv5"], box_pooler=pooler, box_head=head,
+                                 box_predictor=pred).to(cuda)
+    pooler = ROIPooler(output_size=7, scales=(1 / 8.0,), sampling_ratio=0, pooler_type="MOIPool")
+    refs = [OICROutputLayers(head.output_shape, box2box_transform=b2b, num_classes=k, refine_k=i,
+                             refine_reg=[False] * kr) for i in range(kr)]
+    return JTSMROIHeadsB200(num_classes=k, box_in_features=["conv5"], box_pooler=pooler, box_head=head, box_predictor=pred,
+                            refine_K=kr, refine_reg=[False] * kr, box_refinery=refs).to(cuda)
+
+
+def _inputs(cuda, counts=(120, 90), c=16, k=6, with_sp=False):
+    from jtsm_b200.structures import Boxes, Instances
+
+    g = synth.generator(17)
+    boxes = [synth.proposals(g, n, 600, 800) for n in counts]
+    feat = synth.feature_map(g, len(counts), c, 75, 100).to(cuda).requires_grad_()
+    labels = synth.image_labels(g, len(counts), k)
+    sp = oh = None
+    if with_sp:
+        sp, oh, _, s = synth.superpixel_case(g, boxes, 600, 800, 22)
+    props, tgts, off = [], [], 0
+    for i, (b, l) in enumerate(zip(boxes, labels)):
+        fields = dict(proposal_boxes=Boxes(b.to(cuda)), objectness_logits=torch.rand(b.shape[0], generator=g).to(cuda))
+        if with_sp:
+            fields["oh_labels"] = oh[off:off + b.shape[0]].to(cuda)
+        props.append(Instances((600, 800), **fields))
+        tgts.append(Instances((600, 800), gt_classes=l.to(cuda)))
+        off += b.shape[0]
+    return feat, props, tgts, (sp.to(cuda) if with_sp else None)
+
+
+@gpu
+def test_wsddn_heads_train_and_infer(cuda):
+    heads = _heads("wsddn", cuda)
+    feat, props, tgts, _ = _inputs(cuda)
+    heads.train()
+    for m in heads.modules():  # the neck's dropout would draw a different mask in the eager re-run below
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+    _, losses = heads(None, {"conv5": feat}, props, tgts)
+    assert set(losses) == {"loss_cls"}
+    losses["loss_cls"].backward()
+    assert feat.grad is not None and float(feat.grad.abs().sum()) > 0
+    # eager definition of the same step (roi_heads_wsddn.py:300-311, fast_rcnn_wsddn.py:571-584, 346-379)
+    with torch.no_grad():
+        from jtsm_b200.layers import RoIPool
+        from jtsm_b200.poolers import convert_boxes_to_pooler_format
+
+        rois = convert_boxes_to_pooler_format([p.proposal_boxes for p in props])
+        x = RoIPool((7, 7), 1 / 8.0)(feat.detach(), rois)
+        x = x * torch.cat([p.objectness_logits + 1 for p in props]).view(-1, 1, 1, 1)
+        x = heads.box_head(x)
+        C, D = heads.box_predictor.cls(x), heads.box_predictor.det(x)
+        n = [len(p) for p in props]
+        s = torch.cat([torch.softmax(c_, 1) * torch.softmax(d_, 0) for c_, d_ in zip(C.split(n), D.split(n))])
+        img = torch.cat([t.sum(0, keepdim=True) for t in s.split(n)]).clamp(1e-6, 1 - 1e-6)
+        oh = torch.zeros_like(img)
+        for i, t in enumerate(tgts):
+            oh[i, t.gt_classes] = 1
+        want = torch.nn.functional.binary_cross_entropy(img, oh)
+    assert abs(float(losses["loss_cls"].detach()) - float(want)) <= 1e-5 * float(want)
+    heads.eval()
+    with torch.no_grad():
+        inst, extra, all_scores, all_boxes = heads(None, {"conv5": feat.detach()}, props)
+    assert len(inst) == 2 and extra == {} and tuple(all_scores[0].shape[-2:]) == (120, 7)
+
+
+@gpu
+def test_jtsm_heads_box_branch_pooling_and_step(cuda):
+    heads = _heads("jtsm", cuda)
+    feat, props, tgts, sp = _inputs(cuda, with_sp=True)
+    heads.train()
+    heads.superpixels = sp
+    fused, scale = heads._pool({"conv5": feat.detach()}, props)
+    # the reference's arithmetic (roi_heads_jtsm.py:597-625) on the un-fused op
+    with torch.no_grad():
+        out, argmax = heads.box_pooler([feat.detach()], [p.proposal_boxes for p in props],
+                                       oh_labels_list=[p.oh_labels for p in props], superpixels=sp)
+        mask_scale = argmax.size(2) * argmax.size(3) * (
+            (argmax[:, 0, :, :] != -1).view(argmax.size(0), -1).sum(dim=1).to(dtype=torch.float32) + 1).reciprocal()
+        want = out * mask_scale.view(-1, 1, 1, 1)
+        want = want * torch.cat([p.objectness_logits + 1 for p in props]).view(-1, 1, 1, 1)
+    assert torch.equal(fused, want)
+    assert float((argmax[:, 0] == -1).float().mean()) > 0.05  # the superpixel masks really empty some bins
+    _, losses = heads(None, {"conv5": feat}, props, tgts, superpixels=sp)
+    assert set(losses) == {"loss_cls", "loss_cls_r0", "loss_cls_r1"}
+    sum(losses.values()).backward()
+    assert torch.isfinite(feat.grad).all() and float(feat.grad.abs().sum()) > 0
+    assert heads.cnt_superpixels[0].shape[-1] == props[0].oh_labels.shape[1]
+    assert int(heads.cnt_superpixels[0].sum()) == 600 * 800
+    heads.eval()
+    with torch.no_grad():
+        inst, _, all_scores, _ = heads(None, {"conv5": feat.detach()}, props, superpixels=sp)
+    assert len(inst) == 2 and tuple(all_scores[1].shape[-2:]) == (90, 7)
+
+
+def test_heads_register_in_a_registry():
+    from jtsm_b200.roi_heads import register_all
+
+    class Reg:
+        def __init__(self):
+            self.names = []
+
+        def register(self, c):
+            self.names.append(c.__name__)
+
+    r = register_all(Reg())
+    assert r.names == ["OICRROIHeadsB200", "WSDDNROIHeadsB200", "JTSMROIHeadsB200"]
