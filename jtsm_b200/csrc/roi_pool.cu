@@ -15,9 +15,12 @@
 //     a packed table (roi_bins.cuh) instead of per output element.
 //   * threads map to consecutive (roi, bin) outputs, so for a fixed channel a
 //     warp writes contiguous 4*P*P-byte runs of the [R, C, P, P] output.
+#include <type_traits>
+
 #include "roi_bins.cuh"
 #include "roi_pool_rmq.cuh"
 #include "roi_pool_rmqk.cuh"
+#include "roi_pool_rmqp.cuh"
 
 namespace jtsm {
 
@@ -328,9 +331,21 @@ constexpr size_t kMaxPlaneSmem = 200 * 1024;
 // Row bands for a plane (RmqBands, roi_bins.cuh): one band when plane + tables fit shared memory, else bands of the
 // largest height whose plane + tables + staging buffer fit, overlapping by the tallest bin of a RoI inside the map.
 // nb = 0: not feasible (very wide maps, where a band would be shorter than ~1.5 bins) -> direct-scan kernels.
-RmqBands pick_bands(int height, int width, int PH) {
+// packed: the 16-bit kernel of roi_pool_rmqp.cuh (40 B per cell, no fp32 plane) instead of 24 B per cell.
+RmqBands pick_bands(int height, int width, int PH, bool packed = false) {
   const long long hw = (long long)height * width;
   if (hw <= 0 || width > 4096) return {0, 0, 0};
+  if (packed) {
+    if (hw < (1 << 20) && rp_smem_core((int)hw) <= 227 * 1024) return {1, height, height};
+    int Hb = (int)((227 * 1024 - kRpHeader - 64) / (40 * (long long)width));
+    while (Hb > 0 && rp_smem_core(Hb * width) > 227 * 1024) --Hb;
+    const int O = (height + PH - 1) / PH + 1;
+    const int S = Hb - O;
+    if (Hb < 3 || S < 1 || 3 * S < Hb || (long long)Hb * width > 65535) return {0, 0, 0};
+    const int nb = (height - O + S - 1) / S;
+    if (nb < 1 || nb > 255) return {0, 0, 0};
+    return {nb, S, Hb};
+  }
   if (hw < (1 << 20) && rk_smem_core((int)hw) <= 227 * 1024) return {1, height, height};
   // bands as tall as plane + tables allow (24 B per cell): no staging buffer in banded mode -- fewer bands (fewer table
   // builds and descriptor sweeps per plane) are worth more than the bulk-copy fetch (150 x 200: 6 bands instead of 8)
@@ -421,12 +436,64 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
   }
 }
 
+// 16-bit feature maps: packed (value, index) tables (roi_pool_rmqp.cuh) when the band geometry allows it.
+bool rmqp_eligible(int dtype, int batch, int channels, int height, int width, int num_rois, int PH, int PW) {
+  return dtype != JTSM_F32 && tuning("roi_pool_fwd_pack16", 1) && !tuning("roi_pool_fwd_keys", 0) &&
+         rmq_eligible(batch, channels, height, width, num_rois, PH, PW) &&
+         // measured (profiles/r2o_roi_pool_pack16.md): wins 15 % while the plane fits ONE band (<= 5.8 K cells: stride-16 /
+         // stride-32 maps); with row bands the band filter of the main loop costs more than the saved look-ups
+         // (75 x 100: 318 us against 228 us), so banded geometries keep the index tables unless forced (knob = 2)
+         (pick_bands(height, width, PH, true).nb == 1 ||
+          (tuning("roi_pool_fwd_pack16", 1) == 2 && pick_bands(height, width, PH, true).nb > 1));
+}
+
+template <typename T, typename A>
+int launch_rmqp(const void* input, int batch, int channels, int height, int width, int num_rois, int PH, int PW,
+                const PoolWorkspace& ws, void* output, void* argmax, cudaStream_t st) {
+  const RmqBands bands = pick_bands(height, width, PH, true);
+  if (bands.nb < 1) return JTSM_ERR_UNSUPPORTED;
+  const int real_planes = batch * channels;
+  const int planes = real_planes * bands.nb;
+  const int hw = bands.Hb * width;
+  const size_t stage = rk_stage_bytes(hw, (int)sizeof(T));
+  const int staged = bands.nb == 1 && rp_smem_core(hw) + stage <= 227 * 1024 && tuning("roi_pool_fwd_tma", 1);
+  const size_t smem = rp_smem_core(hw) + (staged ? stage : 0);
+  auto kern = roi_pool_fwd_rmqp_kernel<T, A, false>;
+  if (bands.nb > 1) kern = roi_pool_fwd_rmqp_kernel<T, A, true>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);  // per call: per device
+  const int per_sm = (int)((227 * 1024) / (smem + 1024)) >= 2 ? 2 : 1;
+  const int max_grid = num_sms() * per_sm;
+  int chunks = tuning("roi_pool_splits", 0);
+  if (chunks <= 0) {
+    const int cap = num_rois / 64 > 1 ? (num_rois / 64 < 64 ? num_rois / 64 : 64) : 1;
+    const int tail = planes % max_grid;
+    double best = 1e30;
+    chunks = 1;
+    for (int c = 1; c <= cap && tail > 0; ++c) {
+      const double cost = (double)((tail * c + max_grid - 1) / max_grid) / c + 0.01 * c;
+      if (cost < best - 1e-9) best = cost, chunks = c;
+    }
+  }
+  if (chunks > 64) chunks = 64;
+  const int items = planes * chunks;
+  const int grid = items < max_grid ? items : max_grid;
+  const unsigned long long in_bytes = (unsigned long long)real_planes * height * width * sizeof(T);
+  kern<<<grid, kRmqThreads, smem, st>>>((const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks,
+                                        items, staged, bands, ws, (T*)output, (A*)argmax);
+  count_launch();
+  return cuda_status();
+}
 template <typename T, typename A>
 int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, int width,
                         int num_rois, int PH, int PW, const PoolWorkspace& ws,
                         const float* row_scale, void* output, void* argmax, cudaStream_t st) {
   const int planes = batch * channels;
   const int algo = tuning("roi_pool_fwd_algo", 0);
+  if constexpr (sizeof(T) == 2) {
+    const int dt = std::is_same<T, __half>::value ? JTSM_F16 : JTSM_BF16;
+    if (rmqp_eligible(dt, batch, channels, height, width, num_rois, PH, PW))
+      return launch_rmqp<T, A>(input, batch, channels, height, width, num_rois, PH, PW, ws, output, argmax, st);
+  }
   if (rmq_eligible(batch, channels, height, width, num_rois, PH, PW))
     return launch_rmq<T, A, false>(input, batch, channels, height, width, num_rois, PH, PW, ws, MoiAux{}, output,
                                    argmax, st);
@@ -451,11 +518,12 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
 }
 
 int run_prep(const float* rois, int num_rois, int batch, int channels, int height, int width, float scale,
-             int PH, int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st, int force_desc = 0) {
+             int PH, int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st, int force_desc = 0,
+             bool packed = false) {
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
   cudaMemsetAsync(ws.ungrouped, 0, 2 * sizeof(int), st);  // ungrouped flag + slow-bin counter
   const int want_desc = force_desc || rmq_eligible(batch, channels, height, width, num_rois, PH, PW);
-  RmqBands bands = pick_bands(height, width, PH);
+  RmqBands bands = pick_bands(height, width, PH, packed);  // the geometry of the kernel that will read the descriptors
   if (bands.nb < 1) bands = {1, height, height};  // descriptors unused then (direct-scan kernels)
   roi_pool_prep_kernel<<<(num_rois + kPrepRois - 1) / kPrepRois, kPrepThreads, 0, st>>>(
       rois, num_rois, batch, height, width, scale, PH, PW, row_scale, want_desc, bands, ws);
@@ -508,8 +576,9 @@ extern "C" int jtsm_roi_pool_forward(const void* input, const float* rois, int d
     return JTSM_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = (cudaStream_t)stream;
   PoolWorkspace ws = carve_pool_workspace(workspace, batch, num_rois, pooled_h, pooled_w, 1);
+  const bool packed = rmqp_eligible(dtype, batch, channels, height, width, num_rois, pooled_h, pooled_w);
   int rc = run_prep(rois, num_rois, batch, channels, height, width, spatial_scale, pooled_h, pooled_w, row_scale,
-                    ws, st);
+                    ws, st, 0, packed);
   if (rc != JTSM_OK) return rc;
   JTSM_DISPATCH_DTYPE(dtype, T, JTSM_DISPATCH_ARGMAX(argmax_dtype, A, {
                         rc = launch_roi_pool_fwd<T, A>(input, batch, channels, height, width,

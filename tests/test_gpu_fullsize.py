@@ -258,6 +258,58 @@ def test_roi_pool_keyed_tables_equal_index_tables(cuda):
                 assert torch.equal(res[name][1], res["scan"][1]), (name, dt, shape)
 
 
+@pytest.mark.parametrize("shape,scale,pooled", [((1, 64, 75, 100), 1 / 8.0, (7, 7)),    # 40 B per cell: two row bands
+                                                ((2, 33, 38, 50), 1 / 16.0, (7, 7)),   # one band, bulk-copy staging
+                                                ((1, 24, 19, 25), 1 / 32.0, (14, 14)),
+                                                ((1, 16, 120, 67), 1 / 8.0, (7, 7))])   # odd width, three bands
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_roi_pool_packed_16bit_tables_equal_index_tables_and_scan(cuda, shape, scale, pooled, dtype):
+    """16-bit feature maps take the packed (value, index) tables (4 look-ups per bin, roi_pool_rmqp.cuh): same values
+    and arg-max as the index tables and the direct scan, including exact ties, -0.0 / +0.0, NaN, +-inf cells, boxes
+    reaching outside the map and un-grouped RoI order."""
+    from jtsm_b200 import _lib, ops
+
+    g = synth.generator(123)
+    n, c, h, w = shape
+    x = synth.feature_map(g, *shape) - 0.3
+    x[:, ::4] = torch.round(x[:, ::4] * 4) / 4  # exact ties after rounding to 16 bits
+    x[:, 1::6] *= 0.0
+    x[:, 1::6, ::3] = -0.0  # -0.0 next to +0.0: equal under `>`, first index wins
+    xd = x.to(dtype)
+    flat = xd.view(-1)
+    pos = torch.randperm(flat.numel(), generator=g)[:600]
+    flat[pos[:200]] = float("nan")
+    flat[pos[200:400]] = float("-inf")
+    flat[pos[400:600]] = float("inf")
+    xd[:, 2] = float("nan")  # whole planes that can never win
+    img_h, img_w = int(h / scale), int(w / scale)
+    boxes = [synth.proposals(g, 500, img_h, img_w) for _ in range(n)]
+    boxes[0][:6] = torch.tensor([[-300.0, -200.0, img_w + 400.0, img_h + 300.0], [0, 0, 1, 1], [5, 5, 5, 5],
+                                 [img_w - 2.0, img_h - 2.0, img_w + 50.0, img_h + 50.0], [0, 0, img_w, 3.0],
+                                 [3.0, 0, 4.0, img_h]])
+    rois = synth.rois_from_boxes(boxes)
+    rois = rois[torch.randperm(rois.shape[0], generator=g)]  # un-grouped batch indices
+    xd, rd = xd.to(cuda), rois.to(cuda)
+    res = {}
+    try:
+        for name, (pack, tma, algo) in {"packed": (2, 1, 0), "packed-no-tma": (2, 0, 0), "index": (0, 1, 0),
+                                        "scan": (0, 1, 1)}.items():
+            _lib.set_tuning("roi_pool_fwd_pack16", pack)
+            _lib.set_tuning("roi_pool_fwd_tma", tma)
+            _lib.set_tuning("roi_pool_fwd_algo", algo)
+            res[name] = ops.roi_pool_forward(xd, rd, scale, pooled)
+    finally:
+        _lib.set_tuning("roi_pool_fwd_pack16", 1)
+        _lib.set_tuning("roi_pool_fwd_tma", 1)
+        _lib.set_tuning("roi_pool_fwd_algo", 0)
+    for name in ("packed", "packed-no-tma", "index"):
+        a, b = res[name][0].float(), res["scan"][0].float()
+        assert torch.equal(torch.isnan(a), torch.isnan(b)), (name, dtype)
+        assert torch.equal(torch.nan_to_num(a, nan=0.0), torch.nan_to_num(b, nan=0.0)), (name, dtype)  # -0.0 == +0.0
+        assert torch.equal(res[name][1], res["scan"][1]), (name, dtype)
+    assert int((res["packed"][1] < 0).sum()) > 0  # bins that nothing can win really occur (int32 argmax: -1)
+
+
 @pytest.mark.parametrize("h,w,scale,pooled,dtype", [
     (150, 200, 1 / 8.0, (7, 7), torch.float32),    # c4's largest augmentation: 8 row bands
     (108, 144, 1 / 8.0, (7, 7), torch.bfloat16),   # 4 bands, 16-bit planes through the staging buffer
