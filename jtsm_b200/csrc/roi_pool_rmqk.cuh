@@ -313,6 +313,67 @@ __device__ __forceinline__ void rk_main_loop(const float* plane, const unsigned 
   }
 }
 
+// Main loop, row-mapped form (index tables, RoIs grouped by image, one band, no mask): the kernels are ISSUE bound
+// (profiles/r2o_roi_pool_pack16.md: 75 instructions per bin, a quarter of them look-ups), so this form removes
+// bookkeeping instead of look-ups.  A thread keeps ONE bin position and walks the RoIs: thread t -> RoI slot t / PP, bin
+// t % PP (G = 1024 / PP RoIs per pass; PP = 49: 980 of 1024 threads work), so the bin id, the output element and the
+// row-scale index advance by constants — no division by PP per bin, no per-bin output offset arithmetic — and the two
+// descriptor sets ping-pong between two register sets (no carried moves).  Same look-ups, same results.
+template <typename T, typename A>
+__device__ __forceinline__ void rk_main_loop_rows(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
+                                                  const RmqItem& it, int PP, int cpp, unsigned W, unsigned magic_pp,
+                                                  T* __restrict__ output, A* __restrict__ argmax) {
+  const unsigned G = (unsigned)kRmqThreads / (unsigned)PP;
+  const unsigned rl = __umulhi(threadIdx.x, magic_pp), bin = threadIdx.x - rl * (unsigned)PP;
+  if (rl >= G) return;  // the 1024 % PP threads without a slot
+  unsigned plane_s, tabs_s;  // volatile: keeps the shared-window bases in registers instead of re-deriving them per round
+  asm volatile("cvt.u32.u64 %0, %1;" : "=r"(plane_s) : "l"(__cvta_generic_to_shared(plane)));
+  asm volatile("cvt.u32.u64 %0, %1;" : "=r"(tabs_s) : "l"(__cvta_generic_to_shared(tabs)));
+  const unsigned r_end = (unsigned)(it.r0 + it.nr), W2 = 2u * W;
+  unsigned r = (unsigned)it.r0 + rl;
+  const uint32_t* pd = ws.bdesc + ((size_t)r * PP + bin);
+  const float* ps = ws.rscale + r;
+  unsigned o = r * (unsigned)cpp + (unsigned)(it.c * PP) + bin;
+  const unsigned dd = G * (unsigned)PP, dO = G * (unsigned)cpp;
+
+  struct Set {
+    unsigned x0, x1;
+    float s0, s1;
+  };
+  auto fetch = [&](Set& f, unsigned rr, const uint32_t* d, const float* sp) {
+    f.x0 = 0u, f.x1 = 0u, f.s0 = 0.f, f.s1 = 0.f;
+    if (rr < r_end) f.x0 = __ldg(d), f.s0 = __ldg(sp);
+    if (rr + G < r_end) f.x1 = __ldg(d + dd), f.s1 = __ldg(sp + G);
+  };
+  auto process = [&](const Set& f, unsigned oo) {
+    const RmqCand b0 = rmq_query_fast(plane_s, tabs_s + (f.x0 & 0x3FFFFu), ((f.x0 >> 18) & 15u) * W2, (f.x0 >> 22) & 31u);
+    const RmqCand b1 = rmq_query_fast(plane_s, tabs_s + (f.x1 & 0x3FFFFu), ((f.x1 >> 18) & 15u) * W2, (f.x1 >> 22) & 31u);
+    const T v0 = Elem<T>::from_f(__fmul_rn(b0.v, f.s0)), v1 = Elem<T>::from_f(__fmul_rn(b1.v, f.s1));
+    const A a0 = b0.v > -FLT_MAX ? (A)b0.i : Arg<A>::enc(-1), a1 = b1.v > -FLT_MAX ? (A)b1.i : Arg<A>::enc(-1);
+    if ((int)f.x0 < 0) {  // x >= 0: slow bin (left to the list) or past the end
+      output[oo] = v0;
+      argmax[oo] = a0;
+    }
+    if ((int)f.x1 < 0) {
+      output[oo + dO] = v1;
+      argmax[oo + dO] = a1;
+    }
+  };
+  if (r >= r_end) return;
+  Set fa, fb;
+  fetch(fa, r, pd, ps);
+  for (;;) {
+    fetch(fb, r + 2u * G, pd + 2u * dd, ps + 2u * G);
+    process(fa, o);
+    r += 2u * G, pd += 2u * dd, ps += 2u * G, o += 2u * dO;
+    if (r >= r_end) break;
+    fetch(fa, r + 2u * G, pd + 2u * dd, ps + 2u * G);
+    process(fb, o);
+    r += 2u * G, pd += 2u * dd, ps += 2u * G, o += 2u * dO;
+    if (r >= r_end) break;
+  }
+}
+
 // The few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%) of RoIs [r_lo, r_hi) for the plane
 // whose tables are resident.  The prep kernel lists them, so no warp of the main loop diverges into the long
 // path; the list is short and every CTA filters it for the RoI range it has just served.
@@ -373,6 +434,8 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
                          int W, int PH, int PW, int chunks, int num_items, int staged, RmqBands bands,
                          PoolWorkspace ws, MoiAux moi, T* __restrict__ output, A* __restrict__ argmax) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  const bool rows_loop = (staged & 2) != 0 && PH * PW <= kRmqThreads;  // bit 1 of `staged`: row-mapped main loop
+  staged &= 1;
   if (kMoi && !moi_rmq_gate(moi.slow_total, moi.total_bins, moi.gate_pct)) return;  // uniform: the list kernel runs
   const int hw = bands.Hb * W;  // cells of a full band = table stride (the whole plane when nb == 1)
   unsigned long long* bar = (unsigned long long*)smem_raw;
@@ -503,7 +566,9 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
         rmq_build_tables(plane, tabs, hw, W);
     }
     if (it.nr > 0) r_hi = it.r0 + it.nr;
-    if (ungrouped)
+    if (!kMoi && !kKeyed && !kBanded && !ungrouped && rows_loop)
+      rk_main_loop_rows<T, A>(plane, tabs, ws, it, PP, cpp, (unsigned)W, magic_pp, output, argmax);
+    else if (ungrouped)
       rk_main_loop<T, A, true, kMoi, kKeyed, kBanded>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
                                              moi.mask_scale, moi.zero_floor, bands.nb, v.band, (unsigned)(v.row0 * W),
                                              output, argmax);
