@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--no-train", action="store_true", help="skip the DDP training-step leg (train_images_per_sec)")
     ap.add_argument("--no-graph", action="store_true", help="launch the step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-sample-rois", type=int, default=0, help="0 = auto (about 10-30 s)")
+    ap.add_argument("--tune", nargs="*", default=[], help="library tuning knobs key=value (A/B experiments only)")
     return ap.parse_args()
 
 
@@ -175,6 +176,9 @@ def run_b200(a):
     import torch.distributed as dist
 
     from jtsm_b200 import _lib, hotpath
+    for kv in a.tune:  # A/B experiments only; the default run sets nothing
+        k, v = kv.split("=")
+        _lib.set_tuning(k, int(v))
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -488,6 +492,9 @@ def run_b200_infer(a):
     import torch.distributed as dist
 
     from jtsm_b200 import _lib, inferpath, synth
+    for kv in a.tune:  # A/B experiments only; the default run sets nothing
+        k, v = kv.split("=")
+        _lib.set_tuning(k, int(v))
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

@@ -19,6 +19,7 @@ Knob g_knobs[] = {
     {"roi_pool_splits", {0}},      // 0 = auto
     {"roi_pool_force_gmem", {0}},  // 1 = skip the smem-plane kernel
     {"roi_pool_fwd_rows", {0}},       // range-max kernel: row-mapped main loop (a thread keeps one bin position); opt-in
+    {"roi_pool_fwd_bandlist", {1}},   // banded planes: per-band RoI lists (1) or the band filter over all bins (0)
     {"roi_pool_fwd_pack16", {1}},     // bf16 / fp16 maps: packed (value, index) tables, 4 look-ups per bin (roi_pool_rmqp.cuh); 1 = single-band planes, 2 = banded too
     {"roi_pool_bwd_super_mb", {0}},   // 7 x 7 backward: MB of accumulation planes the warps in flight spread over (0 = auto)
     {"roi_pool_bwd_algo", {0}},    // 0 = auto (7 x 7: all 49 bins of a (RoI, channel) per lane, else vec4 folding), 1 = one RED per element, 3 = vec4 folding

@@ -51,6 +51,15 @@ roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, in
     if (ok) {
       atomicMin(ws.first + b, r);
       atomicMin(ws.neg_last + b, -r);
+      if (want_desc && bands.nb > 1 && bands.nb <= kBandListBands) {
+        // the bands this RoI has bins in (a bin belongs to the band of its first row; non-decreasing in the bin row)
+        const int b_lo = band_of(range_lo(ws.hbins[(size_t)r * PH]), bands);
+        const int b_hi = band_of(range_lo(ws.hbins[(size_t)r * PH + PH - 1]), bands);
+        for (int bb = b_lo; bb <= b_hi; ++bb) {
+          const int slot = b * kBandListBands + bb;
+          ws.band_list[(size_t)slot * num_rois + atomicAdd(ws.band_cnt + slot, 1)] = r;
+        }
+      }
     }
   }
   if (!want_desc) return;  // uniform
@@ -431,7 +440,9 @@ int launch_rmq(const void* input, int batch, int channels, int height, int width
     const unsigned long long in_bytes = (unsigned long long)real_planes * height * width * sizeof(T);
     // bit 1: the row-mapped main loop (11 % fewer instructions, same time: the kernel is LSU bound at c2 -- opt-in,
     // profiles/r2o_roi_pool_pack16.md)
-    const int flags = staged | (tuning("roi_pool_fwd_rows", 0) ? 2 : 0);
+    // bit 2: banded planes walk the per-band RoI lists instead of filtering every bin by its band
+    const int flags = staged | (tuning("roi_pool_fwd_rows", 0) ? 2 : 0) |
+                      (bands.nb > 1 && bands.nb <= kBandListBands && tuning("roi_pool_fwd_bandlist", 1) ? 4 : 0);
     kern<<<grid, kRmqThreads, smem, st>>>((const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks,
                                           items, flags, bands, ws, moi, (T*)output, (A*)argmax);
     count_launch();
@@ -481,8 +492,9 @@ int launch_rmqp(const void* input, int batch, int channels, int height, int widt
   const int items = planes * chunks;
   const int grid = items < max_grid ? items : max_grid;
   const unsigned long long in_bytes = (unsigned long long)real_planes * height * width * sizeof(T);
+  const int flags = staged | (bands.nb > 1 && bands.nb <= kBandListBands && tuning("roi_pool_fwd_bandlist", 1) ? 4 : 0);
   kern<<<grid, kRmqThreads, smem, st>>>((const T*)input, in_bytes, real_planes, channels, height, width, PH, PW, chunks,
-                                        items, staged, bands, ws, (T*)output, (A*)argmax);
+                                        items, flags, bands, ws, (T*)output, (A*)argmax);
   count_launch();
   return cuda_status();
 }
@@ -525,6 +537,7 @@ int run_prep(const float* rois, int num_rois, int batch, int channels, int heigh
              bool packed = false) {
   cudaMemsetAsync(ws.first, 0x7f, (size_t)batch * 2 * sizeof(int), st);
   cudaMemsetAsync(ws.ungrouped, 0, 2 * sizeof(int), st);  // ungrouped flag + slow-bin counter
+  cudaMemsetAsync(ws.band_cnt, 0, (size_t)batch * kBandListBands * sizeof(int), st);
   const int want_desc = force_desc || rmq_eligible(batch, channels, height, width, num_rois, PH, PW);
   RmqBands bands = pick_bands(height, width, PH, packed);  // the geometry of the kernel that will read the descriptors
   if (bands.nb < 1) bands = {1, height, height};  // descriptors unused then (direct-scan kernels)

@@ -374,6 +374,51 @@ __device__ __forceinline__ void rk_main_loop_rows(const float* plane, const unsi
   }
 }
 
+// Main loop of a BANDED plane over the per-band RoI list (PoolWorkspace::band_list): a warp takes one RoI of image n that has
+// bins in this band and serves its PP bins 64 at a time (two independent chains per lane), keeping those of the band.
+// Against the filter form above (every (band, plane) pass sweeps all bins of the call and skips, warp by warp, those of
+// other bands) the work per pass is proportional to the band's own RoIs.  Entries [q0, q1) of the list.
+template <typename T, typename A, bool kKeyed>
+__device__ __forceinline__ void rk_main_loop_list(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
+                                                  int n, int c, int q0, int q1, int num_rois, int PP, int cpp, unsigned W,
+                                                  unsigned hw, int band, unsigned arg_off, T* __restrict__ output,
+                                                  A* __restrict__ argmax) {
+  const unsigned plane_s = smem_u32(plane), tabs_s = smem_u32(tabs);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int* list = ws.band_list + (size_t)(n * kBandListBands + band) * num_rois;
+  for (int q = q0 + warp; q < q1; q += kRmqThreads / 32) {
+    const unsigned r = (unsigned)__ldg(list + q);
+    const float sc = __ldg(ws.rscale + r);
+    const unsigned i0 = r * (unsigned)PP, ob = r * (unsigned)cpp + (unsigned)(c * PP);
+    for (int b0 = 0; b0 < PP; b0 += 64) {
+      unsigned x[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int bin = b0 + k * 32 + lane;
+        x[k] = 0u;
+        if (bin < PP) {
+          x[k] = __ldg(ws.bdesc + i0 + bin);
+          if ((int)__ldg(ws.bband + i0 + bin) != band) x[k] = 0u;
+        }
+      }
+      RmqCand best[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+        best[k] = kKeyed ? rk_query_fast(plane_s, tabs_s, x[k], W, hw)
+                         : rmq_query_fast(plane_s, tabs_s + (x[k] & 0x3FFFFu), ((x[k] >> 18) & 15u) * (2u * W),
+                                          (x[k] >> 22) & 31u);
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+        if ((int)x[k] < 0) {
+          const unsigned o = ob + (unsigned)(b0 + k * 32 + lane);
+          const bool none = !(best[k].v > -FLT_MAX);
+          output[o] = Elem<T>::from_f(__fmul_rn(best[k].v, sc));
+          argmax[o] = none ? Arg<A>::enc(-1) : (A)(best[k].i + arg_off);
+        }
+    }
+  }
+}
+
 // The few bins without a fast descriptor (empty, elongated, > 16 cells: ~2%) of RoIs [r_lo, r_hi) for the plane
 // whose tables are resident.  The prep kernel lists them, so no warp of the main loop diverges into the long
 // path; the list is short and every CTA filters it for the RoI range it has just served.
@@ -381,7 +426,10 @@ template <typename T, typename A, bool kMoi, bool kKeyed>
 __device__ __forceinline__ void rk_slow_pass(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
                                              const T* __restrict__ input, const RmqVPlane& vpl, int r_lo, int r_hi,
                                              bool ungrouped, int channels, int hw, int H, int W, int PH, int PW,
-                                             const RmqBands& bands, T* __restrict__ output, A* __restrict__ argmax) {
+                                             const RmqBands& bands, T* __restrict__ output, A* __restrict__ argmax,
+                                             int chunks = 0) {
+  // chunks > 0 (band-list mode): the CTA has served chunks [r_lo, r_hi) of this (band, plane) -- the slow list is dealt
+  // by entry number modulo `chunks`, and the image is checked per entry
   const int PP = PH * PW;
   if (kMoi) return;  // the visit-list kernel answers every bin without a fast descriptor
   const int n = vpl.nc / channels, c = vpl.nc - n * channels;
@@ -390,8 +438,13 @@ __device__ __forceinline__ void rk_slow_pass(const float* plane, const unsigned 
     const int e = __ldg(ws.slow_list + j);
     const int id = e & 0x3FFFFFFF;
     const int rr = id / PP, b = id - rr * PP;
-    if (rr < r_lo || rr >= r_hi) continue;
-    if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+    if (chunks > 0) {
+      const int jc = j % chunks;
+      if (jc < r_lo || jc >= r_hi || __ldg(ws.batch_idx + rr) != n) continue;
+    } else {
+      if (rr < r_lo || rr >= r_hi) continue;
+      if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+    }
     const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
     const int ph = b / PW, pw = b - ph * PW;
     const uint32_t hb = __ldg(ws.hbins + (size_t)rr * PH + ph), wb = __ldg(ws.wbins + (size_t)rr * PW + pw);
@@ -435,6 +488,8 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
                          PoolWorkspace ws, MoiAux moi, T* __restrict__ output, A* __restrict__ argmax) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const bool rows_loop = (staged & 2) != 0 && PH * PW <= kRmqThreads;  // bit 1 of `staged`: row-mapped main loop
+  const bool band_list = kBanded && (staged & 4) != 0;                 // bit 2: per-band RoI lists (banded planes)
+  const int num_rois = ws.num_rois;
   staged &= 1;
   if (kMoi && !moi_rmq_gate(moi.slow_total, moi.total_bins, moi.gate_pct)) return;  // uniform: the list kernel runs
   const int hw = bands.Hb * W;  // cells of a full band = table stride (the whole plane when nb == 1)
@@ -501,7 +556,7 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
     if (vp != cur_vp) {
       if (cur_vp >= 0)
         rk_slow_pass<T, A, kMoi, kKeyed>(plane, tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW,
-                                         bands, output, argmax);
+                                         bands, output, argmax, band_list ? chunks : 0);
       __syncthreads();  // everyone is done with the old plane and tables
       // ---- unpack: staged bytes (or global memory) -> fp32 plane, sanitised; min / max of the plane
       float lo = FLT_MAX, hi = -FLT_MAX;
@@ -560,13 +615,20 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
       cur_vp = vp;
       cur = v;
       r_lo = it.r0, r_hi = it.r0;
+      if (band_list) r_lo = chunk, r_hi = chunk;  // chunk numbers served, for the slow pass
       if (kKeyed)
         rk_build_tables(plane, tabs, hw, W, stats[0], stats[1]);
       else
         rmq_build_tables(plane, tabs, hw, W);
     }
     if (it.nr > 0) r_hi = it.r0 + it.nr;
-    if (!kMoi && !kKeyed && !kBanded && !ungrouped && rows_loop)
+    if (band_list) {
+      r_hi = chunk + 1;
+      const int cnt = __ldg(ws.band_cnt + it.n * kBandListBands + v.band);
+      const int q0 = (int)((long long)cnt * chunk / chunks), q1 = (int)((long long)cnt * (chunk + 1) / chunks);
+      rk_main_loop_list<T, A, kKeyed>(plane, tabs, ws, it.n, it.c, q0, q1, num_rois, PP, cpp, (unsigned)W, (unsigned)hw,
+                                      v.band, (unsigned)(v.row0 * W), output, argmax);
+    } else if (!kMoi && !kKeyed && !kBanded && !ungrouped && rows_loop)
       rk_main_loop_rows<T, A>(plane, tabs, ws, it, PP, cpp, (unsigned)W, magic_pp, output, argmax);
     else if (ungrouped)
       rk_main_loop<T, A, true, kMoi, kKeyed, kBanded>(plane, tabs, ws, it, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
@@ -579,7 +641,7 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
   }
   if (cur_vp >= 0)
     rk_slow_pass<T, A, kMoi, kKeyed>(plane, tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW, bands,
-                                     output, argmax);
+                                     output, argmax, band_list ? chunks : 0);
 }
 
 }  // namespace jtsm

@@ -169,20 +169,66 @@ __device__ __forceinline__ void rp_main_loop(const unsigned* tabs, const PoolWor
   }
 }
 
+// banded plane over the per-band RoI list (see rk_main_loop_list): a warp per RoI, 64 bins at a time
+template <typename T, typename A>
+__device__ __forceinline__ void rp_main_loop_list(const unsigned* tabs, const PoolWorkspace& ws, int n, int c, int q0, int q1,
+                                                  int num_rois, int PP, int cpp, unsigned W, int band, unsigned arg_off,
+                                                  T* __restrict__ output, A* __restrict__ argmax) {
+  const unsigned tabs_s = smem_u32(tabs);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int* list = ws.band_list + (size_t)(n * kBandListBands + band) * num_rois;
+  for (int q = q0 + warp; q < q1; q += kRmqThreads / 32) {
+    const unsigned r = (unsigned)__ldg(list + q);
+    const float sc = __ldg(ws.rscale + r);
+    const unsigned i0 = r * (unsigned)PP, ob = r * (unsigned)cpp + (unsigned)(c * PP);
+    for (int b0 = 0; b0 < PP; b0 += 64) {
+      unsigned x[2], best[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int bin = b0 + k * 32 + lane;
+        x[k] = 0u;
+        if (bin < PP) {
+          x[k] = __ldg(ws.bdesc + i0 + bin);
+          if ((int)__ldg(ws.bband + i0 + bin) != band) x[k] = 0u;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const unsigned base = tabs_s + 2u * (x[k] & 0x3FFFFu), dh = ((x[k] >> 18) & 15u) * (4u * W), db = 2u * ((x[k] >> 22) & 31u);
+        best[k] = max(max(lds_u32(base), lds_u32(base + db)), max(lds_u32(base + dh), lds_u32(base + dh + db)));
+      }
+#pragma unroll
+      for (int k = 0; k < 2; ++k)
+        if ((int)x[k] < 0) {
+          const unsigned o = ob + (unsigned)(b0 + k * 32 + lane);
+          const bool none = (best[k] >> 16) == 0u;
+          const float v = none ? -FLT_MAX : rp_value<T>(best[k]);
+          output[o] = Elem<T>::from_f(__fmul_rn(v, sc));
+          argmax[o] = none ? Arg<A>::enc(-1) : (A)(0xFFFFu - (best[k] & 0xFFFFu) + arg_off);
+        }
+    }
+  }
+}
+
 template <typename T, typename A>
 __device__ __forceinline__ void rp_slow_pass(const unsigned* tabs, const PoolWorkspace& ws, const T* __restrict__ input,
                                              const RmqVPlane& vpl, int r_lo, int r_hi, bool ungrouped, int channels, int hw,
                                              int H, int W, int PH, int PW, const RmqBands& bands, T* __restrict__ output,
-                                             A* __restrict__ argmax) {
-  const int PP = PH * PW;
+                                             A* __restrict__ argmax, int chunks = 0) {
+  const int PP = PH * PW;  // chunks > 0: band-list mode, [r_lo, r_hi) are chunk numbers (see rk_slow_pass)
   const int n = vpl.nc / channels, c = vpl.nc - n * channels;
   const int ns = __ldg(ws.slow_count);
   for (int j = threadIdx.x; j < ns; j += kRmqThreads) {
     const int e = __ldg(ws.slow_list + j);
     const int id = e & 0x3FFFFFFF;
     const int rr = id / PP, b = id - rr * PP;
-    if (rr < r_lo || rr >= r_hi) continue;
-    if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+    if (chunks > 0) {
+      const int jc = j % chunks;
+      if (jc < r_lo || jc >= r_hi || __ldg(ws.batch_idx + rr) != n) continue;
+    } else {
+      if (rr < r_lo || rr >= r_hi) continue;
+      if (ungrouped && __ldg(ws.batch_idx + rr) != n) continue;
+    }
     const unsigned so = ((unsigned)rr * (unsigned)channels + (unsigned)c) * (unsigned)PP + (unsigned)b;
     const int ph = b / PW, pw = b - ph * PW;
     const uint32_t hb = __ldg(ws.hbins + (size_t)rr * PH + ph), wb = __ldg(ws.wbins + (size_t)rr * PW + pw);
@@ -218,6 +264,8 @@ roi_pool_fwd_rmqp_kernel(const T* __restrict__ input, unsigned long long input_b
                          int W, int PH, int PW, int chunks, int num_items, int staged, RmqBands bands, PoolWorkspace ws,
                          T* __restrict__ output, A* __restrict__ argmax) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
+  const bool band_list = kBanded && (staged & 4) != 0;  // bit 2 of `staged`: per-band RoI lists
+  staged &= 1;
   const int hw = bands.Hb * W;
   unsigned long long* bar = (unsigned long long*)smem_raw;
   unsigned* tabs = (unsigned*)(smem_raw + kRpHeader);
@@ -270,7 +318,8 @@ roi_pool_fwd_rmqp_kernel(const T* __restrict__ input, unsigned long long input_b
     const RmqItem it = rmq_item(v.nc, chunk, chunks, channels, ws);
     if (vp != cur_vp) {
       if (cur_vp >= 0)
-        rp_slow_pass<T, A>(tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW, bands, output, argmax);
+        rp_slow_pass<T, A>(tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW, bands, output, argmax,
+                           band_list ? chunks : 0);
       __syncthreads();  // everyone is done with the old tables
       if (in_flight == vp) {
         mbar_wait(bar, parity);
@@ -294,10 +343,17 @@ roi_pool_fwd_rmqp_kernel(const T* __restrict__ input, unsigned long long input_b
       cur_vp = vp;
       cur = v;
       r_lo = it.r0, r_hi = it.r0;
+      if (band_list) r_lo = chunk, r_hi = chunk;
       rp_build_tables(tabs, hw, W);
     }
     if (it.nr > 0) r_hi = it.r0 + it.nr;
-    if (ungrouped)
+    if (band_list) {
+      r_hi = chunk + 1;
+      const int cnt = __ldg(ws.band_cnt + it.n * kBandListBands + v.band);
+      const int q0 = (int)((long long)cnt * chunk / chunks), q1 = (int)((long long)cnt * (chunk + 1) / chunks);
+      rp_main_loop_list<T, A>(tabs, ws, it.n, it.c, q0, q1, ws.num_rois, PP, cpp, (unsigned)W, v.band,
+                              (unsigned)(v.row0 * W), output, argmax);
+    } else if (ungrouped)
       rp_main_loop<T, A, true, kBanded>(tabs, ws, it, PP, cpp, (unsigned)W, magic_pp, v.band, (unsigned)(v.row0 * W), output,
                                         argmax);
     else
@@ -305,7 +361,8 @@ roi_pool_fwd_rmqp_kernel(const T* __restrict__ input, unsigned long long input_b
                                          output, argmax);
   }
   if (cur_vp >= 0)
-    rp_slow_pass<T, A>(tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW, bands, output, argmax);
+    rp_slow_pass<T, A>(tabs, ws, input, cur, r_lo, r_hi, ungrouped, channels, hw, H, W, PH, PW, bands, output, argmax,
+                       band_list ? chunks : 0);
 }
 
 }  // namespace jtsm

@@ -243,17 +243,20 @@ def test_roi_pool_keyed_tables_equal_index_tables(cuda):
             xd, rd = x.to(cuda).to(dt), rois.to(cuda)
             res = {}
             try:
-                for name, (keys, tma, algo) in {"keyed+tma": (1, 1, 0), "keyed": (1, 0, 0), "index": (0, 1, 0),
-                                                "index-no-tma": (0, 0, 0), "scan": (0, 1, 1)}.items():
+                for name, (keys, tma, algo, rows) in {"keyed+tma": (1, 1, 0, 0), "keyed": (1, 0, 0, 0), "index": (0, 1, 0, 0),
+                                                      "index-no-tma": (0, 0, 0, 0), "index-rows": (0, 1, 0, 1),
+                                                      "scan": (0, 1, 1, 0)}.items():
                     _lib.set_tuning("roi_pool_fwd_keys", keys)
                     _lib.set_tuning("roi_pool_fwd_tma", tma)
                     _lib.set_tuning("roi_pool_fwd_algo", algo)
+                    _lib.set_tuning("roi_pool_fwd_rows", rows)  # row-mapped main loop (single-image RoI order only)
                     res[name] = ops.roi_pool_forward(xd, rd, scale, (7, 7))
             finally:
                 _lib.set_tuning("roi_pool_fwd_keys", 0)
                 _lib.set_tuning("roi_pool_fwd_tma", 1)
                 _lib.set_tuning("roi_pool_fwd_algo", 0)
-            for name in ("keyed+tma", "keyed", "index", "index-no-tma"):
+                _lib.set_tuning("roi_pool_fwd_rows", 0)
+            for name in ("keyed+tma", "keyed", "index", "index-no-tma", "index-rows"):
                 assert torch.equal(res[name][0], res["scan"][0]), (name, dt, shape)
                 assert torch.equal(res[name][1], res["scan"][1]), (name, dt, shape)
 
@@ -333,16 +336,29 @@ def test_roi_pool_banded_planes_vs_oracle(cuda, oracle, h, w, scale, pooled, dty
     ref, rarg = oracle.roi_pool_forward(x.float().numpy(), rois.numpy(), scale, pooled)
     res = {}
     try:
-        for name, (keys, tma, algo) in {"bands": (0, 1, 0), "bands-no-tma": (0, 0, 0), "bands-keyed": (1, 1, 0),
-                                        "scan": (0, 1, 1)}.items():
+        # band lists (default) / band filter; index, keyed and (16-bit maps) packed tables; un-grouped RoI order too
+        for name, (keys, tma, algo, lists, pack) in {"bands": (0, 1, 0, 1, 0), "bands-filter": (0, 1, 0, 0, 0),
+                                                     "bands-no-tma": (0, 0, 0, 1, 0), "bands-keyed": (1, 1, 0, 1, 0),
+                                                     "bands-keyed-filter": (1, 1, 0, 0, 0), "bands-packed": (0, 1, 0, 1, 2),
+                                                     "bands-packed-filter": (0, 1, 0, 0, 2), "scan": (0, 1, 1, 1, 0)}.items():
             _lib.set_tuning("roi_pool_fwd_keys", keys)
             _lib.set_tuning("roi_pool_fwd_tma", tma)
             _lib.set_tuning("roi_pool_fwd_algo", algo)
+            _lib.set_tuning("roi_pool_fwd_bandlist", lists)
+            _lib.set_tuning("roi_pool_fwd_pack16", pack)
             res[name] = ops.roi_pool_forward(x.to(cuda), rois.to(cuda), scale, pooled)
+        perm = torch.randperm(rois.shape[0], generator=g)
+        _lib.set_tuning("roi_pool_fwd_keys", 0)
+        _lib.set_tuning("roi_pool_fwd_pack16", 1)
+        shuffled = ops.roi_pool_forward(x.to(cuda), rois[perm].to(cuda), scale, pooled)
     finally:
         _lib.set_tuning("roi_pool_fwd_keys", 0)
         _lib.set_tuning("roi_pool_fwd_tma", 1)
         _lib.set_tuning("roi_pool_fwd_algo", 0)
+        _lib.set_tuning("roi_pool_fwd_bandlist", 1)
+        _lib.set_tuning("roi_pool_fwd_pack16", 1)
+    assert np.array_equal(shuffled[0].float().cpu().numpy(), ref[perm.numpy()]), "un-grouped RoIs"
+    assert np.array_equal(shuffled[1].cpu().numpy(), rarg[perm.numpy()]), "un-grouped RoIs"
     for name, (out, arg) in res.items():
         assert np.array_equal(out.float().cpu().numpy(), ref), name
         assert np.array_equal(arg.cpu().numpy(), rarg), name
