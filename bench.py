@@ -189,6 +189,8 @@ def run_b200(a):
     dev = torch.device("cuda", local)
     numa_bound = bind_to_gpu_numa_node(local) if world > 1 else False
     if world > 1:
+        # the training leg captures a DDP step into a CUDA graph: PyTorch asks for NCCL's async error handling to be off
+        os.environ.setdefault("TORCH_NCCL_ASYNC_ERROR_HANDLING", "0")
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()  # fail loudly if libjtsm_b200.so is missing
 
@@ -384,53 +386,70 @@ def train_leg(a, wl, dev, world, rank, barrier):
     from jtsm_b200 import trainstep
 
     cfg = wl["cfg"]
-    ts = trainstep.TrainStep(cfg, dev, world=world, tf32=True)
+    ts = trainstep.TrainStep(cfg, dev, world=world, tf32=True, fused_sgd=True)
     batch = ts.make_batch(wl)
     steps = max(3, min(a.steps, 10))
 
-    def timed(sync):
+    def timed(fn):
         for _ in range(3):
-            ts.step(batch, sync=sync)
+            fn()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for _ in range(steps):
-            ts.step(batch, sync=sync)
+            fn()
         e1.record()
         barrier()
         return e0.elapsed_time(e1) / steps
 
-    ms = timed(True)
-    ms_local, ar_alone = None, None
+    ms_eager = timed(lambda: ts.step(batch, sync=True))
+    ar_alone = None
     if world > 1:
         flat = torch.empty(ts.num_params(), dtype=torch.float32, device=dev)
-        for _ in range(2):
-            dist.all_reduce(flat)
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            dist.all_reduce(flat)
-        e1.record()
-        barrier()
-        ar_alone = e0.elapsed_time(e1) / steps
-        ms_local = timed(False)  # same step without the gradient all-reduce (replicas diverge: timing only, run last)
-    tm = torch.tensor([ms, ms_local or 0.0, ar_alone or 0.0], dtype=torch.float64, device=dev)
+        ar_alone = timed(lambda: dist.all_reduce(flat))
+        del flat
+    # the whole step (forward, backward, DDP all-reduce, optimizer) as ONE CUDA graph: the eager step is launch bound
+    # (~105 kernels, 3.8 ms of GPU work in 5.6 ms at N = 1); skipped with --no-graph or when the capture fails
+    ms_graph, graph_err = None, None
+    if not a.no_graph:
+        try:
+            ts.capture(batch)
+        except Exception as e:  # noqa: BLE001 -- reported in the JSON line, the eager number stands
+            graph_err = "%s: %s" % (type(e).__name__, str(e).splitlines()[0][:200])
+        ok = torch.tensor([0.0 if graph_err else 1.0], device=dev)
+        if world > 1:  # replay only if EVERY rank captured (the graph holds the all-reduce)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok) > 0:
+            ms_graph = timed(ts.replay)
+        elif graph_err is None:
+            graph_err = "capture failed on another rank"
+    loss = None
+    if world == 1 and (ms_graph is not None or graph_err is None):  # after a failed capture the RNG state is unusable
+        loss = float(ts.replay() if ms_graph is not None else ts.step(batch))
+    ms_local = None
+    if world > 1 and graph_err is None:  # no all-reduce: replicas diverge, timing only, run last
+        ms_local = timed(lambda: ts.step(batch, sync=False))
+    tm = torch.tensor([ms_eager, ms_local or 0.0, ar_alone or 0.0, ms_graph if ms_graph is not None else -1.0],
+                      dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-    ms, ms_local, ar_alone = (float(v) for v in tm.tolist())
-    loss = float(ts.step(batch)) if world == 1 else None
+    ms_eager, ms_local, ar_alone, ms_graph = (float(v) for v in tm.tolist())
+    if ms_graph <= 0:
+        ms_graph = None
+    ms = ms_graph if ms_graph is not None else ms_eager
     return {
         "train_images_per_sec": world * cfg["N"] * 1e3 / ms,
-        "allreduce_ms": (ms - ms_local) if world > 1 else 0.0,
+        "allreduce_ms": (ms_eager - ms_local) if (world > 1 and ms_local) else (0.0 if world == 1 else None),
         "train_step": {
-            "ms_per_step": ms, "ms_per_step_without_allreduce": ms_local if world > 1 else None,
+            "ms_per_step": ms, "launch": "cuda_graph_replay" if ms_graph is not None else "eager",
+            "ms_per_step_eager": ms_eager, "graph_error": graph_err,
+            "ms_per_step_without_allreduce": ms_local if world > 1 else None,
             "allreduce_alone_ms": ar_alone if world > 1 else None, "allreduce_bytes": 4 * ts.num_params(),
-            "allreduce_ms_means": "exposed: step time under DDP minus the same step inside no_sync()",
+            "allreduce_ms_means": "exposed, eager: step time under DDP minus the same step inside no_sync()",
             "params": ts.num_params(), "images_per_gpu": cfg["N"], "steps": steps,
             "what": "RoIPool x objectness -> fc6/fc7 (torch GEMMs, TF32 tensor cores) -> WSDDN MIL + BCE -> Kr x "
                     "(pseudo-gt, label assignment, weighted CE[, box reg]) -> backward (autograd Functions, DDP "
-                    "gradient all-reduce over NCCL) -> SGD momentum step; conv5 map resident on the device",
+                    "gradient all-reduce over NCCL) -> fused SGD momentum step; conv5 map resident on the device",
             "loss_after": loss,
         },
     }

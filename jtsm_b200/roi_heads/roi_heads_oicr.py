@@ -102,12 +102,20 @@ class OICRROIHeadsB200(nn.Module):
 
     # ------------------------------------------------------------------ forward
     def forward(self, images, features: Dict[str, torch.Tensor], proposals: List[Instances],
-                targets: Optional[List[Instances]] = None):
-        """Training: (proposals, losses).  Inference: (pred_instances, {}, all_scores, all_boxes)  (roi_heads_oicr.py:302-345)."""
-        self.gt_classes_img, self.gt_classes_img_int, self.gt_classes_img_oh = get_image_level_gt(targets, self.num_classes)
+                targets: Optional[List[Instances]] = None, image_level_gt=None):
+        """Training: (proposals, losses).  Inference: (pred_instances, {}, all_scores, all_boxes)  (roi_heads_oicr.py:302-345).
+        image_level_gt (extension): a ready `(gt_classes_img, gt_classes_img_int, gt_classes_img_oh)` triple -- what
+        `get_image_level_gt(targets)` returns, whose `torch.unique` synchronises -- so that a whole training step can be
+        captured into a CUDA graph (trainstep.TrainStep.capture); gt_classes_img_int may be the device-side class lists of
+        `ops.image_class_lists`."""
+        if image_level_gt is not None:
+            self.gt_classes_img, self.gt_classes_img_int, self.gt_classes_img_oh = image_level_gt
+        else:
+            self.gt_classes_img, self.gt_classes_img_int, self.gt_classes_img_oh = get_image_level_gt(targets,
+                                                                                                     self.num_classes)
         self.images = images
         if self.training:
-            assert targets, "'targets' argument is required during training"
+            assert targets or image_level_gt is not None, "'targets' argument is required during training"
             del targets
             losses = self._forward_box(features, proposals)
             self.iter += 1

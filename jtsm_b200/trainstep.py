@@ -41,7 +41,7 @@ def build_heads(cfg, fc_dims=(4096, 4096)):
 
 
 class TrainStep:
-    def __init__(self, cfg, device, world=1, fc_dims=(4096, 4096), lr=1e-3, tf32=False):
+    def __init__(self, cfg, device, world=1, fc_dims=(4096, 4096), lr=1e-3, tf32=False, fused_sgd=False):
         self.cfg, self.dev, self.world = cfg, device, world
         if tf32:  # the fc GEMMs are torch's; TF32 tensor cores keep fp32 storage / fp32 accumulate (process-wide switch)
             torch.backends.cuda.matmul.allow_tf32 = True
@@ -50,10 +50,16 @@ class TrainStep:
         self.heads.train()
         self.model = self.heads
         if world > 1:
-            self.model = nn.parallel.DistributedDataParallel(self.heads, device_ids=[device.index],
-                                                             broadcast_buffers=False, gradient_as_bucket_view=True)
+            # constructed on a side stream: what PyTorch asks for when the backward is later captured into a CUDA graph
+            side = torch.cuda.Stream(device)
+            side.wait_stream(torch.cuda.current_stream(device))
+            with torch.cuda.stream(side):
+                self.model = nn.parallel.DistributedDataParallel(self.heads, device_ids=[device.index],
+                                                                 broadcast_buffers=False, gradient_as_bucket_view=True)
+            torch.cuda.current_stream(device).wait_stream(side)
         self.params = [p for p in self.heads.parameters() if p.requires_grad]
-        self.opt = torch.optim.SGD(self.params, lr=lr, momentum=0.9, weight_decay=5e-4)
+        self.opt = torch.optim.SGD(self.params, lr=lr, momentum=0.9, weight_decay=5e-4, fused=bool(fused_sgd))
+        self.graph = None
 
     def num_params(self):
         return sum(p.numel() for p in self.params)
@@ -69,7 +75,13 @@ class TrainStep:
                                        objectness_logits=wl["objectness"][off:off + n].to(self.dev)))
             targets.append(Instances((cfg["img_h"], cfg["img_w"]), gt_classes=l.to(self.dev)))
             off += n
-        return dict(feat=feat, proposals=proposals, targets=targets)
+        # image-level labels ready on the device (get_image_level_gt's torch.unique would synchronise every step)
+        from . import ops
+        from .roi_heads import get_image_level_gt
+
+        gt_img, gt_int, oh = get_image_level_gt(targets, cfg["K"])
+        lists = ops.image_class_lists([g.cpu() for g in gt_int], self.dev)
+        return dict(feat=feat, proposals=proposals, targets=targets, image_level_gt=(gt_img, lists, oh))
 
     def step(self, batch, sync=True):
         """forward + backward (+ DDP all-reduce) + optimizer step -> total loss (device scalar)."""
@@ -77,12 +89,47 @@ class TrainStep:
         batch["feat"].grad = None
         ctx = self.model.no_sync() if (self.world > 1 and not sync) else _null()
         with ctx:
-            _, losses = self.model(None, {"conv5": batch["feat"]}, batch["proposals"], batch["targets"])
+            _, losses = self.model(None, {"conv5": batch["feat"]}, batch["proposals"], batch["targets"],
+                                   image_level_gt=batch.get("image_level_gt"))
             loss = sum(losses.values())
             loss.backward()
         self.opt.step()
-        self.last_losses = losses
+        self.last_losses = {k: v.detach() for k, v in losses.items()}  # detached: no autograd graph is kept alive
         return loss.detach()
+
+    # ------------------------------------------------------------------ the whole step as ONE CUDA graph
+    def capture(self, batch, warmup=11):
+        """forward + backward (+ DDP all-reduce) + optimizer step captured into a CUDA graph over the STATIC tensors of
+        `batch` (copy new inputs into them, then `replay()`).  Everything between the Linear layers goes through the C
+        ABI on the capturing stream and nothing synchronises (the image-level labels come precomputed), so the step's
+        ~105 launches cost one graph launch.  PyTorch's recipe for whole-network capture: eager warm-up iterations on a
+        side stream (>= 11 with DDP), gradients set to None before the capture so that they live in the graph's pool."""
+        dev = self.dev
+        self.last_losses = None  # an autograd graph kept alive from an earlier stream would pin its AccumulateGrad nodes
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup if self.world > 1 else 3):
+                self.step(batch)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.opt.zero_grad(set_to_none=True)
+        batch["feat"].grad = None
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            _, losses = self.model(None, {"conv5": batch["feat"]}, batch["proposals"], batch["targets"],
+                                   image_level_gt=batch.get("image_level_gt"))
+            loss = sum(losses.values())
+            loss.backward()
+            self.opt.step()
+            self.graph_loss = loss.detach()
+            del loss, losses
+        self.graph_batch = batch
+        return self.graph
+
+    def replay(self):
+        self.graph.replay()
+        return self.graph_loss
 
 
 class _null:

@@ -25,3 +25,22 @@ for _ in range(n):
 e1.record()
 torch.cuda.synchronize()
 print("ms_per_step", e0.elapsed_time(e1) / n)
+
+if len(sys.argv) > 2 and sys.argv[2] == "graph":
+    import traceback
+
+    ts2 = TrainStep(wl["cfg"], dev, world=1, tf32=True, lr=1e-3, fused_sgd=True)
+    b2 = ts2.make_batch(wl)
+    try:
+        ts2.capture(b2)
+        for _ in range(3):
+            ts2.replay()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(n):
+            ts2.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        print("graph ms_per_step", e0.elapsed_time(e1) / n, "loss", float(ts2.graph_loss))
+    except Exception:
+        traceback.print_exc()
