@@ -106,6 +106,10 @@ class TrainStep:
         side stream (>= 11 with DDP), gradients set to None before the capture so that they live in the graph's pool."""
         dev = self.dev
         self.last_losses = None  # an autograd graph kept alive from an earlier stream would pin its AccumulateGrad nodes
+        try:  # parameters that stepped eagerly on another stream keep their AccumulateGrad nodes: harmless here, noisy
+            torch.autograd.graph.set_warn_on_accumulate_grad_stream_mismatch(False)
+        except AttributeError:
+            pass
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
