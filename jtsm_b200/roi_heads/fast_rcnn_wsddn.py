@@ -14,7 +14,8 @@ return values, the math behind them on the sm_100a kernels:
 `Instances` or jtsm_b200.structures.Instances).  With `cmil=True` (WSL.CMIL) the training forward runs `forward_cmil`
 (:621-667): objectness = row sums of the scores, pairwise IoU of the proposals and the ROIMerge clique merge of the C / D
 rows, all on the device (the reference copies S, the R x R IoU matrix, C and D to the host for its CPU-only op), and
-returns the 4-tuple of the reference.  The ContextLocNet variant (`context=True`) is outside the ported path and raises."""
+returns the 4-tuple of the reference.  `context=True` is the ContextLocNet variant (`forward_contextlocnet`, :600-619):
+class stream on the RoI features, detection stream = det(frame) - det(context) of ROILoopPool's three pools."""
 from typing import Dict, Union
 
 import torch
@@ -95,11 +96,12 @@ class WSDDNOutputLayers(nn.Module):
         gt_classes_img_oh (extension, optional): image-level one-hot labels [N, K]; when the caller already has them
         the BCE loss comes out of the same launch and `losses()` reuses it."""
         if context:
-            raise NotImplementedError("ContextLocNet (forward_contextlocnet) is outside the ported hot path")
-        if x.dim() > 2:
-            x = torch.flatten(x, start_dim=1)
-        C = self.cls(x)
-        D = self.det(x)
+            C, D = self.forward_contextlocnet(x, proposals=proposals)
+        else:
+            if x.dim() > 2:
+                x = torch.flatten(x, start_dim=1)
+            C = self.cls(x)
+            D = self.det(x)
         merged = self.cmil and self.training
         if merged:
             C, D, Oscores, Oproposal_deltas = self.forward_cmil(C, D, proposals)
@@ -113,6 +115,13 @@ class WSDDNOutputLayers(nn.Module):
         if merged:
             return scores, proposal_deltas, Oscores, Oproposal_deltas
         return scores, proposal_deltas
+
+    def forward_contextlocnet(self, x, proposals=None):
+        """ContextLocNet streams (fast_rcnn_wsddn.py:600-619): `x` = (RoI, frame, context) features -- the three pools of
+        ROILoopPool after the box head -- -> (cls(x), det(frame) - det(context))."""
+        x, Fx, Cx = x[:]
+        x, Fx, Cx = (t.flatten(start_dim=1) if t.dim() > 2 else t for t in (x, Fx, Cx))
+        return self.cls(x), self.det(Fx) - self.det(Cx)
 
     def forward_cmil(self, C, D, proposals):
         """fast_rcnn_wsddn.py:621-667: -> (MC, MD, scores of the un-merged rows, zero deltas).  One image per call, as in

@@ -1,8 +1,11 @@
-"""`WSDDNROIHeadsB200` and `JTSMROIHeadsB200`: the other two registered WSL heads on the sm_100a path.
+"""`WSDDNROIHeadsB200`, `ContextLocNetROIHeadsB200` and `JTSMROIHeadsB200`: the other registered WSL heads on the sm_100a path.
 
 * WSDDNROIHeads (projects/WSL/wsl/modeling/roi_heads/roi_heads_wsddn.py:28-330): pooling x objectness -> box head ->
   `WSDDNOutputLayers` -> BCE; no refinement branches.  = `OICRROIHeadsB200` with `refine_K = 0`, kept as its own class so
   that `MODEL.ROI_HEADS.NAME` and `from_config` read like the reference's.
+* ContextLocNetROIHeads (roi_heads_contextlocnet.py:284-335): ROILoopPool gives the RoI, frame and context pools of every
+  proposal ([3R, C, P, P]); all three go through the box head and `WSDDNOutputLayers(..., context=True)` scores them as
+  cls(RoI), det(frame) - det(context).
 * JTSMROIHeads, BOX branch (roi_heads_jtsm.py:197-752, BASELINE.json configs[2]): the OICR chain over JTSM's pooler --
   MOIPool restricted by the proposals' superpixel sets (`oh_labels`) -- with the pooled features scaled by
   `mask_scale = P^2 / (#non-empty bins + 1)` (roi_heads_jtsm.py:607-620, recomputed there from the returned arg-max with
@@ -33,6 +36,25 @@ class WSDDNROIHeadsB200(OICRROIHeadsB200):
         for k in ("refine_K", "refine_mist", "refine_reg", "box_refinery"):
             ret.pop(k, None)
         return ret
+
+
+class ContextLocNetROIHeadsB200(WSDDNROIHeadsB200):
+    def __init__(self, **kwargs):
+        super().__init__(**kwargs)
+        assert self.box_pooler is None or self.box_pooler.pooler_type == "ROILoopPool", "ContextLocNet pools with ROILoopPool"
+
+    def _forward_box(self, features, proposals):
+        feats = [features[f] for f in self.box_in_features]
+        x = self.box_pooler(feats, [p.proposal_boxes for p in proposals])  # [3R, C, P, P]: RoI | frame | context
+        scale = torch.cat([p.objectness_logits + 1 for p in proposals], dim=0)
+        x = x * torch.cat([scale, scale, scale], dim=0).view(-1, 1, 1, 1)
+        parts = list(torch.chunk(self.box_head(x), 3, dim=0))
+        if self.training:
+            predictions = self.box_predictor(parts, proposals, context=True, gt_classes_img_oh=self.gt_classes_img_oh)
+            return self.box_predictor.losses(predictions, proposals, self.gt_classes_img_oh)
+        predictions = self.box_predictor(parts, proposals, context=True)
+        pred_instances, _, all_scores, all_boxes = self.box_predictor.inference(predictions, proposals)
+        return pred_instances, all_scores, all_boxes
 
 
 class _NoRefine:
@@ -92,9 +114,9 @@ class JTSMROIHeadsB200(OICRROIHeadsB200):
 
 def register_all(registry):
     """Register the three heads in a detectron2 `ROI_HEADS_REGISTRY`."""
-    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, JTSMROIHeadsB200):
+    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, ContextLocNetROIHeadsB200, JTSMROIHeadsB200):
         registry.register(c)
     return registry
 
 
-__all__ = ["WSDDNROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]
+__all__ = ["WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]

@@ -158,3 +158,23 @@ def test_wsddn_layer_standalone_losses_and_autograd_without_fused_loss(cuda):
     img = torch.cat([t.sum(0, keepdim=True) for t in s.split([50, 40])]).clamp(1e-6, 1 - 1e-6)
     want = torch.nn.functional.binary_cross_entropy(img, oh)
     assert abs(res[0][0] - float(want)) <= 1e-5 * float(want)
+
+
+def test_wsddn_layer_contextlocnet_streams(cuda):
+    """`forward(context=True)` (fast_rcnn_wsddn.py:560-561, 600-619): C = cls(x), D = det(frame) - det(context), then the
+    usual per-image softmax product -- against the eager definition."""
+    from jtsm_b200.box_regression import Box2BoxTransform
+    from jtsm_b200.roi_heads import WSDDNOutputLayers
+    from jtsm_b200.structures import Boxes, Instances
+
+    g = torch.Generator().manual_seed(8)
+    layer = WSDDNOutputLayers(24, box2box_transform=Box2BoxTransform((10.0, 10.0, 5.0, 5.0)), num_classes=7).to(cuda)
+    feats = tuple(torch.rand(90, 24, generator=g).to(cuda).requires_grad_() for _ in range(3))
+    props = [Instances((600, 800), proposal_boxes=Boxes(torch.rand(n, 4, device=cuda) * 100)) for n in (50, 40)]
+    scores, deltas = layer(feats, props, context=True)
+    C = layer.cls(feats[0])
+    D = layer.det(feats[1]) - layer.det(feats[2])
+    want = torch.cat([torch.softmax(c, 1) * torch.softmax(d, 0) for c, d in zip(C.split([50, 40]), D.split([50, 40]))])
+    torch.testing.assert_close(scores, want, rtol=1e-5, atol=1e-9)
+    scores.sum().backward()
+    assert all(f.grad is not None and float(f.grad.abs().sum()) > 0 for f in feats)

@@ -118,6 +118,50 @@ def test_jtsm_heads_box_branch_pooling_and_step(cuda):
     assert len(inst) == 2 and tuple(all_scores[1].shape[-2:]) == (90, 7)
 
 
+@gpu
+def test_contextlocnet_heads_train_and_infer(cuda):
+    """ROILoopPool -> box head on the three pools -> cls(RoI), det(frame) - det(context) (roi_heads_contextlocnet.py:
+    284-335): loss equal to the eager composition over the un-fused ops, gradients reach the feature map."""
+    from jtsm_b200.box_regression import Box2BoxTransform
+    from jtsm_b200.poolers import ROIPooler
+    from jtsm_b200.roi_heads import ContextLocNetROIHeadsB200, DiscriminativeAdaptionNeck, WSDDNOutputLayers
+
+    torch.manual_seed(4)
+    c, k, d = 16, 6, 24
+    shape = type("ShapeSpec", (), dict(channels=c, height=7, width=7, stride=None))()
+    head = DiscriminativeAdaptionNeck(shape, fc_dims=(d, d))
+    pred = WSDDNOutputLayers(head.output_shape, box2box_transform=Box2BoxTransform((10.0, 10.0, 5.0, 5.0)), num_classes=k)
+    pooler = ROIPooler(output_size=7, scales=(1 / 8.0,), sampling_ratio=0, pooler_type="ROILoopPool")
+    heads = ContextLocNetROIHeadsB200(num_classes=k, box_in_features=["conv5"], box_pooler=pooler, box_head=head,
+                                      box_predictor=pred).to(cuda)
+    for m in heads.modules():
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+    feat, props, tgts, _ = _inputs(cuda, c=c, k=k)
+    heads.train()
+    _, losses = heads(None, {"conv5": feat}, props, tgts)
+    losses["loss_cls"].backward()
+    assert float(feat.grad.abs().sum()) > 0
+    with torch.no_grad():
+        x = pooler([feat.detach()], [p.proposal_boxes for p in props])
+        sc = torch.cat([p.objectness_logits + 1 for p in props])
+        x = head(x * torch.cat([sc, sc, sc]).view(-1, 1, 1, 1))
+        a, f, cx = torch.chunk(x, 3, dim=0)
+        C, D = pred.cls(a), pred.det(f) - pred.det(cx)
+        n = [len(p) for p in props]
+        s = torch.cat([torch.softmax(c_, 1) * torch.softmax(d_, 0) for c_, d_ in zip(C.split(n), D.split(n))])
+        img = torch.cat([t.sum(0, keepdim=True) for t in s.split(n)]).clamp(1e-6, 1 - 1e-6)
+        oh = torch.zeros_like(img)
+        for i, t in enumerate(tgts):
+            oh[i, t.gt_classes] = 1
+        want = torch.nn.functional.binary_cross_entropy(img, oh)
+    assert abs(float(losses["loss_cls"].detach()) - float(want)) <= 1e-5 * float(want)
+    heads.eval()
+    with torch.no_grad():
+        inst, _, all_scores, _ = heads(None, {"conv5": feat.detach()}, props)
+    assert len(inst) == 2 and tuple(all_scores[0].shape[-2:]) == (120, k + 1)
+
+
 def test_heads_register_in_a_registry():
     from jtsm_b200.roi_heads import register_all
 
@@ -129,4 +173,4 @@ def test_heads_register_in_a_registry():
             self.names.append(c.__name__)
 
     r = register_all(Reg())
-    assert r.names == ["OICRROIHeadsB200", "WSDDNROIHeadsB200", "JTSMROIHeadsB200"]
+    assert r.names == ["OICRROIHeadsB200", "WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "JTSMROIHeadsB200"]
