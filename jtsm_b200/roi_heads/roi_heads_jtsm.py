@@ -57,6 +57,39 @@ class ContextLocNetROIHeadsB200(WSDDNROIHeadsB200):
         return pred_instances, all_scores, all_boxes
 
 
+class CMILROIHeadsB200(OICRROIHeadsB200):
+    """CMILROIHeads (roi_heads_cmil.py:36-470), the part that differs from the OICR heads: after the usual pseudo-gt +
+    IoU label assignment of a branch, `ROILabel` re-labels the proposals -- seeds by class score, capped foreground /
+    background slots in a random visiting order, weights = the image score of the seed's class (:419-437).  The
+    reference moves S, the R x R IoU matrix, the labels and the class weights to the host for its CPU-only op on every
+    branch; here the IoU matrix comes from `jtsm_pairwise_iou` and the op runs on the device (`jtsm_roi_label_forward`).
+    One image per call, like the reference (its op asserts a square IoU matrix).  `box_predictor` may be a
+    `WSDDNOutputLayers(cmil=True)`; the un-merged scores (third element of its training 4-tuple) seed the branches."""
+
+    def __init__(self, *, roi_label=None, **kwargs):
+        super().__init__(**kwargs)
+        self.roi_label = roi_label
+
+    @torch.no_grad()
+    def _label_proposals(self, prev_scores, prev_boxes, proposals, counts, suffix=""):
+        out = super()._label_proposals(prev_scores, prev_boxes, proposals, counts, suffix)
+        if self.roi_label is None:
+            return out
+        assert len(proposals) == 1, "ROILabel takes the proposals of ONE image (square IoU matrix)"
+        from .. import ops
+
+        boxes = proposals[0].proposal_boxes.tensor
+        U = ops.pairwise_iou(boxes, boxes)
+        RL, RW = self.roi_label(prev_scores, U, self.gt_classes_img_oh, self.pred_class_img_logits)
+        q = Instances(proposals[0].image_size)
+        for name, v in out[0].get_fields().items():
+            if name not in ("gt_classes", "gt_weights", "loss_weights"):
+                q.set(name, v)
+        q.gt_classes = RL.to(torch.int64)  # :436-437; the losses derive their row weights from gt_weights again
+        q.gt_weights = RW.to(torch.float32)
+        return [q]
+
+
 class _NoRefine:
     """cfg view with WSL.REFINE_NUM = 0 (the WSDDN configs do not carry the refinement keys)."""
 
@@ -114,9 +147,9 @@ class JTSMROIHeadsB200(OICRROIHeadsB200):
 
 def register_all(registry):
     """Register the three heads in a detectron2 `ROI_HEADS_REGISTRY`."""
-    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, ContextLocNetROIHeadsB200, JTSMROIHeadsB200):
+    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, ContextLocNetROIHeadsB200, CMILROIHeadsB200, JTSMROIHeadsB200):
         registry.register(c)
     return registry
 
 
-__all__ = ["WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]
+__all__ = ["WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "CMILROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]

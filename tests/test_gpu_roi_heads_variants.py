@@ -162,6 +162,56 @@ def test_contextlocnet_heads_train_and_infer(cuda):
     assert len(inst) == 2 and tuple(all_scores[0].shape[-2:]) == (120, k + 1)
 
 
+@gpu
+def test_cmil_heads_relabel_with_roi_label(cuda):
+    """CMILROIHeadsB200: every branch's labels are ROILabel's (roi_heads_cmil.py:419-437), computed on the device from
+    the branch's input scores, the proposals' IoU matrix, the image labels and the image scores -- compared with the
+    restatement (oracle/ref_cmil.py, pinned to the reference's C++) under the same visiting order."""
+    from jtsm_b200.box_regression import Box2BoxTransform
+    from jtsm_b200.layers import ROILabel
+    from jtsm_b200.poolers import ROIPooler
+    from jtsm_b200.roi_heads import CMILROIHeadsB200, DiscriminativeAdaptionNeck, OICROutputLayers, WSDDNOutputLayers
+    from oracle import ref_cmil, ref_heads
+
+    torch.manual_seed(6)
+    c, k, d, kr = 16, 6, 24, 2
+    shape = type("ShapeSpec", (), dict(channels=c, height=7, width=7, stride=None))()
+    head = DiscriminativeAdaptionNeck(shape, fc_dims=(d, d))
+    b2b = Box2BoxTransform(weights=(10.0, 10.0, 5.0, 5.0))
+    pred = WSDDNOutputLayers(head.output_shape, box2box_transform=b2b, num_classes=k)
+    refs = [OICROutputLayers(head.output_shape, box2box_transform=b2b, num_classes=k, refine_k=i, refine_reg=[False] * kr)
+            for i in range(kr)]
+    pooler = ROIPooler(output_size=7, scales=(1 / 8.0,), sampling_ratio=0, pooler_type="ROIPool")
+    gen = torch.Generator(device=cuda).manual_seed(11)
+    label = ROILabel(0.3, 0.3, 0.0, 32, 96, 1, 0, 1 << 20, generator=gen)
+    heads = CMILROIHeadsB200(num_classes=k, box_in_features=["conv5"], box_pooler=pooler, box_head=head, box_predictor=pred,
+                             refine_K=kr, refine_reg=[False] * kr, box_refinery=refs, roi_label=label).to(cuda)
+    feat, props, tgts, _ = _inputs(cuda, counts=(400,), c=c, k=k)
+    heads.train()
+    seen = []
+    orig = label.forward
+
+    def spy(S, U, L, CW, perm=None):
+        perm = torch.randperm(S.shape[0], device=S.device, generator=gen)
+        RL, RW = orig(S, U, L, CW, perm=perm)
+        seen.append((S.cpu().numpy(), U.cpu().numpy(), L.cpu().numpy(), CW.cpu().numpy(), perm.cpu().numpy(),
+                     RL.cpu().numpy(), RW.cpu().numpy()))
+        return RL, RW
+
+    label.forward = spy
+    _, losses = heads(None, {"conv5": feat}, props, tgts)
+    assert set(losses) == {"loss_cls", "loss_cls_r0", "loss_cls_r1"} and len(seen) == kr
+    sum(losses.values()).backward()
+    assert torch.isfinite(feat.grad).all() and float(feat.grad.abs().sum()) > 0
+    boxes = props[0].proposal_boxes.tensor.cpu()
+    for S, U, L, CW, perm, RL, RW in seen:
+        assert np.array_equal(U, ref_heads.pairwise_iou(boxes, boxes).numpy())
+        want = ref_cmil.roi_label_forward(S, U, L, CW.reshape(-1), perm, 0.3, 0.3, 0.0, 32, 96, 1)
+        assert np.array_equal(RL, want["RL"]) and np.array_equal(RW, want["RW"])
+        assert want["bg_rois"] == 97
+    assert int(label.P[9]) == kr
+
+
 def test_heads_register_in_a_registry():
     from jtsm_b200.roi_heads import register_all
 
@@ -173,4 +223,5 @@ def test_heads_register_in_a_registry():
             self.names.append(c.__name__)
 
     r = register_all(Reg())
-    assert r.names == ["OICRROIHeadsB200", "WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "JTSMROIHeadsB200"]
+    assert r.names == ["OICRROIHeadsB200", "WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "CMILROIHeadsB200",
+                       "JTSMROIHeadsB200"]
