@@ -122,6 +122,27 @@ class OICROutputLayers(nn.Module):
             losses["loss_box_reg" + suffix] = lb.reshape(())
         return {k: v * self.loss_weight.get(k, 1.0) for k, v in losses.items()}
 
+    def losses_pcl(self, predictions, proposals, last_scores, gt_classes_img_oh):
+        """The PCL refinement loss (fast_rcnn_oicr.py:589-613 -> PCLOutputs.pcl_loss :917-937): proposal-cluster targets
+        from the PREVIOUS stream's scores (`jtsm_b200.pcl.PCL`: centre selection on the host like the reference's
+        sklearn / numpy code, proposal clusters on the device) and `pcl_loss` on this stream's softmax (background =
+        column 0 in PCL's layout).  One image per call, as the reference asserts."""
+        from .. import pcl
+        from ..layers import pcl_loss
+
+        scores, proposal_deltas = predictions
+        assert len(proposals) == 1, "PCL: batch size shoud be equal to 1"
+        if self.has_reg:
+            raise NotImplementedError("PCL with WSL.REFINE_REG is not ported")
+        probs = torch.softmax(scores, dim=-1)
+        im_labels = gt_classes_img_oh.detach().cpu().numpy()
+        t = pcl.PCL(proposals[0].proposal_boxes.tensor, last_scores.detach(), im_labels, probs.detach())
+        loss = pcl_loss(probs, t["labels"], t["cls_loss_weights"], t["gt_assignment"], t["pc_labels"], t["pc_probs"],
+                        t["pc_count"], t["img_cls_loss_weights"], t["im_labels_real"])
+        scores._jtsm_probs = probs.detach()
+        losses = {"loss_cls_r" + str(self.refine_k): loss}
+        return {k: v * self.loss_weight.get(k, 1.0) for k, v in losses.items()}
+
     def accuracy_counters(self, predictions):
         """Device int32 [4] behind `_log_accuracy` (fast_rcnn_oicr.py:252-280), without its four host syncs; None
         before `losses` ran on these predictions."""

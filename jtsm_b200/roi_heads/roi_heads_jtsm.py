@@ -90,6 +90,27 @@ class CMILROIHeadsB200(OICRROIHeadsB200):
         return [q]
 
 
+class PCLROIHeadsB200(OICRROIHeadsB200):
+    """PCLROIHeads (roi_heads_pcl.py:300-368): the refinement streams are trained with the PCL loss on proposal clusters
+    built from the previous stream's scores instead of OICR's top-1 pseudo labels; inference rotates the background
+    column last (`pcl_bg=True`)."""
+
+    def _forward_predictors(self, box_features, proposals):
+        if not self.training:
+            predictions_K = [self.box_refinery[k](box_features) for k in range(self.refine_K)]
+            pred_instances, _, all_scores, all_boxes = self.box_refinery[-1].inference(predictions_K, proposals, pcl_bg=True)
+            return pred_instances, all_scores, all_boxes
+        predictions = self.box_predictor(box_features, proposals, gt_classes_img_oh=self.gt_classes_img_oh)
+        losses = self.box_predictor.losses(predictions, proposals, self.gt_classes_img_oh)
+        self.pred_class_img_logits = self.box_predictor.predict_probs_img(predictions, proposals).detach()
+        prev_scores = predictions[0].detach()
+        for k in range(self.refine_K):
+            predictions_k = self.box_refinery[k](box_features)
+            losses.update(self.box_refinery[k].losses_pcl(predictions_k, proposals, prev_scores, self.gt_classes_img_oh))
+            prev_scores = self.box_refinery[k].predict_probs(predictions_k, proposals)[0].detach()
+        return losses
+
+
 class _NoRefine:
     """cfg view with WSL.REFINE_NUM = 0 (the WSDDN configs do not carry the refinement keys)."""
 
@@ -147,9 +168,10 @@ class JTSMROIHeadsB200(OICRROIHeadsB200):
 
 def register_all(registry):
     """Register the three heads in a detectron2 `ROI_HEADS_REGISTRY`."""
-    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, ContextLocNetROIHeadsB200, CMILROIHeadsB200, JTSMROIHeadsB200):
+    for c in (OICRROIHeadsB200, WSDDNROIHeadsB200, ContextLocNetROIHeadsB200, CMILROIHeadsB200, PCLROIHeadsB200,
+              JTSMROIHeadsB200):
         registry.register(c)
     return registry
 
 
-__all__ = ["WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "CMILROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]
+__all__ = ["WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "CMILROIHeadsB200", "PCLROIHeadsB200", "JTSMROIHeadsB200", "register_all", "get_image_level_gt"]

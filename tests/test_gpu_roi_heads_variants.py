@@ -212,6 +212,61 @@ def test_cmil_heads_relabel_with_roi_label(cuda):
     assert int(label.P[9]) == kr
 
 
+@gpu
+def test_pcl_heads_refinement_loss(cuda):
+    """PCLROIHeadsB200 (roi_heads_pcl.py:329-349): per stream, PCL targets from the previous stream's scores + pcl_loss on
+    this stream's softmax.  The first stream's loss is recomputed from the pieces that are pinned to the reference
+    (host centre selection with the checker's IoU, oracle/ref_pcl.py proposal clusters, oracle C pcl_loss)."""
+    from jtsm_b200 import pcl
+    from jtsm_b200.box_regression import Box2BoxTransform
+    from jtsm_b200.poolers import ROIPooler
+    from jtsm_b200.roi_heads import DiscriminativeAdaptionNeck, OICROutputLayers, PCLROIHeadsB200, WSDDNOutputLayers
+    from oracle import capi, ref_heads, ref_pcl
+
+    torch.manual_seed(9)
+    c, k, d, kr = 16, 6, 24, 2
+    shape = type("ShapeSpec", (), dict(channels=c, height=7, width=7, stride=None))()
+    head = DiscriminativeAdaptionNeck(shape, fc_dims=(d, d))
+    b2b = Box2BoxTransform(weights=(10.0, 10.0, 5.0, 5.0))
+    pred = WSDDNOutputLayers(head.output_shape, box2box_transform=b2b, num_classes=k)
+    refs = [OICROutputLayers(head.output_shape, box2box_transform=b2b, num_classes=k, refine_k=i, refine_reg=[False] * kr)
+            for i in range(kr)]
+    pooler = ROIPooler(output_size=7, scales=(1 / 8.0,), sampling_ratio=0, pooler_type="ROIPool")
+    heads = PCLROIHeadsB200(num_classes=k, box_in_features=["conv5"], box_pooler=pooler, box_head=head, box_predictor=pred,
+                            refine_K=kr, refine_reg=[False] * kr, box_refinery=refs).to(cuda)
+    for m in heads.modules():
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+    feat, props, tgts, _ = _inputs(cuda, counts=(500,), c=c, k=k)
+    heads.train()
+    _, losses = heads(None, {"conv5": feat}, props, tgts)
+    assert set(losses) == {"loss_cls", "loss_cls_r0", "loss_cls_r1"}
+    sum(losses.values()).backward()
+    assert torch.isfinite(feat.grad).all() and float(feat.grad.abs().sum()) > 0
+    # stream 0 from the pinned pieces
+    with torch.no_grad():
+        x, _ = heads._pool({"conv5": feat.detach()}, props)
+        x = heads.box_head(x)
+        mil = heads.box_predictor(x, props)[0]
+        probs = torch.softmax(heads.box_refinery[0](x)[0], dim=-1)
+    boxes = props[0].proposal_boxes.tensor.cpu().numpy()
+    oh = np.zeros((1, k), np.float32)
+    oh[0, tgts[0].gt_classes.cpu().numpy()] = 1
+    cpu_iou = lambda b: ref_heads.pairwise_iou(torch.from_numpy(b), torch.from_numpy(b)).numpy()
+    cb, cc, cs = pcl.graph_centers(boxes, np.clip(mil.cpu().numpy(), 1e-9, 1 - 1e-9), oh, iou_fn=cpu_iou)
+    pn = np.clip(probs.cpu().numpy(), 1e-9, 1 - 1e-9)
+    t = ref_pcl.proposal_clusters(boxes, cb, cc, cs, pn)
+    real = np.concatenate([np.ones((1, 1), np.float32), oh], axis=1)
+    _, want = capi.pcl_loss_forward(probs.cpu().numpy(), t["labels"].astype(np.float32), t["cls_loss_weights"],
+                                    t["pc_labels"].astype(np.float32), t["pc_probs"], t["img_cls_loss_weights"], real)
+    want = float(want)
+    assert abs(float(losses["loss_cls_r0"].detach()) - want) <= 1e-4 * abs(want)
+    heads.eval()
+    with torch.no_grad():
+        inst, _, all_scores, _ = heads(None, {"conv5": feat.detach()}, props)
+    assert len(inst) == 1 and tuple(all_scores[0].shape[-2:]) == (500, k + 1)
+
+
 def test_heads_register_in_a_registry():
     from jtsm_b200.roi_heads import register_all
 
@@ -224,4 +279,4 @@ def test_heads_register_in_a_registry():
 
     r = register_all(Reg())
     assert r.names == ["OICRROIHeadsB200", "WSDDNROIHeadsB200", "ContextLocNetROIHeadsB200", "CMILROIHeadsB200",
-                       "JTSMROIHeadsB200"]
+                       "PCLROIHeadsB200", "JTSMROIHeadsB200"]
