@@ -55,11 +55,13 @@ struct PoolWorkspace {
   int* slow_count;   // [1]            number of bins without a fast descriptor
   int* slow_list;    // [R * PH * PW]  their ids (r * PH*PW + bin), in no particular order; bit 30 = does not fit a band
   unsigned char* bband;  // [R * PH * PW]  row band of the bin (planes larger than shared memory, RmqBands)
-  // per (image, band) lists of the RoIs that have bins in the band (banded planes with <= kBandListBands bands): the
-  // banded main loop walks these instead of filtering every bin of the call by its band
-  int* band_cnt;   // [batch * kBandListBands]
-  int* band_list;  // [batch * kBandListBands * R]
-  int num_rois;    // R (stride of band_list)
+  // bin ids (r * PH*PW + bin) grouped by (image, band) for banded planes with <= kBandListBands bands: the banded main
+  // loop walks its band's segment densely instead of filtering every bin of the call by its band
+  int* band_cnt;   // [batch * kBandListBands]      bins per (image, band)
+  int* band_off;   // [batch * kBandListBands + 1]  exclusive scan of band_cnt
+  int* band_cur;   // [batch * kBandListBands]      fill cursors
+  int* band_list;  // [R * PH * PW]
+  int num_rois;    // R
 };
 constexpr int kBandListBands = 16;
 
@@ -106,8 +108,8 @@ inline size_t pool_workspace_bytes(int batch, int num_rois, int pooled_h, int po
   b += 2 * align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
   b += align_up((size_t)num_rois * 4, 256);
   b += align_up((size_t)num_rois * pooled_h * pooled_w, 256);  // bband
-  b += align_up((size_t)batch * kBandListBands * 4, 256);
-  b += align_up((size_t)batch * kBandListBands * num_rois * 4, 256);
+  b += 3 * align_up(((size_t)batch * kBandListBands + 1) * 4, 256);
+  b += align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
   return b + 256;
 }
 
@@ -126,7 +128,9 @@ inline PoolWorkspace carve_pool_workspace(void* ws, int batch, int num_rois, int
   w.rscale = (float*)p; p += align_up((size_t)num_rois * 4, 256);
   w.slow_list = (int*)p; p += align_up((size_t)num_rois * pooled_h * pooled_w * 4, 256);
   w.bband = (unsigned char*)p; p += align_up((size_t)num_rois * pooled_h * pooled_w, 256);
-  w.band_cnt = (int*)p; p += align_up((size_t)batch * kBandListBands * 4, 256);
+  w.band_cnt = (int*)p; p += align_up(((size_t)batch * kBandListBands + 1) * 4, 256);
+  w.band_off = (int*)p; p += align_up(((size_t)batch * kBandListBands + 1) * 4, 256);
+  w.band_cur = (int*)p; p += align_up(((size_t)batch * kBandListBands + 1) * 4, 256);
   w.band_list = (int*)p;
   w.num_rois = num_rois;
   return w;

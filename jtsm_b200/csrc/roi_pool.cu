@@ -52,12 +52,16 @@ roi_pool_prep_kernel(const float* __restrict__ rois, int num_rois, int batch, in
       atomicMin(ws.first + b, r);
       atomicMin(ws.neg_last + b, -r);
       if (want_desc && bands.nb > 1 && bands.nb <= kBandListBands) {
-        // the bands this RoI has bins in (a bin belongs to the band of its first row; non-decreasing in the bin row)
-        const int b_lo = band_of(range_lo(ws.hbins[(size_t)r * PH]), bands);
-        const int b_hi = band_of(range_lo(ws.hbins[(size_t)r * PH + PH - 1]), bands);
-        for (int bb = b_lo; bb <= b_hi; ++bb) {
-          const int slot = b * kBandListBands + bb;
-          ws.band_list[(size_t)slot * num_rois + atomicAdd(ws.band_cnt + slot, 1)] = r;
+        // bins per (image, band): a bin belongs to the band of its first row (non-decreasing in the bin row), so a RoI's
+        // bins of one band are a run of whole bin rows
+        int run_band = -1, run_rows = 0;
+        for (int p = 0; p <= PH; ++p) {
+          const int bb = p < PH ? band_of(range_lo(ws.hbins[(size_t)r * PH + p]), bands) : -2;
+          if (bb != run_band) {
+            if (run_rows > 0) atomicAdd(ws.band_cnt + b * kBandListBands + run_band, run_rows * PW);
+            run_band = bb, run_rows = 0;
+          }
+          ++run_rows;
         }
       }
     }
@@ -532,6 +536,41 @@ int launch_roi_pool_fwd(const void* input, int batch, int channels, int height, 
   return cuda_status();
 }
 
+// band lists, pass 2: offsets of the (image, band) segments, then every RoI writes the ids of its bins into its bands'
+// segments (a run of whole bin rows per band; the order of the runs inside a segment is whatever the atomics give --
+// every bin is written exactly once by the pooling kernel either way)
+__global__ void band_scan_kernel(int slots, PoolWorkspace ws) {
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int i = 0; i < slots; ++i) {
+      ws.band_off[i] = acc;
+      acc += ws.band_cnt[i];
+      ws.band_cur[i] = 0;
+    }
+    ws.band_off[slots] = acc;
+  }
+}
+__global__ void band_fill_kernel(int num_rois, int PH, int PW, RmqBands bands, PoolWorkspace ws) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= num_rois) return;
+  const int b = ws.batch_idx[r];
+  if (b < 0) return;
+  int run_band = -1, run_rows = 0, run_p0 = 0;
+  for (int p = 0; p <= PH; ++p) {
+    const int bb = p < PH ? band_of(range_lo(ws.hbins[(size_t)r * PH + p]), bands) : -2;
+    if (bb != run_band) {
+      if (run_rows > 0) {
+        const int slot = b * kBandListBands + run_band, n = run_rows * PW;
+        int* dst = ws.band_list + ws.band_off[slot] + atomicAdd(ws.band_cur + slot, n);
+        const int id0 = r * PH * PW + run_p0 * PW;
+        for (int k = 0; k < n; ++k) dst[k] = id0 + k;
+      }
+      run_band = bb, run_rows = 0, run_p0 = p;
+    }
+    ++run_rows;
+  }
+}
+
 int run_prep(const float* rois, int num_rois, int batch, int channels, int height, int width, float scale,
              int PH, int PW, const float* row_scale, const PoolWorkspace& ws, cudaStream_t st, int force_desc = 0,
              bool packed = false) {
@@ -544,6 +583,11 @@ int run_prep(const float* rois, int num_rois, int batch, int channels, int heigh
   roi_pool_prep_kernel<<<(num_rois + kPrepRois - 1) / kPrepRois, kPrepThreads, 0, st>>>(
       rois, num_rois, batch, height, width, scale, PH, PW, row_scale, want_desc, bands, ws);
   count_launch();
+  if (want_desc && bands.nb > 1 && bands.nb <= kBandListBands && num_rois > 0) {
+    band_scan_kernel<<<1, 32, 0, st>>>(batch * kBandListBands, ws);
+    band_fill_kernel<<<(num_rois + 255) / 256, 256, 0, st>>>(num_rois, PH, PW, bands, ws);
+    count_launch(2);
+  }
   return cuda_status();
 }
 

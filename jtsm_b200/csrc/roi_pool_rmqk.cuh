@@ -374,48 +374,58 @@ __device__ __forceinline__ void rk_main_loop_rows(const float* plane, const unsi
   }
 }
 
-// Main loop of a BANDED plane over the per-band RoI list (PoolWorkspace::band_list): a warp takes one RoI of image n that has
-// bins in this band and serves its PP bins 64 at a time (two independent chains per lane), keeping those of the band.
-// Against the filter form above (every (band, plane) pass sweeps all bins of the call and skips, warp by warp, those of
-// other bands) the work per pass is proportional to the band's own RoIs.  Entries [q0, q1) of the list.
+// Main loop of a BANDED plane over its band's segment of the bin-id list (PoolWorkspace::band_list, built by the prep
+// kernels): the generic loop above with one indirection -- position -> bin id -> descriptor -- so every lane of every
+// round holds a bin of THIS band (the filter form sweeps all bins of the call per (band, plane) pass and runs mostly
+// empty warps; a RoI-per-warp list form kept a third of the lanes busy on 150 x 200 maps).  Positions [j0, j1).
 template <typename T, typename A, bool kKeyed>
 __device__ __forceinline__ void rk_main_loop_list(const float* plane, const unsigned short* tabs, const PoolWorkspace& ws,
-                                                  int n, int c, int q0, int q1, int num_rois, int PP, int cpp, unsigned W,
-                                                  unsigned hw, int band, unsigned arg_off, T* __restrict__ output,
+                                                  int c, int j0, int j1, int PP, int cpp, unsigned W, unsigned hw,
+                                                  unsigned magic_pp, unsigned arg_off, T* __restrict__ output,
                                                   A* __restrict__ argmax) {
+  const unsigned o_c = (unsigned)(c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned plane_s = smem_u32(plane), tabs_s = smem_u32(tabs);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int* list = ws.band_list + (size_t)(n * kBandListBands + band) * num_rois;
-  for (int q = q0 + warp; q < q1; q += kRmqThreads / 32) {
-    const unsigned r = (unsigned)__ldg(list + q);
-    const float sc = __ldg(ws.rscale + r);
-    const unsigned i0 = r * (unsigned)PP, ob = r * (unsigned)cpp + (unsigned)(c * PP);
-    for (int b0 = 0; b0 < PP; b0 += 64) {
-      unsigned x[2];
+  constexpr int K = kRmqBinsPerThread;
+  unsigned j = (unsigned)j0 + threadIdx.x;
+  const unsigned j_end = (unsigned)j1;
+  unsigned xn[K], idn[K];
+  float scn[K];
+  auto fetch = [&](unsigned jj) {
 #pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int bin = b0 + k * 32 + lane;
-        x[k] = 0u;
-        if (bin < PP) {
-          x[k] = __ldg(ws.bdesc + i0 + bin);
-          if ((int)__ldg(ws.bband + i0 + bin) != band) x[k] = 0u;
-        }
+    for (int k = 0; k < K; ++k) {
+      const unsigned jk = jj + k * kRmqThreads;
+      xn[k] = 0u, idn[k] = 0u, scn[k] = 0.f;
+      if (jk < j_end) {
+        idn[k] = (unsigned)__ldg(ws.band_list + jk);
+        xn[k] = __ldg(ws.bdesc + idn[k]);
+        scn[k] = __ldg(ws.rscale + __umulhi(idn[k], magic_pp));
       }
-      RmqCand best[2];
-#pragma unroll
-      for (int k = 0; k < 2; ++k)
-        best[k] = kKeyed ? rk_query_fast(plane_s, tabs_s, x[k], W, hw)
-                         : rmq_query_fast(plane_s, tabs_s + (x[k] & 0x3FFFFu), ((x[k] >> 18) & 15u) * (2u * W),
-                                          (x[k] >> 22) & 31u);
-#pragma unroll
-      for (int k = 0; k < 2; ++k)
-        if ((int)x[k] < 0) {
-          const unsigned o = ob + (unsigned)(b0 + k * 32 + lane);
-          const bool none = !(best[k].v > -FLT_MAX);
-          output[o] = Elem<T>::from_f(__fmul_rn(best[k].v, sc));
-          argmax[o] = none ? Arg<A>::enc(-1) : (A)(best[k].i + arg_off);
-        }
     }
+  };
+  fetch(j);
+  while (j < j_end) {
+    unsigned x[K], o[K];
+    float sc[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      x[k] = xn[k], sc[k] = scn[k];
+      o[k] = idn[k] + __umulhi(idn[k], magic_pp) * o_r + o_c;
+    }
+    j += K * kRmqThreads;
+    fetch(j);
+    RmqCand best[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      best[k] = kKeyed ? rk_query_fast(plane_s, tabs_s, x[k], W, hw)
+                       : rmq_query_fast(plane_s, tabs_s + (x[k] & 0x3FFFFu), ((x[k] >> 18) & 15u) * (2u * W),
+                                        (x[k] >> 22) & 31u);
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      if ((int)x[k] < 0) {  // x >= 0: slow bin (left to the list) or past the end
+        const bool none = !(best[k].v > -FLT_MAX);
+        output[o[k]] = Elem<T>::from_f(__fmul_rn(best[k].v, sc[k]));
+        argmax[o[k]] = none ? Arg<A>::enc(-1) : (A)(best[k].i + arg_off);
+      }
   }
 }
 
@@ -489,7 +499,6 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const bool rows_loop = (staged & 2) != 0 && PH * PW <= kRmqThreads;  // bit 1 of `staged`: row-mapped main loop
   const bool band_list = kBanded && (staged & 4) != 0;                 // bit 2: per-band RoI lists (banded planes)
-  const int num_rois = ws.num_rois;
   staged &= 1;
   if (kMoi && !moi_rmq_gate(moi.slow_total, moi.total_bins, moi.gate_pct)) return;  // uniform: the list kernel runs
   const int hw = bands.Hb * W;  // cells of a full band = table stride (the whole plane when nb == 1)
@@ -624,10 +633,11 @@ roi_pool_fwd_rmq_kernel(const T* __restrict__ input, unsigned long long input_by
     if (it.nr > 0) r_hi = it.r0 + it.nr;
     if (band_list) {
       r_hi = chunk + 1;
-      const int cnt = __ldg(ws.band_cnt + it.n * kBandListBands + v.band);
-      const int q0 = (int)((long long)cnt * chunk / chunks), q1 = (int)((long long)cnt * (chunk + 1) / chunks);
-      rk_main_loop_list<T, A, kKeyed>(plane, tabs, ws, it.n, it.c, q0, q1, num_rois, PP, cpp, (unsigned)W, (unsigned)hw,
-                                      v.band, (unsigned)(v.row0 * W), output, argmax);
+      const int slot = it.n * kBandListBands + v.band;
+      const int off = __ldg(ws.band_off + slot), cnt = __ldg(ws.band_off + slot + 1) - off;
+      const int j0 = off + (int)((long long)cnt * chunk / chunks), j1 = off + (int)((long long)cnt * (chunk + 1) / chunks);
+      rk_main_loop_list<T, A, kKeyed>(plane, tabs, ws, it.c, j0, j1, PP, cpp, (unsigned)W, (unsigned)hw, magic_pp,
+                                      (unsigned)(v.row0 * W), output, argmax);
     } else if (!kMoi && !kKeyed && !kBanded && !ungrouped && rows_loop)
       rk_main_loop_rows<T, A>(plane, tabs, ws, it, PP, cpp, (unsigned)W, magic_pp, output, argmax);
     else if (ungrouped)

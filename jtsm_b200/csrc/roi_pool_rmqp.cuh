@@ -169,44 +169,54 @@ __device__ __forceinline__ void rp_main_loop(const unsigned* tabs, const PoolWor
   }
 }
 
-// banded plane over the per-band RoI list (see rk_main_loop_list): a warp per RoI, 64 bins at a time
+// banded plane over its band's segment of the bin-id list (see rk_main_loop_list): positions [j0, j1)
 template <typename T, typename A>
-__device__ __forceinline__ void rp_main_loop_list(const unsigned* tabs, const PoolWorkspace& ws, int n, int c, int q0, int q1,
-                                                  int num_rois, int PP, int cpp, unsigned W, int band, unsigned arg_off,
+__device__ __forceinline__ void rp_main_loop_list(const unsigned* tabs, const PoolWorkspace& ws, int c, int j0, int j1, int PP,
+                                                  int cpp, unsigned W, unsigned magic_pp, unsigned arg_off,
                                                   T* __restrict__ output, A* __restrict__ argmax) {
+  const unsigned o_c = (unsigned)(c * PP), o_r = (unsigned)(cpp - PP);
   const unsigned tabs_s = smem_u32(tabs);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int* list = ws.band_list + (size_t)(n * kBandListBands + band) * num_rois;
-  for (int q = q0 + warp; q < q1; q += kRmqThreads / 32) {
-    const unsigned r = (unsigned)__ldg(list + q);
-    const float sc = __ldg(ws.rscale + r);
-    const unsigned i0 = r * (unsigned)PP, ob = r * (unsigned)cpp + (unsigned)(c * PP);
-    for (int b0 = 0; b0 < PP; b0 += 64) {
-      unsigned x[2], best[2];
+  constexpr int K = kRmqBinsPerThread;
+  unsigned j = (unsigned)j0 + threadIdx.x;
+  const unsigned j_end = (unsigned)j1;
+  unsigned xn[K], idn[K];
+  float scn[K];
+  auto fetch = [&](unsigned jj) {
 #pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const int bin = b0 + k * 32 + lane;
-        x[k] = 0u;
-        if (bin < PP) {
-          x[k] = __ldg(ws.bdesc + i0 + bin);
-          if ((int)__ldg(ws.bband + i0 + bin) != band) x[k] = 0u;
-        }
+    for (int k = 0; k < K; ++k) {
+      const unsigned jk = jj + k * kRmqThreads;
+      xn[k] = 0u, idn[k] = 0u, scn[k] = 0.f;
+      if (jk < j_end) {
+        idn[k] = (unsigned)__ldg(ws.band_list + jk);
+        xn[k] = __ldg(ws.bdesc + idn[k]);
+        scn[k] = __ldg(ws.rscale + __umulhi(idn[k], magic_pp));
       }
-#pragma unroll
-      for (int k = 0; k < 2; ++k) {
-        const unsigned base = tabs_s + 2u * (x[k] & 0x3FFFFu), dh = ((x[k] >> 18) & 15u) * (4u * W), db = 2u * ((x[k] >> 22) & 31u);
-        best[k] = max(max(lds_u32(base), lds_u32(base + db)), max(lds_u32(base + dh), lds_u32(base + dh + db)));
-      }
-#pragma unroll
-      for (int k = 0; k < 2; ++k)
-        if ((int)x[k] < 0) {
-          const unsigned o = ob + (unsigned)(b0 + k * 32 + lane);
-          const bool none = (best[k] >> 16) == 0u;
-          const float v = none ? -FLT_MAX : rp_value<T>(best[k]);
-          output[o] = Elem<T>::from_f(__fmul_rn(v, sc));
-          argmax[o] = none ? Arg<A>::enc(-1) : (A)(0xFFFFu - (best[k] & 0xFFFFu) + arg_off);
-        }
     }
+  };
+  fetch(j);
+  while (j < j_end) {
+    unsigned x[K], o[K], best[K];
+    float sc[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      x[k] = xn[k], sc[k] = scn[k];
+      o[k] = idn[k] + __umulhi(idn[k], magic_pp) * o_r + o_c;
+    }
+    j += K * kRmqThreads;
+    fetch(j);
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const unsigned base = tabs_s + 2u * (x[k] & 0x3FFFFu), dh = ((x[k] >> 18) & 15u) * (4u * W), db = 2u * ((x[k] >> 22) & 31u);
+      best[k] = max(max(lds_u32(base), lds_u32(base + db)), max(lds_u32(base + dh), lds_u32(base + dh + db)));
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      if ((int)x[k] < 0) {
+        const bool none = (best[k] >> 16) == 0u;
+        const float v = none ? -FLT_MAX : rp_value<T>(best[k]);
+        output[o[k]] = Elem<T>::from_f(__fmul_rn(v, sc[k]));
+        argmax[o[k]] = none ? Arg<A>::enc(-1) : (A)(0xFFFFu - (best[k] & 0xFFFFu) + arg_off);
+      }
   }
 }
 
@@ -349,10 +359,10 @@ roi_pool_fwd_rmqp_kernel(const T* __restrict__ input, unsigned long long input_b
     if (it.nr > 0) r_hi = it.r0 + it.nr;
     if (band_list) {
       r_hi = chunk + 1;
-      const int cnt = __ldg(ws.band_cnt + it.n * kBandListBands + v.band);
-      const int q0 = (int)((long long)cnt * chunk / chunks), q1 = (int)((long long)cnt * (chunk + 1) / chunks);
-      rp_main_loop_list<T, A>(tabs, ws, it.n, it.c, q0, q1, ws.num_rois, PP, cpp, (unsigned)W, v.band,
-                              (unsigned)(v.row0 * W), output, argmax);
+      const int slot = it.n * kBandListBands + v.band;
+      const int off = __ldg(ws.band_off + slot), cnt = __ldg(ws.band_off + slot + 1) - off;
+      const int j0 = off + (int)((long long)cnt * chunk / chunks), j1 = off + (int)((long long)cnt * (chunk + 1) / chunks);
+      rp_main_loop_list<T, A>(tabs, ws, it.c, j0, j1, PP, cpp, (unsigned)W, magic_pp, (unsigned)(v.row0 * W), output, argmax);
     } else if (ungrouped)
       rp_main_loop<T, A, true, kBanded>(tabs, ws, it, PP, cpp, (unsigned)W, magic_pp, v.band, (unsigned)(v.row0 * W), output,
                                         argmax);
