@@ -350,8 +350,10 @@ RmqBands pick_bands(int height, int width, int PH, bool packed = false) {
   if (hw <= 0 || width > 4096) return {0, 0, 0};
   if (packed) {
     if (hw < (1 << 20) && rp_smem_core((int)hw) <= 227 * 1024) return {1, height, height};
-    int Hb = (int)((227 * 1024 - kRpHeader - 64) / (40 * (long long)width));
-    while (Hb > 0 && rp_smem_core(Hb * width) > 227 * 1024) --Hb;
+    // 40 B of tables + 2 B of bulk-copy staging per cell: with only two or three bands the band's plane is worth
+    // fetching behind the previous band's queries (the index kernel's many-band geometries prefer taller bands)
+    int Hb = (int)((227 * 1024 - kRpHeader - 128) / (42 * (long long)width));
+    while (Hb > 0 && rp_smem_core(Hb * width) + rk_stage_bytes(Hb * width, 2) > 227 * 1024) --Hb;
     const int O = (height + PH - 1) / PH + 1;
     const int S = Hb - O;
     if (Hb < 3 || S < 1 || 3 * S < Hb || (long long)Hb * width > 65535) return {0, 0, 0};
@@ -474,7 +476,7 @@ int launch_rmqp(const void* input, int batch, int channels, int height, int widt
   const int planes = real_planes * bands.nb;
   const int hw = bands.Hb * width;
   const size_t stage = rk_stage_bytes(hw, (int)sizeof(T));
-  const int staged = bands.nb == 1 && rp_smem_core(hw) + stage <= 227 * 1024 && tuning("roi_pool_fwd_tma", 1);
+  const int staged = rp_smem_core(hw) + stage <= 227 * 1024 && tuning("roi_pool_fwd_tma", 1);
   const size_t smem = rp_smem_core(hw) + (staged ? stage : 0);
   auto kern = roi_pool_fwd_rmqp_kernel<T, A, false>;
   if (bands.nb > 1) kern = roi_pool_fwd_rmqp_kernel<T, A, true>;
